@@ -1,0 +1,318 @@
+/*
+ * ORACLE — TEST INFRASTRUCTURE ONLY (see orc_board.h).
+ * Pointer-tree MCTS restated from reference mcts_alphaZero.py:24-192 (TreeNode, MCTS)
+ * and mcts_pure.py:15-243 (rollout_policy_fn, policy_value_fn, TreeNode, MCTS).
+ * Numeric types follow what the reference actually computes with a Python-float leaf
+ * value: prior P float32 (AlphaZero) or float64 (pure), c_puct*P in
+ * P's type, sqrt/div/Q in float64.
+ */
+#include "orc_board.h"
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+typedef struct {
+    int W, H, c1, c2, c3;
+    const float *p[16];
+} orc_net;
+int orc_net_forward(const orc_net *net, const float *planes, int B, float *logp, float *value);
+
+enum { ORC_EVAL_NET = 0, ORC_EVAL_HASH = 1, ORC_EVAL_PURE = 2, ORC_EVAL_CALLBACK = 3 };
+
+/* host callback evaluator: fills probs[n_avail] for board->availables order and *value */
+typedef void (*orc_eval_cb)(const orc_board *b, float *probs, float *value);
+
+typedef struct orc_node {
+    struct orc_node *parent;
+    int n_children;
+    int *acts;               /* insertion order = evaluator order (ascending moves) */
+    struct orc_node **kids;
+    int n_visits;
+    double Q, u, P;
+    int p_f32;               /* prior is np.float32 (AlphaZero) vs float64 (pure) */
+} orc_node;
+
+typedef struct {
+    orc_node *root;
+    double c_puct;
+    int n_playout;
+    int eval_kind;
+    const orc_net *net;
+    orc_eval_cb cb;
+    uint64_t salt;           /* hash evaluator salt / philox seed for rollouts */
+    uint32_t game_id, search_id, playout_idx;
+    long long n_evals, n_terminal, n_rollout_plies, n_nodes;
+} orc_mcts;
+
+static orc_node *node_new(orc_mcts *m, orc_node *parent, double P, int p_f32)
+{
+    orc_node *n = (orc_node *)calloc(1, sizeof(orc_node));
+    n->parent = parent;
+    n->P = P;
+    n->p_f32 = p_f32;
+    m->n_nodes++;
+    return n;
+}
+
+static void node_free(orc_node *n)
+{
+    if (!n) return;
+    for (int i = 0; i < n->n_children; ++i) node_free(n->kids[i]);
+    free(n->acts);
+    free(n->kids);
+    free(n);
+}
+
+/* mcts_alphaZero.py:38-45 expand (children keyed by action, inserted in evaluator order) */
+static void node_expand(orc_mcts *m, orc_node *n, const int *acts, const double *probs, int k,
+                        int p_f32)
+{
+    if (k == 0) return;
+    n->acts = (int *)malloc(sizeof(int) * k);
+    n->kids = (orc_node **)malloc(sizeof(orc_node *) * k);
+    n->n_children = k;
+    for (int i = 0; i < k; ++i) {
+        n->acts[i] = acts[i];
+        n->kids[i] = node_new(m, n, probs[i], p_f32);
+    }
+}
+
+/* mcts_alphaZero.py:75-83 get_value: u = c_puct * P * sqrt(N_parent) / (1 + N); Q + u */
+static double node_get_value(orc_node *n, double c_puct)
+{
+    double cp;
+    if (n->p_f32) cp = (double)((float)c_puct * (float)n->P);
+    else cp = c_puct * n->P;
+    n->u = cp * sqrt((double)n->parent->n_visits) / (double)(1 + n->n_visits);
+    return n->Q + n->u;
+}
+
+/* mcts_alphaZero.py:48-55 select: Python max -> first maximum in insertion order */
+static int node_select(orc_node *n, double c_puct)
+{
+    int best = 0;
+    double bv = node_get_value(n->kids[0], c_puct);
+    for (int i = 1; i < n->n_children; ++i) {
+        double v = node_get_value(n->kids[i], c_puct);
+        if (v > bv) { bv = v; best = i; }
+    }
+    return best;
+}
+
+/* mcts_alphaZero.py:57-73 update / update_recursive (parent first, with -value) */
+static void node_update_recursive(orc_node *n, double leaf_value)
+{
+    if (n->parent) node_update_recursive(n->parent, -leaf_value);
+    n->n_visits += 1;
+    n->Q += 1.0 * (leaf_value - n->Q) / (double)n->n_visits;
+}
+
+static uint64_t splitmix64(uint64_t x)
+{
+    x += 0x9E3779B97F4A7C15ull;
+    uint64_t z = x;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+/* Synthetic, integer-defined evaluator used to drive oracle and CUDA tree kernels with
+ * bit-identical priors/values (not in the reference; numpy twin in tests/helpers.py). */
+void orc_hash_eval(const orc_board *b, uint64_t salt, float *probs /*[n_avail]*/, float *value)
+{
+    uint64_t key = splitmix64(salt + 1000ull + (uint64_t)b->current_player);
+    int S = b->width * b->height;
+    for (int m = 0; m < S; ++m)
+        if (b->states[m]) key ^= splitmix64(salt + (uint64_t)(m * 2 + (b->states[m] - 1)) + 1ull);
+    uint32_t sum = 0;
+    uint32_t w[ORC_MAXS];
+    for (int i = 0; i < b->n_avail; ++i) {
+        uint64_t h = splitmix64(key + (uint64_t)b->availables[i] + 1ull);
+        uint32_t t = (uint32_t)(h >> 56) + 1u;
+        w[i] = t * t * t;
+        sum += w[i];
+    }
+    for (int i = 0; i < b->n_avail; ++i) probs[i] = (float)w[i] / (float)sum;
+    int vi = (int)(splitmix64(key ^ 0x5555555555555555ull) % 2001ull) - 1000;
+    *value = (float)vi / 1000.0f;
+}
+
+/* policy_value_net_pytorch.py:96-115 policy_value_fn (value wrapped as float) */
+static void eval_net(orc_mcts *m, const orc_board *b, float *probs, float *value)
+{
+    int S = b->width * b->height;
+    double st[4 * ORC_MAXS];
+    float pl[4 * ORC_MAXS], logp[ORC_MAXS];
+    orc_board_current_state(b, st);
+    for (int i = 0; i < 4 * S; ++i) pl[i] = (float)st[i];
+    orc_net_forward(m->net, pl, 1, logp, value);
+    for (int i = 0; i < b->n_avail; ++i) probs[i] = expf(logp[b->availables[i]]);
+}
+
+/* mcts_pure.py:193-212 _evaluate_rollout with rollout_policy_fn (:15-30): each ply a
+ * uniformly random move of the current move_target box.  The reference draws
+ * np.random.rand per candidate and takes the argmax (= uniform choice); here the choice
+ * is index = mulhi32(philox(...)[0], n_target), bit-identical to the CUDA rollout kernel. */
+static int evaluate_rollout(orc_mcts *m, orc_board *b, int limit)
+{
+    int player = b->current_player;
+    int winner = -1, end = 0;
+    for (int i = 0; i < limit; ++i) {
+        end = orc_board_game_end(b, &winner);
+        if (end) break;
+        orc_board_get_move_target(b);
+        uint32_t r[4];
+        orc_philox4x32((uint32_t)m->salt, (uint32_t)(m->salt >> 32), m->playout_idx, (uint32_t)i,
+                       m->game_id, m->search_id, r);
+        uint32_t idx = (uint32_t)(((uint64_t)r[0] * (uint64_t)b->n_target) >> 32);
+        orc_board_do_move(b, b->move_target[idx]);
+        m->n_rollout_plies++;
+    }
+    if (!end) winner = -1; /* limit reached: reference keeps the last winner (-1) */
+    if (winner == -1) return 0;
+    return winner == player ? 1 : -1;
+}
+
+/* mcts_alphaZero.py:113-148 _playout / mcts_pure.py:156-191 _playout. */
+static void playout(orc_mcts *m, orc_board *state)
+{
+    orc_node *node = m->root;
+    while (node->n_children != 0) {
+        int i = node_select(node, m->c_puct);
+        orc_board_do_move(state, node->acts[i]);
+        node = node->kids[i];
+    }
+    int acts[ORC_MAXS];
+    double probs[ORC_MAXS];
+    float pf[ORC_MAXS];
+    float vf = 0.f;
+    int k = 0, p_f32 = 1;
+    double leaf_value = 0.0;
+    /* the evaluator is called BEFORE the end check (:132-134 / :176-179) */
+    if (m->eval_kind == ORC_EVAL_PURE) {
+        orc_board_get_move_target(state);               /* mcts_pure.py:33-46 */
+        k = state->n_target;
+        for (int i = 0; i < k; ++i) { acts[i] = state->move_target[i]; probs[i] = 1.0 / (double)k; }
+        p_f32 = 0;
+    } else {
+        if (m->eval_kind == ORC_EVAL_NET) eval_net(m, state, pf, &vf);
+        else if (m->eval_kind == ORC_EVAL_HASH) orc_hash_eval(state, m->salt, pf, &vf);
+        else m->cb(state, pf, &vf);
+        k = state->n_avail;
+        for (int i = 0; i < k; ++i) { acts[i] = state->availables[i]; probs[i] = (double)pf[i]; }
+        leaf_value = (double)vf;
+    }
+    m->n_evals++;
+    int winner;
+    int end = orc_board_game_end(state, &winner);
+    if (!end) node_expand(m, node, acts, probs, k, p_f32);
+    if (m->eval_kind == ORC_EVAL_PURE) {
+        leaf_value = (double)evaluate_rollout(m, state, 1000);
+    } else if (end) {
+        m->n_terminal++;
+        if (winner == -1) leaf_value = 0.0;
+        else leaf_value = (winner == state->current_player) ? 1.0 : -1.0;
+    }
+    node_update_recursive(node, -leaf_value);
+}
+
+orc_mcts *orc_mcts_new(double c_puct, int n_playout, int eval_kind, const orc_net *net,
+                       orc_eval_cb cb, uint64_t salt)
+{
+    orc_mcts *m = (orc_mcts *)calloc(1, sizeof(orc_mcts));
+    m->c_puct = c_puct;
+    m->n_playout = n_playout;
+    m->eval_kind = eval_kind;
+    m->net = net;
+    m->cb = cb;
+    m->salt = salt;
+    m->root = node_new(m, NULL, 1.0, 0);
+    return m;
+}
+
+void orc_mcts_free(orc_mcts *m)
+{
+    if (!m) return;
+    node_free(m->root);
+    free(m);
+}
+
+void orc_mcts_set_stream(orc_mcts *m, uint32_t game_id, uint32_t search_id)
+{
+    m->game_id = game_id;
+    m->search_id = search_id;
+}
+
+/* mcts_alphaZero.py:154-181 get_move_probs up to the visit counts (the softmax is applied
+ * by the caller in float64 numpy exactly like :179); mcts_pure.py:214-231 get_move's loop.
+ * Returns the number of root children; acts/visits/q are filled in insertion order. */
+int orc_mcts_search(orc_mcts *m, const orc_board *b, int n_playout, int *acts, int *visits,
+                    double *q, double *prior)
+{
+    if (n_playout < 0) n_playout = m->n_playout;
+    for (int n = 0; n < n_playout; ++n) {
+        orc_board copy = *b;                             /* copy.deepcopy(state) :162 */
+        m->playout_idx = (uint32_t)n;
+        playout(m, &copy);
+    }
+    orc_node *r = m->root;
+    for (int i = 0; i < r->n_children; ++i) {
+        if (acts) acts[i] = r->acts[i];
+        if (visits) visits[i] = r->kids[i]->n_visits;
+        if (q) q[i] = r->kids[i]->Q;
+        if (prior) prior[i] = r->kids[i]->P;
+    }
+    return r->n_children;
+}
+
+int orc_mcts_root_visits(const orc_mcts *m) { return m->root->n_visits; }
+double orc_mcts_root_q(const orc_mcts *m) { return m->root->Q; }
+long long orc_mcts_stat(const orc_mcts *m, int which)
+{
+    switch (which) {
+    case 0: return m->n_evals;
+    case 1: return m->n_terminal;
+    case 2: return m->n_rollout_plies;
+    case 3: return m->n_nodes;
+    }
+    return -1;
+}
+
+/* mcts_alphaZero.py:183-192 update_with_move */
+void orc_mcts_update_with_move(orc_mcts *m, int last_move)
+{
+    orc_node *r = m->root;
+    for (int i = 0; i < r->n_children; ++i)
+        if (r->acts[i] == last_move) {
+            orc_node *c = r->kids[i];
+            r->kids[i] = NULL;
+            c->parent = NULL;
+            node_free(r);
+            m->root = c;
+            return;
+        }
+    node_free(r);
+    m->root = node_new(m, NULL, 1.0, 0);
+}
+
+/* mcts_pure.py:214-231 get_move: n_playout playouts, most-visited child (first max). */
+int orc_pure_get_move(orc_mcts *m, const orc_board *b)
+{
+    int acts[ORC_MAXS], visits[ORC_MAXS];
+    int k = orc_mcts_search(m, b, -1, acts, visits, NULL, NULL);
+    if (k == 0) return -1;
+    int best = 0;
+    for (int i = 1; i < k; ++i) if (visits[i] > visits[best]) best = i;
+    return acts[best];
+}
+
+/* One rollout from a position (for distribution tests against the reference). */
+int orc_rollout_once(const orc_board *b, uint64_t seed, uint32_t game_id, uint32_t search_id,
+                     uint32_t playout_idx)
+{
+    orc_mcts m;
+    memset(&m, 0, sizeof(m));
+    m.salt = seed; m.game_id = game_id; m.search_id = search_id; m.playout_idx = playout_idx;
+    orc_board copy = *b;
+    return evaluate_rollout(&m, &copy, 1000);
+}
