@@ -1,0 +1,249 @@
+// gz_common.cuh — shared device helpers: 256-bit bitboards, Philox, warp reductions.
+//
+// Bitboard layout (all board sizes up to 15x15): cell (h, w) -> bit h*16 + w of a 256-bit
+// word stored as 4 x u64 (row stride 16, so column 15 is an always-empty guard column and
+// rows >= H are empty).  With the guard column, line scans by shift 1 (E), 16 (N),
+// 17 (NE) and 15 (NW) never wrap between rows, so the reference's explicit range guards
+// (game.py:144-158) hold by construction.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define GZ_WARP 32
+
+struct BB {
+    uint64_t w[4];
+};
+
+__host__ __device__ __forceinline__ BB bb_zero()
+{
+    BB b;
+    b.w[0] = b.w[1] = b.w[2] = b.w[3] = 0ull;
+    return b;
+}
+__host__ __device__ __forceinline__ BB bb_or(const BB &a, const BB &b)
+{
+    BB r;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) r.w[i] = a.w[i] | b.w[i];
+    return r;
+}
+__host__ __device__ __forceinline__ BB bb_and(const BB &a, const BB &b)
+{
+    BB r;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) r.w[i] = a.w[i] & b.w[i];
+    return r;
+}
+__host__ __device__ __forceinline__ BB bb_andnot(const BB &a, const BB &b) // a & ~b
+{
+    BB r;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) r.w[i] = a.w[i] & ~b.w[i];
+    return r;
+}
+__host__ __device__ __forceinline__ bool bb_any(const BB &a)
+{
+    return (a.w[0] | a.w[1] | a.w[2] | a.w[3]) != 0ull;
+}
+__host__ __device__ __forceinline__ int bb_bit(int move, int width)
+{
+    return (move / width) * 16 + (move % width);
+}
+__host__ __device__ __forceinline__ bool bb_test(const BB &a, int bit)
+{
+    return (a.w[bit >> 6] >> (bit & 63)) & 1ull;
+}
+__host__ __device__ __forceinline__ void bb_set(BB &a, int bit)
+{
+    a.w[bit >> 6] |= 1ull << (bit & 63);
+}
+__device__ __forceinline__ int bb_popc(const BB &a)
+{
+    return __popcll(a.w[0]) + __popcll(a.w[1]) + __popcll(a.w[2]) + __popcll(a.w[3]);
+}
+// logical right shift of the 256-bit word by s, 0 < s < 64 (branch-free funnel shifts)
+__host__ __device__ __forceinline__ BB bb_shr(const BB &a, int s)
+{
+    BB r;
+    r.w[0] = (a.w[0] >> s) | (a.w[1] << (64 - s));
+    r.w[1] = (a.w[1] >> s) | (a.w[2] << (64 - s));
+    r.w[2] = (a.w[2] >> s) | (a.w[3] << (64 - s));
+    r.w[3] = (a.w[3] >> s);
+    return r;
+}
+// n-in-a-row detector for one colour: t_k = b & (t_{k-1} >> s); non-zero after n-1 steps
+// iff some line of n stones exists in direction s (has_a_winner, game.py:129-160;
+// overlines count, as in the reference).
+__host__ __device__ __forceinline__ bool bb_has_line(const BB &b, int n)
+{
+    const int dirs[4] = {1, 16, 17, 15};
+    bool win = false;
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        BB t = b;
+        for (int k = 1; k < n; ++k) t = bb_and(b, bb_shr(t, dirs[d]));
+        win = win || bb_any(t);
+    }
+    return win;
+}
+// full-board mask for a W x H board
+__host__ __device__ __forceinline__ BB bb_board_mask(int W, int H)
+{
+    BB m = bb_zero();
+    uint64_t row = (1ull << W) - 1ull;
+    for (int h = 0; h < H; ++h) m.w[h >> 2] |= row << ((h & 3) * 16);
+    return m;
+}
+__host__ __device__ __forceinline__ uint32_t bb_row(const BB &a, int h)
+{
+    return (uint32_t)(a.w[h >> 2] >> ((h & 3) * 16)) & 0xFFFFu;
+}
+
+// Board.get_move_target (game.py:35-58): bounding box of all stones grown by 2 with the
+// reference's clipping; empty board -> rows 5..9 x cols 5..9.  Returns box & legal.
+__host__ __device__ __forceinline__ BB bb_move_target(const BB &occ, const BB &legal, int W, int H)
+{
+    int top, bottom, left, right;
+    uint32_t cols = 0;
+    int rmin = 99, rmax = -1;
+    for (int h = 0; h < H; ++h) {
+        uint32_t r = bb_row(occ, h);
+        cols |= r;
+        if (r) {
+            if (h < rmin) rmin = h;
+            rmax = h;
+        }
+    }
+    if (rmax < 0) {
+        top = 9; bottom = 5; left = 5; right = 9;
+    } else {
+        int cmin = 0, cmax = 0;
+        for (int c = 0; c < 16; ++c)
+            if ((cols >> c) & 1u) { cmin = c; break; }
+        for (int c = 15; c >= 0; --c)
+            if ((cols >> c) & 1u) { cmax = c; break; }
+        top = (rmax <= H - 2) ? rmax + 2 : H;
+        bottom = (rmin >= 2) ? rmin - 2 : 0;
+        left = (cmin >= 2) ? cmin - 2 : 0;
+        right = (cmax <= W - 2) ? cmax + 2 : W;
+    }
+    BB box = bb_zero();
+    if (right > 15) right = 15;
+    if (left > 15) return box;
+    uint32_t rowmask = (uint32_t)(((1ull << (right + 1)) - 1ull) & ~((1ull << left) - 1ull)) & 0xFFFFu;
+    for (int h = bottom; h <= top && h < 16; ++h) box.w[h >> 2] |= (uint64_t)rowmask << ((h & 3) * 16);
+    return bb_and(box, legal);
+}
+
+// index (bit position) of the k-th set bit (k from 0) of a 256-bit word
+__device__ __forceinline__ int bb_select(const BB &a, int k)
+{
+    int base = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        int c = __popcll(a.w[i]);
+        if (k < c) {
+            uint64_t x = a.w[i];
+            for (int j = 0; j < k; ++j) x &= x - 1ull;
+            return base + __ffsll((long long)x) - 1;
+        }
+        k -= c;
+        base += 64;
+    }
+    return -1;
+}
+__host__ __device__ __forceinline__ int bb_bit_to_move(int bit, int W) { return (bit >> 4) * W + (bit & 15); }
+
+// Philox4x32-10 (identical to oracle/orc_board.c:orc_philox4x32)
+struct Philox4 {
+    uint32_t x, y, z, w;
+};
+__host__ __device__ __forceinline__ Philox4 philox4x32(uint32_t k0, uint32_t k1, uint32_t c0,
+                                                       uint32_t c1, uint32_t c2, uint32_t c3)
+{
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint64_t p0 = (uint64_t)M0 * c0;
+        uint64_t p1 = (uint64_t)M1 * c2;
+        uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+        uint32_t n1 = (uint32_t)p1;
+        uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+        uint32_t n3 = (uint32_t)p0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    Philox4 o;
+    o.x = c0; o.y = c1; o.z = c2; o.w = c3;
+    return o;
+}
+
+// per-game board record in HBM: 2 colours x 256 bit = 64 B (4 x 128-bit loads) + 16 B meta
+struct __align__(16) GameBoard {
+    uint64_t stones[2][4]; // [player-1][word]
+};
+struct __align__(16) GameMeta {
+    int32_t n_stones;
+    int32_t last_move;   // reference move id, -1 when empty
+    int32_t start_player; // 0/1: players[start_player] moved first
+    int32_t flags;        // bit0: illegal move was attempted
+};
+
+__device__ __forceinline__ BB load_bb(const uint64_t *p)
+{
+    // two 128-bit loads
+    const ulonglong2 *q = reinterpret_cast<const ulonglong2 *>(p);
+    ulonglong2 a = q[0], b = q[1];
+    BB r;
+    r.w[0] = a.x; r.w[1] = a.y; r.w[2] = b.x; r.w[3] = b.y;
+    return r;
+}
+__device__ __forceinline__ void store_bb(uint64_t *p, const BB &v)
+{
+    ulonglong2 *q = reinterpret_cast<ulonglong2 *>(p);
+    q[0] = make_ulonglong2(v.w[0], v.w[1]);
+    q[1] = make_ulonglong2(v.w[2], v.w[3]);
+}
+
+// game_end from two colour boards (game.py:162-169): returns ended, sets winner (1/2/-1).
+// has_a_winner's early-out (< n+2 stones -> no winner, game.py:136-137) is kept.
+__host__ __device__ __forceinline__ bool bb_game_end(const BB &s0, const BB &s1, int n_stones, int W,
+                                                     int H, int n, int *winner, bool *has_win)
+{
+    bool w0 = false, w1 = false;
+    if (n_stones >= n + 2) {
+        w0 = bb_has_line(s0, n);
+        w1 = bb_has_line(s1, n);
+    }
+    *has_win = w0 || w1;
+    if (w0 || w1) {
+        // both colours winning is unreachable by legal play; the reference would report
+        // the owner of the lowest-index winning stone it meets first — pick player 1.
+        *winner = w0 ? 1 : 2;
+        return true;
+    }
+    *winner = -1;
+    return n_stones >= W * H;
+}
+
+// current_state planes (game.py:92-116) in the RETURNED orientation [4][W][H] (row reversed).
+__device__ __forceinline__ void gz_write_planes(const BB &own, const BB &opp, int last_move,
+                                                int n_stones, int W, int H, float *out, int lane)
+{
+    const int S = W * H;
+    const float colour = (n_stones % 2 == 0) ? 1.f : 0.f;
+    const int lr = last_move >= 0 ? last_move / W : -1;
+    const int lc = last_move >= 0 ? last_move % H : -1;
+    for (int idx = lane; idx < S; idx += GZ_WARP) {
+        int rs = idx / H, c = idx % H;
+        int r = W - 1 - rs;
+        int bit = r * 16 + c;
+        out[idx] = bb_test(own, bit) ? 1.f : 0.f;
+        out[S + idx] = bb_test(opp, bit) ? 1.f : 0.f;
+        out[2 * S + idx] = (n_stones > 0 && r == lr && c == lc) ? 1.f : 0.f;
+        out[3 * S + idx] = colour;
+    }
+}
+

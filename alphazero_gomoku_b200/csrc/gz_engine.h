@@ -1,0 +1,153 @@
+// gz_engine.h — internal engine state (host struct owning the device arrays).
+#pragma once
+#include "../../include/gomoku_b200.h"
+#include "gz_common.cuh"
+#include <string>
+#include <vector>
+
+// Tree node block (one per expanded node, SoA inside the block, Sp = S rounded up to 32):
+//   double Q[Sp] | float P[Sp] | uint32 N[Sp] | int32 child[Sp]      = 20 * Sp bytes
+// P[i] < 0 marks "cell i is not a child".  AlphaZero mode: P = prior (float32, as the
+// reference's np.float32 prob).  Pure mode: P = number of children k (prior = 1/k in
+// float64, mcts_pure.py:45).  child[i] = node index of the expanded child or -1.
+struct NodeView {
+    double *Q;
+    float *P;
+    uint32_t *N;
+    int32_t *child;
+};
+__host__ __device__ __forceinline__ size_t gz_node_bytes(int Sp) { return (size_t)20 * Sp; }
+__host__ __device__ __forceinline__ NodeView gz_node_view(uint8_t *pool, size_t node_index, int Sp)
+{
+    uint8_t *b = pool + node_index * gz_node_bytes(Sp);
+    NodeView v;
+    v.Q = reinterpret_cast<double *>(b);
+    v.P = reinterpret_cast<float *>(b + (size_t)8 * Sp);
+    v.N = reinterpret_cast<uint32_t *>(b + (size_t)12 * Sp);
+    v.child = reinterpret_cast<int32_t *>(b + (size_t)16 * Sp);
+    return v;
+}
+
+// device-side counters (one struct in device memory, updated with warp-aggregated atomics)
+struct DevCounters {
+    unsigned long long select_levels, select_children, playouts, leaf_evals, expanded_children,
+        rollout_plies, pool_overflows, plies, games_finished, samples_out, dropped, wins[3];
+};
+
+struct NetWeights {
+    // device copies, torch layout fp32 (for gz_get_weights) and kernel layouts
+    float *raw[16] = {};
+    size_t raw_elems[16] = {};
+    float *w1 = nullptr;   // conv1 [tap][ci(4)][c1]
+    float *w2 = nullptr;   // conv2 [tap][ci][c2]
+    float *w3 = nullptr;   // conv3 [tap][ci][c3]
+    float *wh = nullptr;   // heads 1x1 [c3][8] (cols 0..3 policy, 4..5 value, 6..7 zero)
+    float *wpfc = nullptr; // policy fc transposed [4S][S]
+    float *wvfc = nullptr; // value fc1 transposed [2S][64]
+    float *bias = nullptr; // packed: b1 | b2 | b3 | bh[8] | bp[S] | bv[64] | wv2[64] | bv2[1]
+    int off_b1 = 0, off_b2 = 0, off_b3 = 0, off_bh = 0, off_bp = 0, off_bv = 0, off_wv2 = 0, off_bv2 = 0;
+    bool loaded = false;
+};
+
+struct gz_engine {
+    gz_config cfg;
+    int W, H, S, Sp, n_in_row, G, cap;
+    int c1, c2, c3;
+    cudaStream_t stream;
+    bool own_stream;
+    std::string err;
+    long long launches;
+
+    // boards
+    GameBoard *boards;
+    GameMeta *meta;
+    int8_t *active; // [G] 1 = slot participates in waves
+    // tree
+    uint8_t *pool;
+    int32_t *free_stack; // [G][cap]
+    int32_t *free_top;   // [G]
+    int32_t *root_node;  // [G] -1 = root is an unexpanded leaf
+    uint32_t *root_N;    // [G]
+    double *root_Q;      // [G]
+    uint32_t *path;      // [G][S] edge ids node*Sp + cell
+    int32_t *path_len;   // [G]
+    // leaves of the current wave
+    int8_t *leaf_state;  // [G] 0 eval, 1 terminal, 2 inactive
+    double *leaf_value;  // [G] terminal value (side to move at the leaf)
+    int32_t *leaf_slot;  // [G] row in the compacted leaf batch
+    int32_t *leaf_count; // [1]
+    float *leaf_planes;  // [G][4][S] compacted rows
+    GameBoard *leaf_board; // [G] leaf position (by game)
+    GameMeta *leaf_meta;   // [G]
+    float *net_probs;    // [G][S] compacted rows
+    float *net_values;   // [G]
+    // net
+    NetWeights wts;
+    float *act1, *act2, *act3; // NHWC activations for the fp32 path
+    int64_t act_cap;           // boards the activation buffers hold
+    // staging for host<->device argument copies
+    void *stage;
+    size_t stage_bytes;
+    // self-play
+    float sp_temp;
+    int sp_recycle;
+    bool sp_begun;
+    int32_t *sp_moves;   // [G][S] moves of the game in progress
+    float *sp_pi;        // [G][S][S] pi per ply of the game in progress
+    int64_t *sp_game_id; // [G]
+    int32_t *sel_moves;  // [G] scratch: chosen moves
+    float *sel_probs;    // [G][S] scratch: pi
+    // finished-game output ring (device), drained by the host
+    int64_t out_cap;     // samples
+    float *out_states;   // [out_cap][4][S]
+    float *out_pi;       // [out_cap][S]
+    float *out_z;        // [out_cap]
+    int64_t *out_gid;    // [out_cap]
+    int32_t *out_ply;    // [out_cap]
+    unsigned long long *out_count; // [1]
+    int64_t out_drained;
+    int64_t gout_cap;    // finished games log
+    int32_t *gout_moves; // [gout_cap][S]
+    int32_t *gout_len;   // [gout_cap]
+    int8_t *gout_winner; // [gout_cap]
+    int64_t *gout_gid;   // [gout_cap]
+    unsigned long long *gout_count; // [1]
+    int64_t gout_drained;
+    DevCounters *counters;
+    // rollouts
+    int8_t *roll_results;
+    int64_t roll_cap;
+};
+
+#define GZ_CUDA(e, call)                                                                     \
+    do {                                                                                     \
+        cudaError_t _err = (call);                                                           \
+        if (_err != cudaSuccess) {                                                           \
+            (e)->err = std::string(#call) + ": " + cudaGetErrorString(_err);                 \
+            return GZ_E_CUDA;                                                                \
+        }                                                                                    \
+    } while (0)
+
+// kernels' launchers (each returns a GZ_* code)
+int gzk_rules_eval(gz_engine *e, const int32_t *d_moves, const int64_t *d_offsets, int64_t n_pos,
+                   const int8_t *d_start, int32_t *d_status, int8_t *d_ended, int8_t *d_winner,
+                   int8_t *d_haswin, uint8_t *d_legal, float *d_planes, uint8_t *d_target,
+                   int8_t *d_cur);
+int gzk_boards_reset(gz_engine *e, const int8_t *d_start);
+int gzk_boards_do_move(gz_engine *e, const int32_t *d_moves, int32_t *d_status);
+int gzk_boards_query(gz_engine *e, int8_t *d_ended, int8_t *d_winner, int8_t *d_cur,
+                     int32_t *d_nstones, int32_t *d_last, uint8_t *d_legal, float *d_planes,
+                     int8_t *d_cells);
+int gzk_tree_reset(gz_engine *e);
+int gzk_select(gz_engine *e, bool pure);
+int gzk_expand_backup(gz_engine *e, const float *d_priors, const float *d_values, bool compacted);
+int gzk_pure_expand_rollout_backup(gz_engine *e, uint32_t search_id, uint32_t playout_idx);
+int gzk_root_visits(gz_engine *e, int32_t *d_visits, double *d_q, int32_t *d_rootn);
+int gzk_update_with_move(gz_engine *e, const int32_t *d_moves);
+int gzk_root_select_move(gz_engine *e, float temp, int selfplay, int32_t *d_moves, float *d_probs,
+                         bool best_visits);
+int gzk_selfplay_advance(gz_engine *e);
+int gzk_net_forward(gz_engine *e, const float *d_planes, const int32_t *d_count, int64_t maxB,
+                    float *d_probs, float *d_values);
+int gzk_rollouts(gz_engine *e, int n_rollouts, uint32_t search_id, int8_t *d_results);
+int gz_net_ensure_buffers(gz_engine *e, int64_t B);

@@ -1,0 +1,192 @@
+/*
+ * gomoku_b200 — C ABI of the B200-native Gomoku self-play engine (libgomoku_b200.so).
+ *
+ * The reference (AbcEric/AlphaZero_Gomoku) is pure Python and has no FFI layer; its
+ * boundary is a duck-typed Python protocol.  These entry points are what a
+ * ctypes binding of that protocol needs; each cites the reference interface it replaces
+ * (file:line relative to the reference repo).  The Python classes in
+ * alphazero_gomoku_b200/ (Board, Game, MCTS, MCTSPlayer, PolicyValueNet, TrainPipeline)
+ * are thin ctypes wrappers over exactly these symbols; INTEGRATION.md shows the stub a
+ * maintainer of the reference would add.
+ *
+ * Conventions
+ *   - every function returns 0 on success, <0 on error (GZ_E_*); gz_last_error() gives text.
+ *   - array arguments are caller-owned, valid only for the call, and may be HOST or DEVICE
+ *     pointers (resolved through UVA); engine-owned device memory is never handed out.
+ *   - one host thread per engine, one engine per GPU; not re-entrant (like the reference).
+ *   - all device work runs on the engine's stream (gz_config.stream, or an owned one).
+ *   - moves are reference move ids: move = h * width + w (game.py:70-90); players are 1, 2.
+ */
+#ifndef GOMOKU_B200_H
+#define GOMOKU_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GZ_OK 0
+#define GZ_E_INVALID -1   /* bad argument / bad config (reference raises Exception) */
+#define GZ_E_ILLEGAL -2   /* illegal move (reference: ValueError from list.remove, game.py:122) */
+#define GZ_E_CUDA -3      /* CUDA runtime failure */
+#define GZ_E_NOWEIGHTS -4 /* net used before gz_set_weights */
+#define GZ_E_POOL -5      /* tree pool exhausted (raise nodes_per_game) */
+#define GZ_E_NOGPU -6     /* no CUDA device: there is no CPU fallback */
+
+#define GZ_MAX_SIDE 15
+#define GZ_MAX_CELLS 225
+
+#define GZ_LAYOUT_TORCH 0  /* conv OIHW cross-correlation, fc [out,in] (policy_value_net_pytorch.py:31-41) */
+#define GZ_LAYOUT_THEANO 1 /* conv OIHW flipped, fc [in,out] (policy_value_net.py:118-121 pickles) */
+
+typedef struct gz_engine gz_engine;
+
+/* Mirrors the constructor arguments of Board (game.py:14-23), MCTS / MCTSPlayer
+ * (mcts_alphaZero.py:98-111, :201-203), Net (policy_value_net_pytorch.py:25-41) and the
+ * hard-coded self-play constants (Dirichlet 0.1 / 0.25, mcts_alphaZero.py:236-240). */
+typedef struct {
+    int32_t width, height, n_in_row;
+    int32_t n_games;         /* concurrent game slots G resident on this GPU */
+    int32_t n_playout;       /* playouts per move (used to size the tree pool) */
+    int32_t nodes_per_game;  /* tree pool capacity per game; 0 = 4 * n_playout + 8 */
+    float c_puct;            /* 5 */
+    float dirichlet_alpha;   /* 0.1 */
+    float dirichlet_eps;     /* 0.25 */
+    int32_t trunk[3];        /* conv widths, reference 32/64/128; 0 = reference */
+    uint64_t seed;           /* Philox key */
+    uint64_t game_id_base;   /* global id of slot 0's first game (rank * G in multi-GPU) */
+    int32_t device;          /* CUDA ordinal */
+    int32_t net_impl;        /* 0 = default, 1 = fp32 CUDA-core path, 2 = tcgen05 path */
+    void *stream;            /* cudaStream_t to run on; NULL = engine creates its own */
+} gz_config;
+
+/* ---- lifecycle ---------------------------------------------------------------------- */
+int gz_create(const gz_config *cfg, gz_engine **out);
+void gz_destroy(gz_engine *e);
+const char *gz_last_error(const gz_engine *e); /* e may be NULL (error of gz_create) */
+int gz_sync(gz_engine *e);                      /* cudaStreamSynchronize on the engine stream */
+int gz_device_count(void);
+const char *gz_version(void);
+
+/* ---- weights: PolicyValueNet(model_file=...) / load_state_dict
+ *      (policy_value_net_pytorch.py:76-78); 16 arrays in state_dict order -------------- */
+int gz_set_weights(gz_engine *e, const float *const ptrs[16], int32_t layout);
+int gz_get_weights(gz_engine *e, float *const ptrs[16]); /* torch layout (get_policy_param, :150) */
+
+/* ---- stateless rules over positions given as move lists (Board, game.py:11-172) ------
+ * Position i is moves[offsets[i] .. offsets[i+1]) played from an empty board with
+ * start_player[i] (0/1, NULL = 0).  Outputs (any may be NULL), all per position:
+ *   status  int32  : 0 ok, GZ_E_ILLEGAL if some move was occupied / out of range
+ *   ended   int8, winner int8 : Board.game_end() (game.py:162-169); winner 1/2/-1
+ *   has_win int8   : Board.has_a_winner()[0] (game.py:129-160)
+ *   legal   uint8[S]: 1 where the cell is in Board.availables
+ *   planes  float[4*S]: Board.current_state() in the returned (row-reversed) orientation
+ *                    (game.py:92-116); square boards only
+ *   target  uint8[S]: Board.get_move_target() membership (game.py:35-58)
+ *   cur_player int8 : Board.get_current_player()                                         */
+int gz_rules_eval(gz_engine *e, const int32_t *moves, const int64_t *offsets, int64_t n_pos,
+                  const int8_t *start_player, int32_t *status, int8_t *ended, int8_t *winner,
+                  int8_t *has_win, uint8_t *legal, float *planes, uint8_t *target,
+                  int8_t *cur_player);
+
+/* ---- engine-resident boards, one per game slot (Board.init_board / do_move / ...) ---- */
+int gz_boards_reset(gz_engine *e, const int8_t *start_player /*[G] or NULL*/);
+int gz_boards_set(gz_engine *e, int32_t game, const int32_t *moves, int32_t n_moves,
+                  int32_t start_player);
+int gz_boards_do_move(gz_engine *e, const int32_t *moves /*[G], <0 = leave*/,
+                      int32_t *status /*[G] or NULL*/);
+int gz_boards_status(gz_engine *e, int8_t *ended, int8_t *winner, int8_t *cur_player,
+                     int32_t *n_stones, int32_t *last_move); /* each [G] or NULL */
+int gz_boards_legal_mask(gz_engine *e, uint8_t *out /*[G,S]*/);
+int gz_boards_planes(gz_engine *e, float *out /*[G,4,W,H]*/);
+int gz_boards_cells(gz_engine *e, int8_t *out /*[G,S]: 0 empty, 1, 2*/);
+
+/* ---- leaf evaluator: PolicyValueNet.policy_value (policy_value_net_pytorch.py:80-94) -
+ * planes float[B,4,W,H]; probs float[B,S] = exp(log_softmax); values float[B] = tanh.    */
+int gz_net_forward(gz_engine *e, const float *planes, int64_t B, float *probs, float *values);
+
+/* ---- search: MCTS.get_move_probs / _playout (mcts_alphaZero.py:113-181) ---------------
+ * gz_search runs n_playout waves; each wave = one playout in every active game
+ * (select -> net on the gathered leaves -> expand + backup).                             */
+int gz_search(gz_engine *e, int32_t n_playout);
+/* Same wave split in two so that a caller-supplied evaluator (the reference's
+ * policy_value_fn protocol, mcts_alphaZero.py:98-107) can sit in the middle:
+ * select fills leaf_* (each [G]; leaf_state 0 = needs evaluation, 1 = terminal, 2 = game
+ * inactive) and the leaf boards; expand_backup consumes priors[G,S] (only legal cells
+ * read) and values[G].                                                                   */
+int gz_search_select(gz_engine *e, int8_t *leaf_state, float *leaf_planes /*[G,4,W,H]*/,
+                     int8_t *leaf_cells /*[G,S] or NULL*/, int8_t *leaf_player /*[G] or NULL*/);
+int gz_search_expand_backup(gz_engine *e, const float *priors, const float *values);
+int gz_root_visits(gz_engine *e, int32_t *visits /*[G,S], -1 = not a child*/,
+                   double *q /*[G,S] or NULL*/, int32_t *root_n /*[G] or NULL*/);
+/* MCTS.update_with_move (mcts_alphaZero.py:183-192): moves[G]; a move that is a root
+ * child re-roots (subtree kept), anything else (e.g. -1) resets to a fresh root.
+ * Does NOT touch the boards.                                                             */
+int gz_update_with_move(gz_engine *e, const int32_t *moves);
+/* MCTSPlayer.get_action after the search (mcts_alphaZero.py:212-262): visit counts ->
+ * softmax(log(v + 1e-10) / temp) -> (self-play) 0.75 p + 0.25 Dir(alpha) -> sampled move.
+ * Writes moves[G] and probs[G,S] (noise-free pi); does not apply the move.               */
+int gz_root_select_move(gz_engine *e, float temp, int32_t selfplay, int32_t *moves,
+                        float *probs);
+
+/* ---- self-play: Game.start_self_play / TrainPipeline.collect_selfplay_data
+ *      (game.py:360-416, train.py:137-159) --------------------------------------------- */
+typedef struct {
+    int64_t n_games;     /* finished games reported */
+    int64_t n_samples;   /* plies recorded over those games */
+    int64_t n_playouts;  /* playouts executed by this call */
+    int64_t n_leaf_evals;/* leaves that went through the net (terminal leaves skip it) */
+    int64_t n_plies;     /* moves played by this call (all slots) */
+    int64_t pool_overflows; /* expansions dropped because the tree pool was full (must be 0) */
+    int64_t n_wins[3];   /* finished games by winner: [tie, player1, player2] */
+} gz_selfplay_stats;
+
+/* Start (or restart) self-play in every slot.  recycle = 1: a slot that finishes a game
+ * immediately starts another (throughput mode); 0: it goes idle (collect n = G games). */
+int gz_selfplay_begin(gz_engine *e, float temp, int32_t recycle);
+/* Play n_plies moves in every active slot (each = n_playout waves + move choice + record). */
+int gz_selfplay_step(gz_engine *e, int32_t n_plies);
+/* Number of finished-game samples waiting to be drained / finished games so far. */
+int gz_selfplay_pending(gz_engine *e, int64_t *n_samples, int64_t *n_games_finished,
+                        int64_t *n_active_slots);
+/* Drain finished-game samples (at most max_samples, whole records): states float[n,4,W,H]
+ * (current_state orientation), pis float[n,S], zs float[n] (winners_z, game.py:396-399),
+ * game_ids int64[n], plies int32[n].  Returns the count in *n_out.                        */
+int gz_selfplay_drain(gz_engine *e, int64_t max_samples, float *states, float *pis, float *zs,
+                      int64_t *game_ids, int32_t *plies, int64_t *n_out);
+/* Finished-game move lists for the reference's {'steps':[...],'winner':w} log line
+ * (game.py:411): moves int32[max_moves], offsets int64[max_games+1], winners int8, ids. */
+int gz_selfplay_drain_games(gz_engine *e, int64_t max_games, int64_t max_moves, int32_t *moves,
+                            int64_t *offsets, int8_t *winners, int64_t *game_ids,
+                            int64_t *n_games_out);
+int gz_selfplay_get_stats(gz_engine *e, gz_selfplay_stats *out, int32_t reset);
+
+/* ---- pure MCTS with random rollouts (mcts_pure.py:156-231) ---------------------------- */
+/* n_playout waves of: select -> uniform priors over Board.move_target -> Philox rollout
+ * to the end of the game -> backup; search_id salts the Philox counter.                   */
+int gz_pure_search(gz_engine *e, int32_t n_playout, uint32_t search_id);
+/* MCTS.get_move (mcts_pure.py:230): most visited root child, first maximum. */
+int gz_pure_best_move(gz_engine *e, int32_t *moves /*[G]*/);
+/* Rollout kernel alone (_evaluate_rollout, mcts_pure.py:193-212) from the resident
+ * boards: n_rollouts per game, results int8[G, n_rollouts] in {-1,0,+1} from the side to
+ * move's view; rollout r of game g uses Philox counter (r, ply, game_id(g), search_id). */
+int gz_rollouts(gz_engine *e, int32_t n_rollouts, uint32_t search_id, int8_t *results,
+                int64_t *total_plies);
+
+/* ---- counters for bench / roofline accounting ---------------------------------------- */
+typedef struct {
+    int64_t kernel_launches;  /* kernels of this library launched since the last reset */
+    int64_t select_levels;    /* tree levels descended (sum over playouts) */
+    int64_t select_children;  /* child slots scored (sum of A_l over levels) */
+    int64_t playouts;
+    int64_t leaf_evals;
+    int64_t expanded_children;/* sum of A_leaf over expansions */
+    int64_t rollout_plies;
+} gz_counters;
+int gz_get_counters(gz_engine *e, gz_counters *out, int32_t reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GOMOKU_B200_H */

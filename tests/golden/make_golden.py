@@ -1,0 +1,285 @@
+"""Generate the golden fixtures in tests/golden/ by IMPORTING the unmodified Python reference
+from /root/reference (build container only).  Run:  python tests/golden/make_golden.py
+
+Fixtures (all small):
+  weights_6_6_4.npz / weights_8_8_5.npz  shipped Theano pickles converted to the torch
+        state_dict layout — data fixtures, not reference source.
+  rules.npz   seeded random positions for 6 board shapes with the reference Board's
+        availables / current_state / has_a_winner / game_end / move_target / current player.
+  corpus.npz  the first recorded 15x15 games of logs/steps.log + human_gomoku.txt and 9x9
+        games of run.log with the reference's per-ply game_end results.
+  net.npz     planes and the reference PyTorch fp32 Net outputs (exp(log_softmax), value).
+  mcts.npz    reference MCTS.get_move_probs visit counts (400 playouts, c_puct 5, shipped
+        weights, value wrapped as float — SURVEY 8c-3) on seeded positions, with tree reuse
+        over two consecutive searches.
+  rollout.npz reference _evaluate_rollout outcome counts from fixed positions (distribution
+        check for the Philox rollout kernel) and pure-MCTS get_move visit statistics.
+"""
+import ast
+import os
+import random
+import re
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+from oracle import ref_harness as rh  # noqa: E402
+
+assert rh.available(), "needs /root/reference"
+G = rh.game()
+AZ = rh.mcts_alphazero()
+PURE = rh.mcts_pure()
+
+
+def save(name, **kw):
+    np.savez_compressed(os.path.join(HERE, name), **kw)
+    print("wrote", name, {k: getattr(v, "shape", None) for k, v in kw.items()})
+
+
+def make_weights():
+    out = {}
+    for name, tag in (("best_policy_6_6_4.model", "6_6_4"), ("best_policy_8_8_5.model", "8_8_5")):
+        arrs = rh.load_theano_weights(name)
+        save("weights_%s.npz" % tag, **{"p%02d" % i: a for i, a in enumerate(arrs)})
+        out[tag] = arrs
+    return out
+
+
+def ref_board_outputs(b):
+    end, winner = b.game_end()
+    hw, _ = b.has_a_winner()
+    S = b.width * b.height
+    legal = np.zeros(S, np.uint8)
+    legal[b.availables] = 1
+    b.get_move_target()
+    tg = np.zeros(S, np.uint8)
+    tg[b.move_target] = 1
+    planes = None
+    if b.width == b.height:
+        planes = np.ascontiguousarray(b.current_state()).astype(np.float32)
+    return int(end), int(winner), int(hw), legal, tg, planes, int(b.current_player)
+
+
+def make_rules():
+    rng = np.random.RandomState(0)
+    shapes = [(6, 6, 4), (8, 8, 5), (9, 9, 5), (15, 15, 5), (3, 3, 3), (7, 7, 3), (8, 6, 4), (11, 11, 5)]
+    kw = {}
+    for (w, h, n) in shapes:
+        S = w * h
+        moves_all, offs, starts = [], [0], []
+        ended, winner, haswin, legal, target, planes, cur = [], [], [], [], [], [], []
+        for t in range(160):
+            sp = t % 2
+            b = G.Board(width=w, height=h, n_in_row=n)
+            b.init_board(sp)
+            k = int(rng.randint(0, S + 1))
+            mv = []
+            for _ in range(k):
+                av = b.availables
+                m = int(av[rng.randint(len(av))])
+                # bias towards extending lines so that wins occur
+                if mv and rng.rand() < 0.5:
+                    cand = [x for x in (mv[-2] + d if len(mv) > 1 else mv[-1] + d
+                                        for d in (1, -1, w, -w, w + 1, -w - 1, w - 1, -w + 1)) if x in av]
+                    if cand:
+                        m = int(cand[rng.randint(len(cand))])
+                b.do_move(m)
+                mv.append(m)
+                if b.game_end()[0]:
+                    break
+            e, wi, hw, lg, tg, pl, cp = ref_board_outputs(b)
+            moves_all += mv
+            offs.append(len(moves_all))
+            starts.append(sp)
+            ended.append(e); winner.append(wi); haswin.append(hw); legal.append(lg); target.append(tg)
+            cur.append(cp)
+            if pl is not None:
+                planes.append(pl)
+        tag = "%dx%dx%d" % (w, h, n)
+        kw[tag + "_moves"] = np.array(moves_all, np.int32)
+        kw[tag + "_offsets"] = np.array(offs, np.int64)
+        kw[tag + "_start"] = np.array(starts, np.int8)
+        kw[tag + "_ended"] = np.array(ended, np.int8)
+        kw[tag + "_winner"] = np.array(winner, np.int8)
+        kw[tag + "_haswin"] = np.array(haswin, np.int8)
+        kw[tag + "_legal"] = np.array(legal, np.uint8)
+        kw[tag + "_target"] = np.array(target, np.uint8)
+        kw[tag + "_cur"] = np.array(cur, np.int8)
+        if planes:
+            kw[tag + "_planes"] = np.array(planes, np.float32)
+    save("rules.npz", **kw)
+
+
+def replay_game_end(w, n, moves):
+    """per-ply reference (ended, winner) for one recorded game; stops at first illegal move."""
+    b = G.Board(width=w, height=w, n_in_row=n)
+    b.init_board(0)
+    res = []
+    for m in moves:
+        if m not in b.availables:
+            break
+        b.do_move(m)
+        e, wi = b.game_end()
+        res.append((int(e), int(wi)))
+    return res
+
+
+def make_corpus():
+    games15 = []
+    with open(os.path.join(rh.REF_DIR, "logs", "steps.log")) as f:
+        for line in f:
+            line = line.strip()
+            if not line.startswith("{"):
+                continue
+            d = ast.literal_eval(line)
+            games15.append([int(x) for x in d["steps"]])
+            if len(games15) >= 120:
+                break
+    with open(os.path.join(rh.REF_DIR, "human_gomoku.txt")) as f:
+        cnt = 0
+        for line in f:
+            line = line.strip()
+            if not line.startswith("["):
+                continue
+            d = ast.literal_eval(line)
+            games15.append([int(x) for x in d[1]])
+            cnt += 1
+            if cnt >= 80:
+                break
+    games9 = []
+    with open(os.path.join(rh.REF_DIR, "run.log"), errors="ignore") as f:
+        for line in f:
+            m = re.search(r"\d-\[([0-9, ]+)\]", line)
+            if m:
+                mv = [int(x) for x in m.group(1).split(",")]
+                if mv and max(mv) < 81:
+                    games9.append(mv)
+    kw = {}
+    for tag, w, games in (("15", 15, games15), ("9", 9, games9[:120])):
+        flat, offs, ended, winner = [], [0], [], []
+        for mv in games:
+            res = replay_game_end(w, 5, mv)
+            mv = mv[:len(res)]
+            flat += mv
+            offs.append(len(flat))
+            ended += [r[0] for r in res]
+            winner += [r[1] for r in res]
+        kw["g%s_moves" % tag] = np.array(flat, np.int32)
+        kw["g%s_offsets" % tag] = np.array(offs, np.int64)
+        kw["g%s_ended" % tag] = np.array(ended, np.int8)     # per ply (prefix) results
+        kw["g%s_winner" % tag] = np.array(winner, np.int8)
+    save("corpus.npz", **kw)
+
+
+def make_net(weights):
+    import torch
+    kw = {}
+    rng = np.random.RandomState(1)
+    for tag, (w, n) in (("6_6_4", (6, 4)), ("8_8_5", (8, 5))):
+        net = rh.make_ref_net(w, w, weights[tag])
+        pls = []
+        while len(pls) < 48:
+            b, _ = rh.random_position(G.Board, w, w, n, rng)
+            if b.game_end()[0]:
+                continue
+            pls.append(np.ascontiguousarray(b.current_state()).astype(np.float32))
+        x = np.stack(pls)
+        probs, vals = net.policy_value(x)
+        kw[tag + "_planes"] = x
+        kw[tag + "_probs"] = probs.astype(np.float32)
+        kw[tag + "_values"] = vals.astype(np.float32).reshape(-1)
+    save("net.npz", **kw)
+
+
+def make_mcts(weights):
+    kw = {}
+    rng = np.random.RandomState(2)
+    for tag, (w, n) in (("6_6_4", (6, 4)), ("8_8_5", (8, 5))):
+        net = rh.make_ref_net(w, w, weights[tag])
+        fn = rh.float_value_fn(net)
+        moves_all, offs, vis1, vis2, mv2 = [], [0], [], [], []
+        cnt = 0
+        while cnt < 6:
+            b, moves = rh.random_position(G.Board, w, w, n, rng, max_plies=12)
+            if b.game_end()[0] or len(b.availables) < 3:
+                continue
+            m = AZ.MCTS(fn, c_puct=5, n_playout=400)
+            acts, _ = m.get_move_probs(b, temp=1.0)
+            v = np.full(w * w, -1, np.int32)
+            for a in acts:
+                v[a] = m._root._children[a]._n_visits
+            # tree reuse: play the most visited move, search again (mcts_alphaZero.py:183-192)
+            best = int(np.argmax(v))
+            m.update_with_move(best)
+            b.do_move(best)
+            v2 = np.full(w * w, -1, np.int32)
+            if not b.game_end()[0]:
+                acts2, _ = m.get_move_probs(b, temp=1.0)
+                for a in acts2:
+                    v2[a] = m._root._children[a]._n_visits
+            moves_all += moves
+            offs.append(len(moves_all))
+            vis1.append(v); vis2.append(v2); mv2.append(best)
+            cnt += 1
+            print("mcts", tag, cnt)
+        kw[tag + "_moves"] = np.array(moves_all, np.int32)
+        kw[tag + "_offsets"] = np.array(offs, np.int64)
+        kw[tag + "_visits1"] = np.array(vis1, np.int32)
+        kw[tag + "_visits2"] = np.array(vis2, np.int32)
+        kw[tag + "_move"] = np.array(mv2, np.int32)
+    save("mcts.npz", **kw)
+
+
+def make_rollout():
+    np.random.seed(0)
+    random.seed(0)
+    kw = {}
+    positions = {
+        "6x6x4_a": (6, 4, [14, 15, 20, 21]),
+        "6x6x4_b": (6, 4, [14, 8, 15, 9, 16]),
+        "8x8x5_a": (8, 5, [27, 28, 35, 36, 19]),
+        "8x8x5_b": (8, 5, []),
+    }
+    for tag, (w, n, moves) in positions.items():
+        b = G.Board(width=w, height=w, n_in_row=n)
+        b.init_board(0)
+        for m in moves:
+            b.do_move(m)
+        mc = PURE.MCTS(PURE.policy_value_fn, 5, 10)
+        counts = np.zeros(3, np.int64)  # [-1, 0, +1]
+        import copy
+        with rh.quiet():
+            for _ in range(3000):
+                r = mc._evaluate_rollout(copy.deepcopy(b))
+                counts[r + 1] += 1
+        kw[tag + "_moves"] = np.array(moves, np.int32)
+        kw[tag + "_counts"] = counts
+        print("rollout", tag, counts)
+    # pure MCTS move choice statistics from one position (first move distribution, 30 runs)
+    w, n, moves = 6, 4, [14, 15, 20]
+    first = np.zeros(36, np.int64)
+    for r in range(30):
+        b = G.Board(width=w, height=w, n_in_row=n)
+        b.init_board(0)
+        for m in moves:
+            b.do_move(m)
+        p = PURE.MCTSPlayer(c_puct=5, n_playout=300)
+        with rh.quiet():
+            mv = p.get_action(b)
+        first[mv] += 1
+    kw["pure_moves"] = np.array(moves, np.int32)
+    kw["pure_first"] = first
+    save("rollout.npz", **kw)
+
+
+if __name__ == "__main__":
+    which = sys.argv[1:] or ["weights", "rules", "corpus", "net", "mcts", "rollout"]
+    weights = make_weights() if "weights" in which or "net" in which or "mcts" in which else None
+    if "rules" in which: make_rules()
+    if "corpus" in which: make_corpus()
+    if "net" in which: make_net(weights)
+    if "mcts" in which: make_mcts(weights)
+    if "rollout" in which: make_rollout()

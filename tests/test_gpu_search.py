@@ -1,0 +1,336 @@
+"""GPU parity tests for the tree kernels, the search loop, rollouts and self-play.
+
+Tiers (BASELINE.json north_star): tree statistics are BIT-EXACT against the oracle when both
+sides see the same evaluator outputs (synthetic integer-hash evaluator, injected through
+gz_search_select / gz_search_expand_backup); with the real net the visit distributions must
+be within total-variation 0.02 of the reference's (golden mcts.npz), exact off near-ties."""
+import os
+
+import numpy as np
+import pytest
+
+from helpers import GOLDEN, hash_eval_batch, load_golden_weights
+
+pytestmark = pytest.mark.gpu
+
+
+def _engine(w, h, n, **kw):
+    from alphazero_gomoku_b200 import Engine
+    return Engine(width=w, height=h, n_in_row=n, **kw)
+
+
+def _random_positions(rng, w, n, G, max_plies):
+    from oracle import orc
+    boards, lists = [], []
+    while len(boards) < G:
+        b = orc.Board(w, w, n)
+        b.init_board(0)
+        mv = []
+        for _ in range(int(rng.randint(0, max_plies + 1))):
+            av = b.availables
+            m = av[rng.randint(len(av))]
+            b.do_move(m)
+            mv.append(m)
+            if b.game_end()[0]:
+                break
+        if b.game_end()[0]:
+            continue
+        boards.append(b)
+        lists.append(mv)
+    return boards, lists
+
+
+def _device_hash_search(e, n_playout, salt):
+    for _ in range(n_playout):
+        st, planes, cells, player = e.search_select()
+        with np.errstate(all="ignore"):
+            priors, values = hash_eval_batch(cells, player, salt)
+        priors = np.nan_to_num(priors)
+        e.search_expand_backup(priors, values)
+
+
+@pytest.mark.parametrize("w,n,G,n_playout,c_puct", [(6, 4, 48, 200, 5.0), (8, 5, 96, 400, 5.0),
+                                                    (9, 5, 24, 150, 3.0), (15, 5, 8, 120, 5.0)])
+def test_tree_bit_exact_with_hash_evaluator(w, n, G, n_playout, c_puct):
+    """select / expand / backup / re-root vs the oracle's pointer tree: identical visit
+    counts AND identical float64 Q for every root child, over two searches with tree reuse."""
+    from oracle import orc
+    rng = np.random.RandomState(w)
+    salt = 1234 + w
+    boards, lists = _random_positions(rng, w, n, G, max_plies=w * w // 2)
+    e = _engine(w, w, n, n_games=G, n_playout=n_playout, c_puct=c_puct)
+    for g, mv in enumerate(lists):
+        e.boards_set(g, mv)
+    _device_hash_search(e, n_playout, salt)
+    vis, q, rn = e.root_visits(want_q=True)
+    trees = []
+    for g, b in enumerate(boards):
+        m = orc.MCTS(c_puct, n_playout, orc.EVAL_HASH, salt=salt)
+        acts, ovis, oq, _ = m.search(b)
+        trees.append(m)
+        assert np.nonzero(vis[g] >= 0)[0].tolist() == acts.tolist()
+        assert np.array_equal(vis[g][acts], ovis), (g, vis[g][acts], ovis)
+        assert np.array_equal(q[g][acts], oq)  # bit-exact float64
+        assert int(rn[g]) == m.root_visits()
+    # tree reuse: play the most visited move everywhere, search again
+    best = np.array([int(np.argmax(vis[g])) for g in range(G)], np.int32)
+    e.update_with_move(best)
+    e.boards_do_move(best)
+    ended = e.boards_status()["ended"]
+    _device_hash_search(e, n_playout // 2, salt)
+    vis2, q2, rn2 = e.root_visits(want_q=True)
+    for g, b in enumerate(boards):
+        trees[g].update_with_move(int(best[g]))
+        b.do_move(int(best[g]))
+        assert bool(ended[g]) == b.game_end()[0]
+        acts, ovis, oq, _ = trees[g].search(b, n_playout // 2)
+        if b.game_end()[0]:
+            # a finished root never gets children (terminal leaves are not expanded)
+            assert (vis2[g] < 0).all() and len(acts) == 0
+        else:
+            assert np.array_equal(vis2[g][acts], ovis)
+            assert np.array_equal(q2[g][acts], oq)
+        assert int(rn2[g]) == trees[g].root_visits()
+    # reset (update_with_move(-1)) gives fresh roots
+    e.update_with_move(np.full(G, -1, np.int32))
+    vis3, rn3 = e.root_visits()
+    assert (vis3 < 0).all() and (rn3 == 0).all()
+    assert e.selfplay_stats()["pool_overflows"] == 0
+    e.close()
+
+
+@pytest.mark.parametrize("tag,w,n", [("6_6_4", 6, 4), ("8_8_5", 8, 5)])
+def test_search_with_net_vs_reference_golden(tag, w, n):
+    """Full device search (net on device) vs the reference's visit counts (400 playouts,
+    shipped weights): TV <= 0.02, and the second search reuses the subtree."""
+    z = np.load(os.path.join(GOLDEN, "mcts.npz"))
+    moves, offs = z[tag + "_moves"], z[tag + "_offsets"]
+    G = len(offs) - 1
+    e = _engine(w, w, n, n_games=G, n_playout=400)
+    e.set_weights(load_golden_weights("weights_" + tag))
+    for g in range(G):
+        e.boards_set(g, moves[offs[g]:offs[g + 1]])
+    e.search(400)
+    vis, rn = e.root_visits()
+    exact = 0
+    for g in range(G):
+        ref = z[tag + "_visits1"][g]
+        assert np.array_equal(vis[g] >= 0, ref >= 0)
+        a, b = np.maximum(vis[g], 0), np.maximum(ref, 0)
+        assert a.sum() == b.sum() == 399
+        tv = 0.5 * np.abs(a / a.sum() - b / b.sum()).sum()
+        exact += int(np.array_equal(a, b))
+        assert tv <= 0.02, (g, tv)
+    mv = z[tag + "_move"].astype(np.int32)
+    e.update_with_move(mv)
+    e.boards_do_move(mv)
+    e.search(400)
+    vis2, _ = e.root_visits()
+    for g in range(G):
+        ref = z[tag + "_visits2"][g]
+        if (ref < 0).all():
+            continue
+        a, b = np.maximum(vis2[g], 0), np.maximum(ref, 0)
+        assert a.sum() == b.sum()
+        tv = 0.5 * np.abs(a / a.sum() - b / b.sum()).sum()
+        exact += int(np.array_equal(a, b))
+        assert tv <= 0.02, (g, tv)
+    print("search vs reference", tag, "exact visit vectors:", exact, "of", 2 * G)
+    e.close()
+
+
+def test_search_with_net_vs_oracle_many_games():
+    """Same as above against the C oracle (its own fp32 net) on more positions, 8x8."""
+    from oracle import orc
+    w, n, G, P = 8, 5, 32, 200
+    arrs = load_golden_weights("weights_8_8_5")
+    rng = np.random.RandomState(11)
+    boards, lists = _random_positions(rng, w, n, G, max_plies=20)
+    e = _engine(w, w, n, n_games=G, n_playout=P)
+    e.set_weights(arrs)
+    for g, mv in enumerate(lists):
+        e.boards_set(g, mv)
+    e.search(P)
+    vis, _ = e.root_visits()
+    onet = orc.Net(w, w, arrs)
+    exact, worst = 0, 0.0
+    for g, b in enumerate(boards):
+        m = orc.MCTS(5, P, orc.EVAL_NET, net=onet)
+        acts, ovis, _, _ = m.search(b)
+        a = np.maximum(vis[g], 0)[acts]
+        tv = 0.5 * np.abs(a / a.sum() - ovis / ovis.sum()).sum()
+        worst = max(worst, tv)
+        exact += int(np.array_equal(a, ovis))
+    print("search vs oracle: exact", exact, "of", G, "worst TV", worst)
+    assert worst <= 0.02
+    assert exact >= G // 2
+    e.close()
+
+
+def test_rollouts_bit_exact_vs_oracle():
+    from oracle import orc
+    for (w, n) in [(6, 4), (8, 5), (15, 5)]:
+        rng = np.random.RandomState(w)
+        G, R, seed, sid = 24, 16, 0x1234567890ABCDEF, 7
+        boards, lists = _random_positions(rng, w, n, G, max_plies=w * w // 3)
+        e = _engine(w, w, n, n_games=G, seed=seed, game_id_base=100)
+        for g, mv in enumerate(lists):
+            e.boards_set(g, mv)
+        res, plies = e.rollouts(R, search_id=sid)
+        for g, b in enumerate(boards):
+            for r in range(R):
+                assert int(res[g, r]) == orc.rollout_once(b, seed, 100 + g, sid, r)
+        assert plies > 0
+        e.close()
+
+
+def test_rollout_distribution_vs_reference_golden():
+    """Outcome frequencies of the Philox rollouts vs 3000 reference rollouts per position."""
+    z = np.load(os.path.join(GOLDEN, "rollout.npz"))
+    for tag, w, n in [("6x6x4_a", 6, 4), ("6x6x4_b", 6, 4), ("8x8x5_a", 8, 5), ("8x8x5_b", 8, 5)]:
+        e = _engine(w, w, n, n_games=1, seed=99)
+        e.boards_set(0, z[tag + "_moves"])
+        R = 20000
+        res, _ = e.rollouts(R, search_id=1)
+        got = np.array([(res == -1).sum(), (res == 0).sum(), (res == 1).sum()], np.float64) / R
+        ref = z[tag + "_counts"].astype(np.float64)
+        nref = ref.sum()
+        ref /= nref
+        sd = np.sqrt(ref * (1 - ref) / nref + got * (1 - got) / R) + 1e-9
+        print("rollout dist", tag, got, ref)
+        assert (np.abs(got - ref) < 5 * sd + 0.005).all(), (tag, got, ref)
+        e.close()
+
+
+@pytest.mark.parametrize("w,n,P", [(6, 4, 300), (8, 5, 200)])
+def test_pure_mcts_bit_exact_vs_oracle(w, n, P):
+    from oracle import orc
+    rng = np.random.RandomState(3)
+    G, seed, sid = 16, 42, 5
+    boards, lists = _random_positions(rng, w, n, G, max_plies=10)
+    e = _engine(w, w, n, n_games=G, n_playout=P, seed=seed, game_id_base=0)
+    for g, mv in enumerate(lists):
+        e.boards_set(g, mv)
+    e.pure_search(P, search_id=sid)
+    vis, rn = e.root_visits()
+    best = e.pure_best_move()
+    for g, b in enumerate(boards):
+        m = orc.MCTS(5, P, orc.EVAL_PURE, salt=seed)
+        m.set_stream(g, sid)
+        acts, ovis, _, _ = m.search(b)
+        assert np.nonzero(vis[g] >= 0)[0].tolist() == acts.tolist()
+        assert np.array_equal(vis[g][acts], ovis)
+        assert int(best[g]) == int(acts[np.argmax(ovis)])
+    e.close()
+
+
+def test_root_select_move_distribution():
+    """pi = softmax(log(v)/temp) exact vs numpy float64; sampled moves follow
+    0.75*pi + 0.25*Dir(0.1) (self-play) resp. pi (match play)."""
+    w, n, G = 6, 4, 4096
+    e = _engine(w, w, n, n_games=G, n_playout=60, seed=7)
+    e.set_weights(load_golden_weights("weights_6_6_4"))
+    e.boards_set(0, [14, 15])
+    for g in range(1, G):
+        e.boards_set(g, [14, 15])
+    e.search(60)
+    vis, _ = e.root_visits()
+    assert (vis == vis[0]).all()  # identical games, deterministic search
+    v = vis[0]
+    acts = np.nonzero(v >= 0)[0]
+    for temp in (1.0, 0.5, 1e-3):
+        moves, probs = e.root_select_move(temp=temp, selfplay=False)
+        x = 1.0 / temp * np.log(v[acts] + 1e-10)
+        p = np.exp(x - x.max())
+        p /= p.sum()
+        assert np.abs(probs[0][acts] - p).max() < 1e-6
+        assert np.abs(probs[0].sum() - 1) < 1e-5
+        cnt = np.bincount(moves, minlength=w * w)[acts]
+        sd = np.sqrt(G * p * (1 - p)) + 1.0
+        assert (np.abs(cnt - G * p) < 5 * sd).all(), (temp, cnt, G * p)
+    moves, probs = e.root_select_move(temp=1.0, selfplay=True)
+    x = np.log(v[acts] + 1e-10)
+    p = np.exp(x - x.max()); p /= p.sum()
+    mix = 0.75 * p + 0.25 / len(acts)
+    cnt = np.bincount(moves, minlength=w * w)[acts]
+    sd = np.sqrt(G * mix * (1 - mix)) + 1.0
+    assert (np.abs(cnt - G * mix) < 5 * sd).all(), (cnt, G * mix)
+    assert np.abs(probs[0][acts] - p).max() < 1e-6  # returned pi is noise-free (A-10)
+    e.close()
+
+
+def test_selfplay_records_match_oracle_replay():
+    """Run device self-play to completion (one game per slot) and re-derive every record
+    from the move lists with the oracle: states, z, pi normalisation, legality, winner."""
+    from oracle import orc
+    w, n, G, P = 6, 4, 48, 48
+    e = _engine(w, w, n, n_games=G, n_playout=P, seed=3)
+    e.set_weights(load_golden_weights("weights_6_6_4"))
+    e.selfplay_begin(temp=1.0, recycle=False)
+    for _ in range(w * w):
+        e.selfplay_step(1)
+        if e.selfplay_pending()[2] == 0:
+            break
+    ns, ng, nact = e.selfplay_pending()
+    assert nact == 0 and ng == G
+    games = e.selfplay_drain_games()
+    data = e.selfplay_drain()
+    assert len(games) == G and len(data["zs"]) == ns == sum(len(m) for _, _, m in games)
+    stats = e.selfplay_stats()
+    assert stats["pool_overflows"] == 0 and stats["n_games"] == G and stats["n_samples"] == ns
+    by_gid = {gid: (win, mv) for gid, win, mv in games}
+    assert sorted(by_gid) == list(range(G))
+    order = np.lexsort((data["plies"], data["game_ids"]))
+    k = 0
+    for gid in sorted(by_gid):
+        win, mv = by_gid[gid]
+        b = orc.Board(w, w, n)
+        b.init_board(0)
+        for t, m in enumerate(mv):
+            i = order[k]; k += 1
+            assert data["game_ids"][i] == gid and data["plies"][i] == t
+            assert np.array_equal(data["states"][i], b.current_state().astype(np.float32))
+            pi = data["pis"][i]
+            assert abs(pi.sum() - 1) < 1e-4
+            assert (pi[[c for c in range(w * w) if c not in b.availables]] == 0).all()
+            z = 0.0 if win == -1 else (1.0 if b.current_player == win else -1.0)
+            assert data["zs"][i] == z
+            assert not b.game_end()[0]
+            b.do_move(m)  # raises if the engine played an illegal move
+        assert b.game_end() == (True, win)
+    e.close()
+
+
+def test_selfplay_pi_matches_oracle_search_with_tree_reuse():
+    """Follow the device's sampled moves with the oracle MCTS (tree reuse) and compare the
+    recorded pi (temp = 1 -> visit fractions) ply by ply: TV <= 0.02."""
+    from oracle import orc
+    w, n, G, P = 6, 4, 6, 120
+    arrs = load_golden_weights("weights_6_6_4")
+    e = _engine(w, w, n, n_games=G, n_playout=P, seed=17)
+    e.set_weights(arrs)
+    e.selfplay_begin(temp=1.0, recycle=False)
+    while e.selfplay_pending()[2] > 0:
+        e.selfplay_step(1)
+    games = e.selfplay_drain_games()
+    data = e.selfplay_drain()
+    onet = orc.Net(w, w, arrs)
+    worst, exact, total = 0.0, 0, 0
+    for gid, win, mv in games:
+        b = orc.Board(w, w, n)
+        b.init_board(0)
+        m = orc.MCTS(5, P, orc.EVAL_NET, net=onet)
+        for t, move in enumerate(mv):
+            acts, ovis, _, _ = m.search(b)
+            i = np.nonzero((data["game_ids"] == gid) & (data["plies"] == t))[0][0]
+            pi = data["pis"][i][acts].astype(np.float64)
+            ref = ovis / ovis.sum()
+            tv = 0.5 * np.abs(pi - ref).sum()
+            worst = max(worst, tv)
+            exact += int(tv < 1e-6)
+            total += 1
+            m.update_with_move(move)
+            b.do_move(move)
+    print("selfplay pi vs oracle: exact", exact, "of", total, "worst TV", worst)
+    assert worst <= 0.02
+    e.close()
