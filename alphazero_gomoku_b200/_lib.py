@@ -90,11 +90,16 @@ _PROTOS = {
     "gz_selfplay_drain": (C.c_int, [_P, C.c_int64, _P, _P, _P, _P, _P, C.POINTER(C.c_int64)]),
     "gz_selfplay_drain_games": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P, _P, _P, C.POINTER(C.c_int64)]),
     "gz_selfplay_get_stats": (C.c_int, [_P, C.POINTER(GzSelfplayStats), C.c_int32]),
+    "gz_selfplay_last": (C.c_int, [_P, _P, _P]),
     "gz_pure_search": (C.c_int, [_P, C.c_int32, C.c_uint32]),
     "gz_pure_best_move": (C.c_int, [_P, _P]),
     "gz_rollouts": (C.c_int, [_P, C.c_int32, C.c_uint32, _P, C.POINTER(C.c_int64)]),
     "gz_get_counters": (C.c_int, [_P, C.POINTER(GzCounters), C.c_int32]),
+    "gz_profile_enable": (C.c_int, [_P, C.c_int32]),
+    "gz_profile_read": (C.c_int, [_P, _P, _P, C.c_int32]),
+    "gz_profile_class_name": (C.c_char_p, [C.c_int32]),
 }
+PROF_CLASSES = 12
 
 _lib = None
 

@@ -214,6 +214,7 @@ extern "C" void gz_destroy(gz_engine *e)
                     e->wts.bias};
     for (void *p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 16; ++i) if (e->wts.raw[i]) cudaFree(e->wts.raw[i]);
+    for (int c = 0; c < GZ_PROF_CLASSES; ++c) for (cudaEvent_t ev : e->prof_ev[c]) cudaEventDestroy(ev);
     if (e->own_stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -811,6 +812,17 @@ extern "C" int gz_selfplay_get_stats(gz_engine *e, gz_selfplay_stats *out, int32
     return GZ_OK;
 }
 
+extern "C" int gz_selfplay_last(gz_engine *e, int32_t *moves, float *probs)
+{
+    if (!e || !e->sp_begun) return GZ_E_INVALID;
+    GZ_CUDA(e, cudaSetDevice(e->cfg.device));
+    const size_t G = e->G, S = e->S;
+    if (moves) GZ_CUDA(e, cudaMemcpyAsync(moves, e->sel_moves, G * 4, cudaMemcpyDefault, e->stream));
+    if (probs) GZ_CUDA(e, cudaMemcpyAsync(probs, e->sel_probs, G * S * 4, cudaMemcpyDefault, e->stream));
+    GZ_CUDA(e, cudaStreamSynchronize(e->stream));
+    return GZ_OK;
+}
+
 // ---- pure MCTS ----------------------------------------------------------------------------------
 extern "C" int gz_pure_search(gz_engine *e, int32_t n_playout, uint32_t search_id)
 {
@@ -872,6 +884,44 @@ extern "C" int gz_get_counters(gz_engine *e, gz_counters *out, int32_t reset)
     if (reset) {
         GZ_CUDA(e, cudaMemset(e->counters, 0, sizeof(DevCounters)));
         e->launches = 0;
+    }
+    return GZ_OK;
+}
+
+// ---- per-kernel-class timing ----------------------------------------------------------------------
+static const char *g_prof_names[GZ_PROF_CLASSES] = {"select", "conv1", "conv2", "conv3", "heads", "expand_backup",
+                                                    "root_select_move", "selfplay_advance", "pure_expand",
+                                                    "rollout", "backup", "other"};
+
+extern "C" const char *gz_profile_class_name(int32_t c)
+{
+    return (c >= 0 && c < GZ_PROF_CLASSES) ? g_prof_names[c] : "";
+}
+
+extern "C" int gz_profile_enable(gz_engine *e, int32_t on)
+{
+    if (!e) return GZ_E_INVALID;
+    e->prof_on = on != 0;
+    return GZ_OK;
+}
+
+extern "C" int gz_profile_read(gz_engine *e, double *ms, int64_t *launches, int32_t reset)
+{
+    if (!e) return GZ_E_INVALID;
+    GZ_CUDA(e, cudaSetDevice(e->cfg.device));
+    GZ_CUDA(e, cudaStreamSynchronize(e->stream));
+    for (int c = 0; c < GZ_PROF_CLASSES; ++c) {
+        for (size_t i = 0; i + 1 < e->prof_used[c]; i += 2) {
+            float t = 0.f;
+            if (cudaEventElapsedTime(&t, e->prof_ev[c][i], e->prof_ev[c][i + 1]) == cudaSuccess) {
+                e->prof_ms[c] += t;
+                e->prof_n[c] += 1;
+            }
+        }
+        e->prof_used[c] = 0;
+        if (ms) ms[c] = e->prof_ms[c];
+        if (launches) launches[c] = e->prof_n[c];
+        if (reset) { e->prof_ms[c] = 0.0; e->prof_n[c] = 0; }
     }
     return GZ_OK;
 }

@@ -117,6 +117,43 @@ struct gz_engine {
     // rollouts
     int8_t *roll_results;
     int64_t roll_cap;
+    // per-kernel-class timing
+    bool prof_on;
+    std::vector<cudaEvent_t> prof_ev[GZ_PROF_CLASSES]; // start/stop pairs
+    size_t prof_used[GZ_PROF_CLASSES];
+    double prof_ms[GZ_PROF_CLASSES];
+    long long prof_n[GZ_PROF_CLASSES];
+};
+
+enum { PC_SELECT = 0, PC_CONV1, PC_CONV2, PC_CONV3, PC_HEADS, PC_EXPAND, PC_MOVE, PC_ADVANCE,
+       PC_PURE_EXPAND, PC_ROLLOUT, PC_BACKUP, PC_OTHER };
+
+// RAII: records a start event now and a stop event at scope exit (only when profiling is on)
+struct ProfScope {
+    gz_engine *e;
+    int c;
+    bool live;
+    ProfScope(gz_engine *eng, int cls) : e(eng), c(cls), live(false)
+    {
+        if (!e->prof_on) return;
+        size_t u = e->prof_used[c];
+        if (u + 2 > e->prof_ev[c].size()) {
+            if (e->prof_ev[c].size() >= 400000) return;
+            for (int i = 0; i < 1024; ++i) {
+                cudaEvent_t ev;
+                if (cudaEventCreate(&ev) != cudaSuccess) return;
+                e->prof_ev[c].push_back(ev);
+            }
+        }
+        cudaEventRecord(e->prof_ev[c][u], e->stream);
+        live = true;
+    }
+    ~ProfScope()
+    {
+        if (!live) return;
+        cudaEventRecord(e->prof_ev[c][e->prof_used[c] + 1], e->stream);
+        e->prof_used[c] += 2;
+    }
 };
 
 #define GZ_CUDA(e, call)                                                                     \

@@ -176,6 +176,7 @@ int gzk_root_select_move(gz_engine *e, float temp, int selfplay, int32_t *d_move
     mp.k0 = (uint32_t)e->cfg.seed; mp.k1 = (uint32_t)(e->cfg.seed >> 32);
     mp.game_id = e->sp_begun ? e->sp_game_id : nullptr;
     mp.game_id_base = e->cfg.game_id_base;
+    ProfScope ps(e, PC_MOVE);
     root_select_kernel<<<gz_warp_blocks(e->G, 4), 128, 0, e->stream>>>(gz_tree_params(e), mp, d_moves,
                                                                         d_probs);
     e->launches++;
@@ -330,6 +331,7 @@ int gzk_selfplay_advance(gz_engine *e)
     sp.gout_moves = e->gout_moves; sp.gout_len = e->gout_len; sp.gout_winner = e->gout_winner;
     sp.gout_gid = e->gout_gid; sp.gout_count = e->gout_count;
     sp.dropped = reinterpret_cast<unsigned long long *>(&e->counters->dropped);
+    ProfScope ps(e, PC_ADVANCE);
     selfplay_advance_kernel<<<gz_warp_blocks(e->G, 4), 128, 0, e->stream>>>(gz_tree_params(e), sp);
     e->launches++;
     GZ_CUDA(e, cudaGetLastError());

@@ -283,30 +283,40 @@ static int gz_net_forward_ffma(gz_engine *e, const float *d_planes, const int32_
     NetDims d = {e->W, e->H, e->S, e->c1, e->c2, e->c3};
     const NetWeights &w = e->wts;
     {
+        ProfScope ps(e, PC_CONV1);
         long long threads = (long long)maxB * e->S * (e->c1 / 8);
         size_t smem = (size_t)(37 * e->c1) * sizeof(float);
         conv1_kernel<<<(unsigned)((threads + 255) / 256), 256, smem, e->stream>>>(
             d_planes, w.w1, w.bias + w.off_b1, e->act1, d_count, maxB, d);
     }
     const unsigned gx = (unsigned)(((long long)maxB * e->S + IG_BM - 1) / IG_BM);
+    {
+    ProfScope ps(e, PC_CONV2);
     if (e->c2 % 128 == 0)
         conv3x3_igemm_kernel<128><<<dim3(gx, e->c2 / 128), 256, 0, e->stream>>>(
             e->act1, w.w2, w.bias + w.off_b2, e->act2, d_count, maxB, e->S, e->W, e->H, e->c1, e->c2);
     else
         conv3x3_igemm_kernel<64><<<dim3(gx, e->c2 / 64), 128, 0, e->stream>>>(
             e->act1, w.w2, w.bias + w.off_b2, e->act2, d_count, maxB, e->S, e->W, e->H, e->c1, e->c2);
+    }
+    {
+    ProfScope ps(e, PC_CONV3);
     if (e->c3 % 128 == 0)
         conv3x3_igemm_kernel<128><<<dim3(gx, e->c3 / 128), 256, 0, e->stream>>>(
             e->act2, w.w3, w.bias + w.off_b3, e->act3, d_count, maxB, e->S, e->W, e->H, e->c2, e->c3);
     else
         conv3x3_igemm_kernel<64><<<dim3(gx, e->c3 / 64), 128, 0, e->stream>>>(
             e->act2, w.w3, w.bias + w.off_b3, e->act3, d_count, maxB, e->S, e->W, e->H, e->c2, e->c3);
+    }
     HeadWeights hw;
     hw.wh = w.wh; hw.bh = w.bias + w.off_bh; hw.wp = w.wpfc; hw.bp = w.bias + w.off_bp;
     hw.wv = w.wvfc; hw.bv = w.bias + w.off_bv; hw.wv2 = w.bias + w.off_wv2; hw.bv2 = w.bias + w.off_bv2;
     size_t hsm = (size_t)(e->c3 * 8 + 7 * e->S + 64 + 8) * sizeof(float);
+    {
+    ProfScope ps(e, PC_HEADS);
     heads_kernel<<<(unsigned)maxB, 128, hsm, e->stream>>>(e->act3, hw, d_probs, d_values, d_count, maxB,
                                                            e->S, e->c3);
+    }
     e->launches += 4;
     GZ_CUDA(e, cudaGetLastError());
     return GZ_OK;

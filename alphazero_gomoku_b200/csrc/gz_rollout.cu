@@ -98,11 +98,14 @@ __global__ void __launch_bounds__(128) backup_only_kernel(TreeParams p)
 int gzk_pure_expand_rollout_backup(gz_engine *e, uint32_t search_id, uint32_t playout_idx)
 {
     TreeParams p = gz_tree_params(e);
-    pure_expand_kernel<<<gz_warp_blocks(e->G, 4), 128, 0, e->stream>>>(p);
+    { ProfScope ps(e, PC_PURE_EXPAND); pure_expand_kernel<<<gz_warp_blocks(e->G, 4), 128, 0, e->stream>>>(p); }
+    {
+    ProfScope ps(e, PC_ROLLOUT);
     pure_rollout_kernel<<<(e->G + 127) / 128, 128, 0, e->stream>>>(
         p, (uint32_t)e->cfg.seed, (uint32_t)(e->cfg.seed >> 32), playout_idx, search_id,
         e->cfg.game_id_base);
-    backup_only_kernel<<<gz_warp_blocks(e->G, 4), 128, 0, e->stream>>>(p);
+    }
+    { ProfScope ps(e, PC_BACKUP); backup_only_kernel<<<gz_warp_blocks(e->G, 4), 128, 0, e->stream>>>(p); }
     e->launches += 3;
     GZ_CUDA(e, cudaGetLastError());
     return GZ_OK;
@@ -131,6 +134,7 @@ int gzk_rollouts(gz_engine *e, int n_rollouts, uint32_t search_id, int8_t *d_res
 {
     long long total = (long long)e->G * n_rollouts;
     if (total <= 0) return GZ_OK;
+    ProfScope ps(e, PC_ROLLOUT);
     rollouts_kernel<<<(unsigned)((total + 127) / 128), 128, 0, e->stream>>>(
         e->boards, e->meta, e->G, n_rollouts, e->W, e->H, e->n_in_row, (uint32_t)e->cfg.seed,
         (uint32_t)(e->cfg.seed >> 32), search_id, e->cfg.game_id_base, d_results, e->counters);

@@ -348,6 +348,7 @@ int gzk_select(gz_engine *e, bool pure)
 {
     GZ_CUDA(e, cudaMemsetAsync(e->leaf_count, 0, sizeof(int32_t), e->stream));
     TreeParams p = gz_tree_params(e);
+    ProfScope ps(e, PC_SELECT);
     if (pure) select_kernel<true><<<gz_warp_blocks(e->G, 4), 128, 0, e->stream>>>(p);
     else select_kernel<false><<<gz_warp_blocks(e->G, 4), 128, 0, e->stream>>>(p);
     e->launches++;
@@ -357,6 +358,7 @@ int gzk_select(gz_engine *e, bool pure)
 
 int gzk_expand_backup(gz_engine *e, const float *d_priors, const float *d_values, bool compacted)
 {
+    ProfScope ps(e, PC_EXPAND);
     expand_backup_kernel<<<gz_warp_blocks(e->G, 4), 128, 0, e->stream>>>(gz_tree_params(e), d_priors,
                                                                           d_values, compacted ? 1 : 0);
     e->launches++;

@@ -268,6 +268,12 @@ class Engine:
         n = n.value
         return [(int(gids[i]), int(winners[i]), moves[offsets[i]:offsets[i + 1]].tolist()) for i in range(n)]
 
+    def selfplay_last(self, moves=None, probs=None):
+        moves = np.zeros(self.G, np.int32) if moves is None else moves
+        probs = np.zeros((self.G, self.S), np.float32) if probs is None else probs
+        self._ck(self.L.gz_selfplay_last(self._h, _ptr(moves), _ptr(probs)))
+        return moves, probs
+
     def selfplay_stats(self, reset=False):
         s = GzSelfplayStats()
         self._ck(self.L.gz_selfplay_get_stats(self._h, C.byref(s), int(reset)))
@@ -294,3 +300,15 @@ class Engine:
         c = GzCounters()
         self._ck(self.L.gz_get_counters(self._h, C.byref(c), int(reset)))
         return {k: getattr(c, k) for k, _ in GzCounters._fields_}
+
+    # ---- per-kernel-class device timing ------------------------------------------------------
+    def profile_enable(self, on=True):
+        self._ck(self.L.gz_profile_enable(self._h, int(bool(on))))
+
+    def profile_read(self, reset=True):
+        """{class name: (device ms, timed launches)} since the last reset."""
+        n = _lib.PROF_CLASSES
+        ms = np.zeros(n, np.float64)
+        cnt = np.zeros(n, np.int64)
+        self._ck(self.L.gz_profile_read(self._h, _ptr(ms), _ptr(cnt), int(reset)))
+        return {self.L.gz_profile_class_name(i).decode(): (float(ms[i]), int(cnt[i])) for i in range(n)}

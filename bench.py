@@ -1,0 +1,367 @@
+#!/usr/bin/env python
+"""bench.py — MCTS playouts/s of the self-play hot path (BASELINE.json metric).
+
+  python bench.py --gpus N --steps K --warmup W            our engine (one rank per GPU)
+  python bench.py --impl reference --gpus N --steps K ...  CPU arm: the oracle port of the
+                                                           reference's CPU path, all host cores
+
+A "step" is one self-play ply in every resident game: n_playout waves of
+(select -> net on the gathered leaves -> expand + backup), then move choice, record, re-root.
+Workload at N=1 = BASELINE.json configs[2] per-GPU share: AlphaZero MCTS 8x8 five-in-a-row,
+400 playouts/move, 16384 concurrent games per GPU, shipped 8x8 weights (tests/golden).
+Prints ONE JSON line (see the task contract for the keys).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "mcts_playouts_per_sec"
+UNIT = "playouts/s"
+
+
+def net_flops(S, trunk=(32, 64, 128)):
+    """Algorithmic FLOPs (2*MAC, dense taps) per evaluated leaf, SURVEY Appendix D."""
+    c1, c2, c3 = trunk
+    conv = {"conv1": 2 * 9 * 4 * c1 * S, "conv2": 2 * 9 * c1 * c2 * S, "conv3": 2 * 9 * c2 * c3 * S,
+            "heads": 2 * (c3 * 6 * S + 4 * S * S + 2 * S * 64 + 64)}
+    conv["total"] = sum(conv.values())
+    return conv
+
+
+def load_weights(width):
+    path = os.path.join(ROOT, "tests", "golden", "weights_%d_%d_%d.npz" % (width, width, 5 if width >= 8 else 4))
+    if os.path.exists(path):
+        z = np.load(path)
+        return [z["p%02d" % i] for i in range(16)], os.path.basename(path)
+    from alphazero_gomoku_b200.engine import weight_shapes
+    rng = np.random.RandomState(0)
+    arrs = []
+    for s in weight_shapes(width, width):
+        fan = int(np.prod(s[1:])) if len(s) > 1 else 1
+        arrs.append((rng.randn(*s) * (np.sqrt(2.0 / fan) if len(s) > 1 else 0.1)).astype(np.float32))
+    return arrs, "random-init (seed 0)"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d, "measured (MEASURED_PEAKS.json)"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---- CPU legs (oracle port of the reference's CPU path) ----------------------------------------
+def cpu_selfplay_worker(arrs, width, n_in_row, n_playout, n_plies, out, idx, seed):
+    from oracle import orc
+    net = orc.Net(width, width, arrs)
+    b = orc.Board(width, width, n_in_row)
+    b.init_board(0)
+    m = orc.MCTS(5, n_playout, orc.EVAL_NET, net=net)
+    rng = np.random.RandomState(seed)
+    done = 0
+    for _ in range(n_plies):
+        acts, vis, _, _ = m.search(b)  # the C call releases the GIL
+        done += n_playout
+        p = vis / vis.sum()
+        mv = int(acts[rng.choice(len(acts), p=p)])
+        m.update_with_move(mv)
+        b.do_move(mv)
+        if b.game_end()[0]:
+            b.init_board(0)
+            m.update_with_move(-1)
+    out[idx] = done
+
+
+def cpu_baseline(arrs, width, n_in_row, n_playout, n_plies=4):
+    """Single-thread oracle port (reference = single-threaded Python) on a bounded sample."""
+    out = [0]
+    t0 = time.perf_counter()
+    cpu_selfplay_worker(arrs, width, n_in_row, n_playout, n_plies, out, 0, 0)
+    dt = time.perf_counter() - t0
+    return {"value": out[0] / dt, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": "oracle/ C port of mcts_alphaZero.MCTS + Net forward, 1 game, first %d plies x %d "
+                      "playouts from the empty %dx%d board, %.1f s" % (n_plies, n_playout, width, width, dt)}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import orc
+    orc.build()
+    arrs, wname = load_weights(args.board)
+    threads = os.cpu_count() or 1
+    plies_per_step = 1
+
+    def step():
+        out = [0] * threads
+        ts = [threading.Thread(target=cpu_selfplay_worker,
+                               args=(arrs, args.board, args.n_in_row, args.playouts, plies_per_step, out, i, i))
+              for i in range(threads)]
+        for t in ts: t.start()
+        for t in ts: t.join()
+        return sum(out)
+
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    total = 0
+    for _ in range(args.steps):
+        total += step()
+    dt = time.perf_counter() - t0
+    val = total / dt
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * dt / max(args.steps, 1),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, wname, games=threads),
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
+                             "sample": "each step: %d host threads x 1 ply x %d playouts (oracle/ C port of the "
+                                       "reference's CPU path; the Python reference cannot travel to this box)"
+                                       % (threads, args.playouts)},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def workload_config(args, wname, games):
+    return {"workload": "AlphaZero MCTS self-play %dx%d %d-in-a-row, %d playouts/move, %d concurrent games per GPU "
+                        "(BASELINE.json configs[2] per-GPU share)" % (args.board, args.board, args.n_in_row,
+                                                                      args.playouts, games),
+            "board": args.board, "n_in_row": args.n_in_row, "n_playout": args.playouts, "games_per_gpu": games,
+            "c_puct": 5, "temp": 1.0, "dirichlet": [0.1, 0.25], "weights": wname,
+            "step": "one self-play ply in every game (n_playout waves + move choice + record + re-root)",
+            "l2": "inputs larger than L2 (tree pool >> 126 MB)"}
+
+
+# ---- GPU arm -------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from alphazero_gomoku_b200 import Engine
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    stream = torch.cuda.Stream(device=dev)
+    arrs, wname = load_weights(args.board)
+    # weights travel the way an update would: rank 0 owns them, NCCL broadcast (NVLink)
+    flat = torch.from_numpy(np.concatenate([a.reshape(-1) for a in arrs])).to(dev)
+    if world > 1:
+        if rank != 0:
+            flat.zero_()
+        dist.broadcast(flat, src=0)
+    sizes = [a.size for a in arrs]
+    dev_arrs = list(torch.split(flat, sizes))
+    eng = Engine(width=args.board, height=args.board, n_in_row=args.n_in_row, n_games=args.games,
+                 n_playout=args.playouts, seed=args.seed + rank, game_id_base=rank << 40, device=local,
+                 stream=stream.cuda_stream)
+    eng.set_weights(dev_arrs)
+    eng.selfplay_begin(temp=1.0, recycle=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    for _ in range(args.warmup):
+        eng.selfplay_step(1)
+    eng.sync()
+    eng.selfplay_stats(reset=True)
+    eng.counters(reset=True)
+    eng.profile_read(reset=True)
+    eng.profile_enable(True)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for _ in range(args.steps):
+        eng.selfplay_step(1)
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    clocks = sampler.stop() if rank == 0 else None
+    eng.profile_enable(False)
+    prof = eng.profile_read(reset=True)
+    ctr = eng.counters(reset=True)
+    stats = eng.selfplay_stats(reset=True)
+
+    # ---- end to end: host weights in, host results out, every step -------------------------------
+    host_w = [torch.from_numpy(a.copy()).pin_memory() for a in arrs]
+    mv = torch.zeros(args.games, dtype=torch.int32).pin_memory()
+    pr = torch.zeros((args.games, args.board * args.board), dtype=torch.float32).pin_memory()
+    h2d = sum(a.numel() * 4 for a in host_w)
+    d2h_total = 0
+    barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        eng.set_weights([a.numpy() for a in host_w])          # H2D: the step's inputs (weights)
+        eng.selfplay_step(1)
+        eng.selfplay_last(mv.numpy(), pr.numpy())             # D2H: (move, move_probs) of the step
+        d = eng.selfplay_drain()                              # D2H: samples of games that finished
+        d2h_total += mv.numel() * 4 + pr.numel() * 4 + sum(v.nbytes for v in d.values())
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    barrier()
+    ctr2 = eng.counters(reset=True)
+    stats2 = eng.selfplay_stats(reset=True)
+
+    playouts = float(ctr["playouts"])
+    t = torch.tensor([ms, e2e_s * 1000.0], dtype=torch.float64, device=dev)
+    s = torch.tensor([playouts, float(ctr2["playouts"]), float(ctr["leaf_evals"]), float(stats["n_plies"]),
+                      float(stats["n_games"] + stats2["n_games"]), float(stats["n_samples"] + stats2["n_samples"]),
+                      float(ctr["kernel_launches"]), float(stats["pool_overflows"] + stats2["pool_overflows"])],
+                     dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(s, op=dist.ReduceOp.SUM)
+    ms_max, e2e_ms_max = t.tolist()
+    tot_playouts, tot_playouts_e2e, tot_leaf, tot_plies, tot_games, tot_samples, tot_launch, tot_over = s.tolist()
+
+    if rank == 0:
+        S = args.board * args.board
+        fl = net_flops(S)
+        pk, pk_src = peaks()
+        # dominant kernel = the class with the largest share of device time
+        dom = max(prof, key=lambda k: prof[k][0])
+        dom_ms, dom_n = prof[dom]
+        total_prof_ms = sum(v[0] for v in prof.values())
+        roof = {"bound": "tensor", "kernel": dom, "unit": "TFLOP/s", "peak": pk["bf16_tflops_sustained"],
+                "peak_source": pk_src + ", sustained bf16 (kernel timed inside a long step)",
+                "traffic": None}
+        if dom in fl and dom_ms > 0:
+            ach = ctr["leaf_evals"] * fl[dom] / (dom_ms * 1e-3) / 1e12
+            roof.update({"achieved": ach, "frac": ach / pk["bf16_tflops_sustained"],
+                         "flops_per_leaf": fl[dom], "avg_launch_ms": dom_ms / max(dom_n, 1), "launches": dom_n,
+                         "share_of_device_time": dom_ms / max(total_prof_ms, 1e-9)})
+        else:  # a tree/rule kernel dominates: HBM roofline with the algorithmic byte formula
+            lv, ch, ex = ctr["select_levels"], ctr["select_children"], ctr["expanded_children"]
+            byts = 16.0 * ch + 16.0 * (lv + ctr["playouts"]) + 20.0 * ex + ctr["leaf_evals"] * (16.0 * S + 4.0 * S + 4.0) + 128.0 * ctr["playouts"]
+            ach = byts / (max(dom_ms, 1e-9) * 1e-3) / 1e9
+            roof.update({"bound": "hbm", "unit": "GB/s", "peak": pk["hbm_gbs"], "achieved": ach,
+                         "frac": ach / pk["hbm_gbs"], "avg_launch_ms": dom_ms / max(dom_n, 1), "launches": dom_n})
+        net_ms = sum(prof[k][0] for k in ("conv1", "conv2", "conv3", "heads"))
+        mean_len = (tot_samples / tot_games) if tot_games > 0 else None
+        value = tot_playouts / (ms_max * 1e-3)
+        plies_per_s = tot_plies / (ms_max * 1e-3)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_max / max(args.steps, 1), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, wname, args.games),
+            "e2e": {"value": tot_playouts_e2e / (e2e_ms_max * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h_total // max(args.steps, 1),
+                    "what": "per step: gz_set_weights from pinned host arrays, gz_selfplay_step(1), "
+                            "gz_selfplay_last + gz_selfplay_drain into host buffers"},
+            "gpu_launches": int(tot_launch),
+            "clocks": clocks,
+            "roofline": roof,
+            "net": {"impl": "fp32 CUDA-core (FFMA) implicit GEMM", "leaf_evals": int(tot_leaf),
+                    "leaf_evals_per_s": tot_leaf / (ms_max * 1e-3),
+                    "algorithmic_tflops": ctr["leaf_evals"] * fl["total"] / max(net_ms * 1e-3, 1e-12) / 1e12,
+                    "flops_per_leaf": fl["total"]},
+            "tree": {"mean_depth": ctr["select_levels"] / max(ctr["playouts"], 1),
+                     "mean_children_per_level": ctr["select_children"] / max(ctr["select_levels"], 1),
+                     "pool_overflows": int(tot_over)},
+            "kernel_ms": {k: round(v[0], 3) for k, v in prof.items() if v[1]},
+            "selfplay": {"plies_per_s": plies_per_s, "games_finished": int(tot_games),
+                         "mean_game_len": mean_len,
+                         "games_per_hour": (plies_per_s / mean_len * 3600.0) if mean_len else None},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            from oracle import orc
+            orc.build()
+            line["cpu_baseline"] = cpu_baseline(arrs, args.board, args.n_in_row, args.playouts, args.cpu_plies)
+        if tot_over:
+            line["invalid"] = "tree pool overflowed: raise nodes_per_game"
+        print(json.dumps(line))
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--games", type=int, default=16384, help="concurrent games per GPU")
+    ap.add_argument("--board", type=int, default=8)
+    ap.add_argument("--n-in-row", type=int, default=5)
+    ap.add_argument("--playouts", type=int, default=400)
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--cpu-plies", type=int, default=4)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -161,6 +161,10 @@ int gz_selfplay_drain_games(gz_engine *e, int64_t max_games, int64_t max_moves, 
                             int64_t *offsets, int8_t *winners, int64_t *game_ids,
                             int64_t *n_games_out);
 int gz_selfplay_get_stats(gz_engine *e, gz_selfplay_stats *out, int32_t reset);
+/* What MCTSPlayer.get_action(board, temp, return_prob=1) returned in the last ply of the last
+ * gz_selfplay_step: moves int32[G] (-2 = idle slot) and move_probs float[G,S]
+ * (mcts_alphaZero.py:257-260).                                                             */
+int gz_selfplay_last(gz_engine *e, int32_t *moves, float *probs);
 
 /* ---- pure MCTS with random rollouts (mcts_pure.py:156-231) ---------------------------- */
 /* n_playout waves of: select -> uniform priors over Board.move_target -> Philox rollout
@@ -185,6 +189,14 @@ typedef struct {
     int64_t rollout_plies;
 } gz_counters;
 int gz_get_counters(gz_engine *e, gz_counters *out, int32_t reset);
+
+
+/* ---- per-kernel-class device timing (CUDA events on the engine stream) for bench.py ----- */
+#define GZ_PROF_CLASSES 12
+int gz_profile_enable(gz_engine *e, int32_t on);
+/* ms[c] = summed device time, launches[c] = timed launches of class c since the last reset */
+int gz_profile_read(gz_engine *e, double *ms /*[GZ_PROF_CLASSES]*/, int64_t *launches, int32_t reset);
+const char *gz_profile_class_name(int32_t c);
 
 #ifdef __cplusplus
 }

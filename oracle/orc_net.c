@@ -16,6 +16,8 @@
  * 0 conv1.w [c1,4,3,3] 1 conv1.b | 2 conv2.w [c2,c1,3,3] 3 b | 4 conv3.w [c3,c2,3,3] 5 b
  * 6 act_conv1.w [4,c3,1,1] 7 b | 8 act_fc1.w [S,4S] 9 b
  * 10 val_conv1.w [2,c3,1,1] 11 b | 12 val_fc1.w [64,2S] 13 b | 14 val_fc2.w [1,64] 15 b */
+#define ORC_NET_MAXS 225
+
 typedef struct {
     int W, H, c1, c2, c3;
     const float *p[16];
@@ -24,24 +26,29 @@ typedef struct {
 static void conv3x3_relu(const float *in, int cin, const float *w, const float *bias,
                          int cout, int H, int W, float *out)
 {
-    for (int co = 0; co < cout; ++co)
-        for (int y = 0; y < H; ++y)
-            for (int x = 0; x < W; ++x) {
-                double acc = bias[co];
-                for (int ci = 0; ci < cin; ++ci)
-                    for (int ky = 0; ky < 3; ++ky) {
-                        int yy = y + ky - 1;
+    /* same sums as the textbook 7-deep loop, reordered so the innermost loop runs over a
+     * contiguous row (vectorisable); accumulation stays in double */
+    double acc[ORC_NET_MAXS];
+    for (int co = 0; co < cout; ++co) {
+        for (int i = 0; i < H * W; ++i) acc[i] = bias[co];
+        for (int ci = 0; ci < cin; ++ci)
+            for (int ky = 0; ky < 3; ++ky)
+                for (int kx = 0; kx < 3; ++kx) {
+                    const double wv = (double)w[((co * cin + ci) * 3 + ky) * 3 + kx];
+                    const int x0 = kx == 0 ? 1 : 0, x1 = kx == 2 ? W - 1 : W;
+                    for (int y = 0; y < H; ++y) {
+                        const int yy = y + ky - 1;
                         if (yy < 0 || yy >= H) continue;
-                        for (int kx = 0; kx < 3; ++kx) {
-                            int xx = x + kx - 1;
-                            if (xx < 0 || xx >= W) continue;
-                            acc += (double)in[(ci * H + yy) * W + xx] *
-                                   (double)w[((co * cin + ci) * 3 + ky) * 3 + kx];
-                        }
+                        const float *src = in + (ci * H + yy) * W + (kx - 1);
+                        double *dst = acc + y * W;
+                        for (int x = x0; x < x1; ++x) dst[x] += (double)src[x] * wv;
                     }
-                float v = (float)acc;
-                out[(co * H + y) * W + x] = v > 0.f ? v : 0.f;
-            }
+                }
+        for (int i = 0; i < H * W; ++i) {
+            float v = (float)acc[i];
+            out[co * H * W + i] = v > 0.f ? v : 0.f;
+        }
+    }
 }
 
 static void conv1x1_relu(const float *in, int cin, const float *w, const float *bias,
