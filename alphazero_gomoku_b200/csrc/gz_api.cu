@@ -1,6 +1,7 @@
 // gz_api.cu — the C ABI (include/gomoku_b200.h) over the kernels.  Single translation unit:
 // the kernel files are included here so device helpers are shared without relocatable code.
 #include "gz_engine.h"
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -211,7 +212,7 @@ extern "C" void gz_destroy(gz_engine *e)
                     e->sel_probs, e->out_states, e->out_pi, e->out_z, e->out_gid, e->out_ply, e->out_count,
                     e->gout_moves, e->gout_len, e->gout_winner, e->gout_gid, e->gout_count, e->counters,
                     e->roll_results, e->wts.w1, e->wts.w2, e->wts.w3, e->wts.wh, e->wts.wpfc, e->wts.wvfc,
-                    e->wts.bias};
+                    e->wts.bias, e->wts.tc_img, e->tc_head, e->tc_dbg};
     for (void *p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 16; ++i) if (e->wts.raw[i]) cudaFree(e->wts.raw[i]);
     for (int c = 0; c < GZ_PROF_CLASSES; ++c) for (cudaEvent_t ev : e->prof_ev[c]) cudaEventDestroy(ev);
@@ -241,6 +242,8 @@ template <typename T> static int gz_upload(gz_engine *e, T **dst, const std::vec
     GZ_CUDA(e, cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
     return GZ_OK;
 }
+
+#include "gz_net_tc.cu"
 
 static void gz_conv_to_tap_major(const std::vector<float> &w, int cout, int cin, std::vector<float> &o)
 {
@@ -295,6 +298,7 @@ int gz_net_prepare_weights(gz_engine *e, std::vector<float> h[16])
     std::copy(h[14].begin(), h[14].end(), t.begin() + w.off_wv2);
     t[w.off_bv2] = h[15][0];
     GZ_TRY(gz_upload(e, &e->wts.bias, t));
+    if (gz_tc_supported(e)) GZ_TRY(gz_tc_prepare_weights(e, h));
     return GZ_OK;
 }
 
@@ -355,6 +359,11 @@ int gzk_net_forward(gz_engine *e, const float *d_planes, const int32_t *d_count,
                     float *d_probs, float *d_values)
 {
     if (!e->wts.loaded) { e->err = "gz_set_weights has not been called"; return GZ_E_NOWEIGHTS; }
+    // net_impl: 0 = tcgen05 path when the trunk is the reference 32/64/128, 1 = fp32 CUDA-core path,
+    // 2 = tcgen05 path or an error
+    const int impl = e->cfg.net_impl;
+    if (impl == 2 || (impl == 0 && gz_tc_supported(e)))
+        return gz_net_forward_tc(e, d_planes, d_count, maxB, d_probs, d_values, false);
     return gz_net_forward_ffma(e, d_planes, d_count, maxB, d_probs, d_values);
 }
 
@@ -529,6 +538,39 @@ extern "C" int gz_net_forward(gz_engine *e, const float *planes, int64_t B, floa
     if (a.rc) return a.rc;
     GZ_TRY(gzk_net_forward(e, dp, nullptr, B, dpr, dv));
     return a.finish();
+}
+
+// Diagnostic: the tcgen05 path with its per-layer activations exported (parity tests).
+extern "C" int gz_debug_net_layers(gz_engine *e, const float *planes, int64_t B, float *act1, float *act2,
+                                   float *act3, float *head, float *probs, float *values)
+{
+    if (!e || !planes || B <= 0) return GZ_E_INVALID;
+    if (!e->wts.loaded) { e->err = "gz_set_weights has not been called"; return GZ_E_NOWEIGHTS; }
+    if (!gz_tc_supported(e)) { e->err = "tcgen05 net path needs a square board and the 32/64/128 trunk"; return GZ_E_INVALID; }
+    GZ_CUDA(e, cudaSetDevice(e->cfg.device));
+    const size_t S = e->S, N = (size_t)B;
+    ArgStage a(e);
+    GZ_TRY(a.reserve(N * S * 20 + N * 8 + 2048));
+    const float *dp = a.in(planes, N * 4 * S);
+    float *dpr = a.out(probs, N * S);
+    float *dv = a.out(values, N);
+    if (a.rc) return a.rc;
+    float *tp = nullptr, *tv = nullptr;
+    if (!dpr) { GZ_CUDA(e, cudaMalloc(&tp, N * S * sizeof(float))); dpr = tp; }
+    if (!dv) { GZ_CUDA(e, cudaMalloc(&tv, N * sizeof(float))); dv = tv; }
+    int rc = gz_tc_ensure_buffers(e, B, true);
+    if (rc == GZ_OK) GZ_CUDA(e, cudaMemsetAsync(e->tc_dbg, 0, N * S * 224 * sizeof(float), e->stream));
+    if (rc == GZ_OK) rc = gz_net_forward_tc(e, dp, nullptr, B, dpr, dv, true);
+    if (rc == GZ_OK) rc = a.finish();
+    if (rc == GZ_OK) {
+        if (act1) GZ_CUDA(e, cudaMemcpy(act1, e->tc_dbg, N * S * 32 * 4, cudaMemcpyDefault));
+        if (act2) GZ_CUDA(e, cudaMemcpy(act2, e->tc_dbg + N * S * 32, N * S * 64 * 4, cudaMemcpyDefault));
+        if (act3) GZ_CUDA(e, cudaMemcpy(act3, e->tc_dbg + N * S * 96, N * S * 128 * 4, cudaMemcpyDefault));
+        if (head) GZ_CUDA(e, cudaMemcpy(head, e->tc_head, N * 6 * S * 4, cudaMemcpyDefault));
+    }
+    if (tp) cudaFree(tp);
+    if (tv) cudaFree(tv);
+    return rc;
 }
 
 // ---- search -----------------------------------------------------------------------------------

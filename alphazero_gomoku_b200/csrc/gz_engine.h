@@ -46,6 +46,8 @@ struct NetWeights {
     float *wvfc = nullptr; // value fc1 transposed [2S][64]
     float *bias = nullptr; // packed: b1 | b2 | b3 | bh[8] | bp[S] | bv[64] | wv2[64] | bv2[1]
     int off_b1 = 0, off_b2 = 0, off_b3 = 0, off_bh = 0, off_bp = 0, off_bv = 0, off_wv2 = 0, off_bv2 = 0;
+    uint8_t *tc_img = nullptr; // tcgen05 path: fp16 hi/lo conv weight image (gz_net_tc.cu layout)
+    float tc_inv[3] = {1.f, 1.f, 1.f}; // 1 / power-of-two weight scale of conv1..3
     bool loaded = false;
 };
 
@@ -85,6 +87,11 @@ struct gz_engine {
     NetWeights wts;
     float *act1, *act2, *act3; // NHWC activations for the fp32 path
     int64_t act_cap;           // boards the activation buffers hold
+    float *tc_head;            // tcgen05 path: ReLU(1x1 head convs) [B][6][S]
+    float *tc_dbg;             // optional per-layer dump for parity tests
+    int64_t tc_cap, tc_dbg_cap;
+    int n_sm;
+    unsigned attr_done;        // bit i: cudaFuncSetAttribute done for kernel i
     // staging for host<->device argument copies
     void *stage;
     size_t stage_bytes;

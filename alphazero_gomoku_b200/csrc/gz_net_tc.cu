@@ -1,0 +1,673 @@
+// gz_net_tc.cu — PolicyValueNet forward (reference policy_value_net_pytorch.py:25-57) on the
+// sm_100a tensor cores (net_impl = 2, the default for the reference trunk 32/64/128).
+//
+//   trunk_tc_kernel   conv1 -> conv2 -> conv3 -> both 1x1 head convs, fused per group of boards:
+//                     activations never leave the SM.  Each 3x3 conv is an implicit GEMM issued as
+//                     tcgen05.mma (M = 128 board cells, N = Cout, K = 16 channels of one filter tap),
+//                     accumulators in TMEM, weights streamed by the bulk-copy engine (cp.async.bulk,
+//                     the TMA unit) through a 4-slot mbarrier ring.
+//   heads_fc_kernel   policy FC + softmax, value FC1 + ReLU + FC2 + tanh in fp32 on CUDA cores over
+//                     tiles of boards (the FC weights of a tile are read once per tile, not per board).
+//
+// Implicit GEMM without im2col.  A board lives in shared memory as rows of a padded line space:
+// cell (i, j) -> row i * P + j with P = W + 1 (one always-zero column separates board rows) and
+// P + 1 zero rows separate consecutive boards, so filter tap (dy, dx) is a constant row shift
+// dy * P + dx.  Activations are stored K-major in the no-swizzle UMMA layout
+// [8-channel chunk][row][8 halves]: 16 bytes per (row, chunk), rows contiguous, so a shifted A
+// tile is the same matrix descriptor with the start address moved by shift * 16 bytes.  Outputs
+// computed for padding rows are forced to zero by the epilogue.
+//
+// fp32-grade numerics on fp16 tensor cores: every operand is split x = hi + lo (two fp16
+// values, 22 mantissa bits) and each product is issued as three MMAs hi*hi + lo*hi + hi*lo with
+// fp32 accumulation in TMEM; weights are pre-scaled by a power of two per layer so that their lo
+// parts stay in the fp16 normal range.  Board planes are exactly {0, 1}; arbitrary float inputs
+// are split the same way.
+// Included by gz_api.cu (single translation unit).
+#include <cuda_fp16.h>
+
+namespace tc {
+constexpr int C1 = 32, C2 = 64, C3 = 128;
+constexpr int ROWS = 256;                 // output rows per group (2 M-tiles of 128)
+constexpr int LEAD = 24;                  // zero rows before row 0 (>= P + 1)
+constexpr int RALLOC = 304;               // LEAD + ROWS + 24 trailing rows
+constexpr int CH = RALLOC * 16;           // bytes of one 8-channel chunk plane
+constexpr int OFF_A0 = 0;                 // input planes: chunk 0 = hi(4 planes) | lo(4 planes), chunk 1 = zeros
+constexpr int OFF_ACT1 = OFF_A0 + 2 * CH; // conv1 output: 4 hi planes, 4 lo planes
+constexpr int OFF_ACT2 = OFF_ACT1 + 8 * CH; // conv2 output: 8 hi planes, 8 lo planes
+constexpr int OFF_W1 = OFF_ACT2 + 16 * CH;  // conv1 weights, resident: [pass][tap][chunk 2][32][8]
+constexpr int W1_BYTES = 2 * 9 * 2 * 32 * 16;
+constexpr int NSTAGE = 4, STAGE_BYTES = 16384;
+constexpr int OFF_RING = OFF_W1 + W1_BYTES;
+constexpr int OFF_WH = OFF_RING + NSTAGE * STAGE_BYTES; // 1x1 head weights fp32 [128][8]
+constexpr int OFF_BIAS = OFF_WH + 4096;   // b1[32] b2[64] b3[128] bh[8]
+constexpr int OFF_BAR = OFF_BIAS + 1024;  // full[4] empty[4] mma_done, tmem base
+constexpr int SMEM_BYTES = OFF_BAR + 128;
+constexpr int W2_STAGE = 8192;            // one tap: [pass][chunk 4][64][8]
+constexpr int W3_STAGE = 16384;           // half a tap: [pass][chunk 4][128][8]
+constexpr int N_STAGES_PER_GROUP = 9 + 18;
+constexpr size_t WIMG_BYTES = (size_t)W1_BYTES + 9 * W2_STAGE + 18 * W3_STAGE;
+constexpr int TM_C1 = 0, TM_C2 = 64, TM_C3 = 256; // TMEM column bases of the three accumulators
+constexpr int THREADS = 320;              // 8 epilogue warps, 1 MMA warp, 1 copy warp
+constexpr int SYNC_THREADS = 288;         // everyone but the copy warp
+} // namespace tc
+
+struct TcGeom {
+    int W, S, P, BS, NB; // board side, cells, row pitch W+1, board stride in rows, boards per group
+};
+
+// ---- PTX wrappers -----------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t tc_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void tc_mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void tc_mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tc_mbar_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok)
+                     : "r"(bar), "r"(parity)
+                     : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void tc_bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void tc_umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                            uint32_t accumulate)
+{
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "setp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+                 "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+                 : "memory");
+}
+__device__ __forceinline__ void tc_umma_commit(uint32_t bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(tc::SYNC_THREADS) : "memory"); }
+__device__ __forceinline__ void tc_tmem_ld32(uint32_t taddr, uint32_t (&v)[32])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]),
+                   "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]),
+                   "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]),
+                   "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                 : "r"(taddr)
+                 : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// K-major, no-swizzle shared-memory matrix descriptor: rows 16 B apart inside an 8-row core
+// matrix, 8-row groups 128 B apart (SBO), the two 8-element K chunks of one MMA lbo bytes apart.
+__device__ __forceinline__ uint64_t tc_desc(uint32_t saddr, uint32_t lbo_bytes)
+{
+    const uint32_t lo = ((saddr >> 4) & 0x3FFFu) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+    const uint32_t hi = (128u >> 4) | (1u << 14); // SBO = 128 B, descriptor version 1 (sm_100)
+    return ((uint64_t)hi << 32) | lo;
+}
+// kind::f16 instruction descriptor: fp16 x fp16 -> fp32, both operands K-major, M = 128
+__device__ __forceinline__ constexpr uint32_t tc_idesc(int N) { return (1u << 4) | ((uint32_t)(N >> 3) << 17) | (8u << 24); }
+
+// split 8 fp32 values into 8 hi halves and 8 lo halves, 16 B each
+__device__ __forceinline__ void tc_split8(const float *f, uint4 &hi, uint4 &lo)
+{
+    uint32_t h[4], l[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const __half2 hh = __floats2half2_rn(f[2 * q], f[2 * q + 1]);
+        const float2 back = __half22float2(hh);
+        const __half2 ll = __floats2half2_rn(f[2 * q] - back.x, f[2 * q + 1] - back.y);
+        h[q] = *reinterpret_cast<const uint32_t *>(&hh);
+        l[q] = *reinterpret_cast<const uint32_t *>(&ll);
+    }
+    hi = make_uint4(h[0], h[1], h[2], h[3]);
+    lo = make_uint4(l[0], l[1], l[2], l[3]);
+}
+
+// ---- fused trunk ------------------------------------------------------------------------------
+// planes  [B][4][S] fp32 in {0,1};  wimg = conv1 image | 9 conv2 stages | 18 conv3 stages (fp16);
+// wh [128][8] fp32 (cols 0-3 policy conv, 4-5 value conv);  bias = b1 | b2 | b3 | bh[8];
+// head_out [B][6][S] fp32 = ReLU(1x1 convs);  dbg (optional) = act1 [B][S][32] | act2 [B][S][64] |
+// act3 [B][S][128] fp32 for parity tests.
+__global__ void __launch_bounds__(tc::THREADS, 1)
+trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wimg, const float *__restrict__ wh,
+                const float *__restrict__ bias, float inv_s1, float inv_s2, float inv_s3,
+                float *__restrict__ head_out, const int32_t *__restrict__ count, long long maxB, TcGeom g,
+                float *__restrict__ dbg)
+{
+    using namespace tc;
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long long B = count ? (long long)*count : maxB;
+    const long long n_groups = (B + g.NB - 1) / g.NB;
+    const uint32_t sbase = tc_smem_u32(smem);
+    const uint32_t bar_full = sbase + OFF_BAR, bar_empty = sbase + OFF_BAR + 32, bar_mma = sbase + OFF_BAR + 64;
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(smem + OFF_BAR + 96);
+
+    // ---- one-time setup ----------------------------------------------------------------------
+    for (int i = tid; i < OFF_W1 / 16; i += THREADS) reinterpret_cast<uint4 *>(smem)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < W1_BYTES / 16; i += THREADS)
+        reinterpret_cast<uint4 *>(smem + OFF_W1)[i] = reinterpret_cast<const uint4 *>(wimg)[i];
+    for (int i = tid; i < C3 * 8; i += THREADS) reinterpret_cast<float *>(smem + OFF_WH)[i] = wh[i];
+    for (int i = tid; i < C1 + C2 + C3 + 8; i += THREADS) reinterpret_cast<float *>(smem + OFF_BIAS)[i] = bias[i];
+    if (tid == 0) {
+        for (int s = 0; s < NSTAGE; ++s) {
+            tc_mbar_init(bar_full + 8 * s, 1);
+            tc_mbar_init(bar_empty + 8 * s, 1);
+        }
+        tc_mbar_init(bar_mma, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sbase + OFF_BAR + 96),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_async_smem(); // zeroed / preloaded smem must be visible to the tensor core's async proxy
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 9) {
+        // ---- weight-stage producer: one lane feeds the ring for every group of this CTA -------
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+                for (int s = 0; s < N_STAGES_PER_GROUP; ++s, ++it) {
+                    const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
+                    tc_mbar_wait(bar_empty + 8 * slot, ph ^ 1u);
+                    const uint32_t bytes = s < 9 ? W2_STAGE : W3_STAGE;
+                    const size_t off = (size_t)W1_BYTES + (s < 9 ? (size_t)s * W2_STAGE
+                                                                 : (size_t)9 * W2_STAGE + (size_t)(s - 9) * W3_STAGE);
+                    tc_mbar_expect_tx(bar_full + 8 * slot, bytes);
+                    tc_bulk_g2s(sbase + OFF_RING + slot * STAGE_BYTES, wimg + off, bytes, bar_full + 8 * slot);
+                }
+            }
+        }
+    } else {
+        // ---- per-thread constants --------------------------------------------------------------
+        // epilogue thread <-> output row r = tile * 128 + lane-of-tile; TMEM lane = r % 128
+        const int tile = warp >> 2;              // warps 0-3 -> tile 0, 4-7 -> tile 1 (warp 8: unused)
+        const int r = tid;                        // rows 0..255 for warps 0-7
+        const int bq = r / g.BS, rr = r % g.BS;
+        const int ci = rr / g.P, cj = rr % g.P;
+        const bool geo_ok = warp < 8 && bq < g.NB && ci < g.W && cj < g.W;
+        const int cell = ci * g.W + cj;
+        const uint32_t t_lane = ((uint32_t)((warp & 3) * 32)) << 16;
+        const float *s_b1 = reinterpret_cast<const float *>(smem + OFF_BIAS);
+        const float *s_b2 = s_b1 + C1, *s_b3 = s_b2 + C2, *s_bh = s_b3 + C3;
+        const float *s_wh = reinterpret_cast<const float *>(smem + OFF_WH);
+        const uint32_t row_off = (uint32_t)(LEAD + r) * 16u;
+        uint32_t mma_phase = 0, it = 0;
+        int shift[9];
+#pragma unroll
+        for (int t = 0; t < 9; ++t) shift[t] = (t / 3 - 1) * g.P + (t % 3 - 1);
+
+        for (long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+            const long long board = grp * g.NB + bq;
+            const bool valid = geo_ok && board < B;
+
+            // ---- phase 0: input planes -> A0 chunk 0 (fp16 hi in channels 0-3, lo in 4-7) -------
+            if (warp < 8) {
+                uint4 v = make_uint4(0, 0, 0, 0);
+                if (valid) {
+                    // channels 0-3 = hi(plane), 4-7 = lo(plane): exact for {0,1} boards, fp32-grade
+                    // for the arbitrary float states policy_value(state_batch) may be given
+                    const float *pp = planes + board * 4 * g.S + cell;
+                    const float x0 = pp[0], x1 = pp[g.S], x2 = pp[2 * g.S], x3 = pp[3 * g.S];
+                    const __half2 a = __floats2half2_rn(x0, x1), b = __floats2half2_rn(x2, x3);
+                    const float2 fa = __half22float2(a), fb = __half22float2(b);
+                    const __half2 la = __floats2half2_rn(x0 - fa.x, x1 - fa.y), lb = __floats2half2_rn(x2 - fb.x, x3 - fb.y);
+                    v.x = *reinterpret_cast<const uint32_t *>(&a);
+                    v.y = *reinterpret_cast<const uint32_t *>(&b);
+                    v.z = *reinterpret_cast<const uint32_t *>(&la);
+                    v.w = *reinterpret_cast<const uint32_t *>(&lb);
+                }
+                *reinterpret_cast<uint4 *>(smem + OFF_A0 + row_off) = v;
+            }
+            tc_fence_async_smem();
+            tc_bar_sync();
+
+            // ---- phase 1: conv1 ------------------------------------------------------------------
+            if (warp == 8) {
+                if (lane == 0) {
+                    tc_fence_after();
+                    for (int j = 0; j < 2; ++j)
+                        for (int t = 0; t < 9; ++t)
+                            for (int p = 0; p < 2; ++p) {
+                                const uint64_t a = tc_desc(sbase + OFF_A0 + (uint32_t)(LEAD + j * 128 + shift[t]) * 16u, CH);
+                                const uint64_t b = tc_desc(sbase + OFF_W1 + (uint32_t)(p * 9 + t) * 1024u, 512);
+                                tc_umma_f16(tmem + TM_C1 + j * C1, a, b, tc_idesc(C1), (t | p) != 0);
+                            }
+                    tc_umma_commit(bar_mma);
+                }
+                __syncwarp();
+            } else {
+                tc_mbar_wait(bar_mma, mma_phase);
+                tc_fence_after();
+                uint32_t v[32];
+                tc_tmem_ld32(tmem + t_lane + TM_C1 + tile * C1, v);
+                float f[32];
+#pragma unroll
+                for (int c = 0; c < 32; ++c) f[c] = valid ? fmaxf(fmaf(__uint_as_float(v[c]), inv_s1, s_b1[c]), 0.f) : 0.f;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint4 hi, lo;
+                    tc_split8(f + 8 * c, hi, lo);
+                    *reinterpret_cast<uint4 *>(smem + OFF_ACT1 + c * CH + row_off) = hi;
+                    *reinterpret_cast<uint4 *>(smem + OFF_ACT1 + (4 + c) * CH + row_off) = lo;
+                }
+                if (dbg && valid) {
+                    float *d = dbg + ((size_t)board * g.S + cell) * C1;
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) d[c] = f[c];
+                }
+                tc_fence_async_smem();
+                tc_fence_before();
+            }
+            mma_phase ^= 1u;
+            tc_bar_sync();
+
+            // ---- phase 2: conv2 (one ring stage per tap) -----------------------------------------
+            if (warp == 8) {
+                if (lane == 0) {
+                    tc_fence_after();
+                    for (int t = 0; t < 9; ++t, ++it) {
+                        const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
+                        tc_mbar_wait(bar_full + 8 * slot, ph);
+                        tc_fence_after();
+                        const uint32_t wst = sbase + OFF_RING + slot * STAGE_BYTES;
+                        for (int j = 0; j < 2; ++j)
+                            for (int ks = 0; ks < 2; ++ks)
+                                for (int p = 0; p < 3; ++p) {
+                                    const int ap = (p == 1), bp = (p == 2);
+                                    const uint64_t a = tc_desc(sbase + OFF_ACT1 + (uint32_t)(ap * 4 + 2 * ks) * CH +
+                                                                   (uint32_t)(LEAD + j * 128 + shift[t]) * 16u, CH);
+                                    const uint64_t b = tc_desc(wst + (uint32_t)bp * 4096u + (uint32_t)ks * 2048u, 1024);
+                                    tc_umma_f16(tmem + TM_C2 + j * C2, a, b, tc_idesc(C2), (t | ks | p) != 0);
+                                }
+                        tc_umma_commit(bar_empty + 8 * slot);
+                    }
+                    tc_umma_commit(bar_mma);
+                }
+                __syncwarp();
+            } else {
+                tc_mbar_wait(bar_mma, mma_phase);
+                tc_fence_after();
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    uint32_t v[32];
+                    tc_tmem_ld32(tmem + t_lane + TM_C2 + tile * C2 + half * 32, v);
+                    float f[32];
+#pragma unroll
+                    for (int c = 0; c < 32; ++c)
+                        f[c] = valid ? fmaxf(fmaf(__uint_as_float(v[c]), inv_s2, s_b2[half * 32 + c]), 0.f) : 0.f;
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        uint4 hi, lo;
+                        tc_split8(f + 8 * c, hi, lo);
+                        *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (half * 4 + c) * CH + row_off) = hi;
+                        *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (8 + half * 4 + c) * CH + row_off) = lo;
+                    }
+                    if (dbg && valid) {
+                        float *d = dbg + (size_t)maxB * g.S * C1 + ((size_t)board * g.S + cell) * C2 + half * 32;
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) d[c] = f[c];
+                    }
+                }
+                tc_fence_async_smem();
+                tc_fence_before();
+            }
+            mma_phase ^= 1u;
+            tc_bar_sync();
+
+            // ---- phase 3: conv3 (two ring stages per tap: input channels 0-31, 32-63) -----------
+            if (warp == 8) {
+                if (lane == 0) {
+                    tc_fence_after();
+                    for (int s = 0; s < 18; ++s, ++it) {
+                        const int t = s >> 1, h = s & 1;
+                        const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
+                        tc_mbar_wait(bar_full + 8 * slot, ph);
+                        tc_fence_after();
+                        const uint32_t wst = sbase + OFF_RING + slot * STAGE_BYTES;
+                        for (int j = 0; j < 2; ++j)
+                            for (int ks = 0; ks < 2; ++ks)
+                                for (int p = 0; p < 3; ++p) {
+                                    const int ap = (p == 1), bp = (p == 2);
+                                    const uint64_t a = tc_desc(sbase + OFF_ACT2 + (uint32_t)(ap * 8 + h * 4 + 2 * ks) * CH +
+                                                                   (uint32_t)(LEAD + j * 128 + shift[t]) * 16u, CH);
+                                    const uint64_t b = tc_desc(wst + (uint32_t)bp * 8192u + (uint32_t)ks * 4096u, 2048);
+                                    tc_umma_f16(tmem + TM_C3 + j * C3, a, b, tc_idesc(C3), (s | ks | p) != 0);
+                                }
+                        tc_umma_commit(bar_empty + 8 * slot);
+                    }
+                    tc_umma_commit(bar_mma);
+                }
+                __syncwarp();
+            } else {
+                tc_mbar_wait(bar_mma, mma_phase);
+                tc_fence_after();
+                float hacc[6];
+#pragma unroll
+                for (int q = 0; q < 6; ++q) hacc[q] = s_bh[q];
+#pragma unroll
+                for (int part = 0; part < 4; ++part) {
+                    uint32_t v[32];
+                    tc_tmem_ld32(tmem + t_lane + TM_C3 + tile * C3 + part * 32, v);
+                    float f[32];
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) {
+                        f[c] = fmaxf(fmaf(__uint_as_float(v[c]), inv_s3, s_b3[part * 32 + c]), 0.f);
+                        const float4 w4 = *reinterpret_cast<const float4 *>(s_wh + (part * 32 + c) * 8);
+                        const float2 w2 = *reinterpret_cast<const float2 *>(s_wh + (part * 32 + c) * 8 + 4);
+                        hacc[0] = fmaf(f[c], w4.x, hacc[0]);
+                        hacc[1] = fmaf(f[c], w4.y, hacc[1]);
+                        hacc[2] = fmaf(f[c], w4.z, hacc[2]);
+                        hacc[3] = fmaf(f[c], w4.w, hacc[3]);
+                        hacc[4] = fmaf(f[c], w2.x, hacc[4]);
+                        hacc[5] = fmaf(f[c], w2.y, hacc[5]);
+                    }
+                    if (dbg && valid) {
+                        float *d = dbg + (size_t)maxB * g.S * (C1 + C2) + ((size_t)board * g.S + cell) * C3 + part * 32;
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) d[c] = f[c];
+                    }
+                }
+                if (valid) {
+                    float *o = head_out + (size_t)board * 6 * g.S + cell;
+#pragma unroll
+                    for (int q = 0; q < 6; ++q) o[(size_t)q * g.S] = fmaxf(hacc[q], 0.f);
+                }
+                tc_fence_before();
+            }
+            mma_phase ^= 1u;
+            tc_bar_sync();
+        }
+    }
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+    }
+}
+
+// ---- FC heads ---------------------------------------------------------------------------------
+// head_in [B][6][S] (rows 0-3 policy planes, 4-5 value planes; flatten order k = c*S + cell as in
+// policy_value_net_pytorch.py:50,54).  wp [4S][S], wv [2S][64] are the transposed FC weights.
+struct FcWeights {
+    const float *wp, *bp, *wv, *bv, *wv2, *bv2;
+};
+
+template <int TB, int NO>
+__global__ void __launch_bounds__(256)
+heads_fc_kernel(const float *__restrict__ head_in, FcWeights w, float *__restrict__ probs, float *__restrict__ values,
+                const int32_t *__restrict__ count, long long maxB, int S)
+{
+    constexpr int TBQ = TB / 4;
+    extern __shared__ __align__(16) float fsm[];
+    const int hs = (6 * S + 3) & ~3;   // row stride of s_h (16-byte aligned rows)
+    const int ls = S + 1;
+    float *s_h = fsm;                   // [TB][hs]
+    float *s_l = s_h + (size_t)TB * hs; // [TB][ls] logits
+    float *s_v = s_l + (size_t)TB * ls; // [TB][64]
+    const long long B = count ? (long long)*count : maxB;
+    const long long b0 = (long long)blockIdx.x * TB;
+    if (b0 >= B) return;
+    const int nb = (int)((B - b0) < TB ? (B - b0) : TB);
+    const int tid = threadIdx.x, tx = tid & 63, ty = tid >> 6;
+    for (int i = tid; i < TB * 6 * S; i += 256) {
+        const int b = i / (6 * S), k = i % (6 * S);
+        s_h[(size_t)b * hs + k] = b < nb ? head_in[(b0 + b) * 6 * S + k] : 0.f;
+    }
+    __syncthreads();
+    // policy FC: thread (tx, ty) -> outputs tx + 64*i, boards ty*TBQ .. +TBQ
+    {
+        float acc[NO][TBQ];
+#pragma unroll
+        for (int i = 0; i < NO; ++i)
+#pragma unroll
+            for (int b = 0; b < TBQ; ++b) acc[i][b] = 0.f;
+        const int K = 4 * S;
+        for (int k = 0; k < K; k += 4) {
+            float wr[NO][4];
+#pragma unroll
+            for (int i = 0; i < NO; ++i) {
+                const int o = tx + 64 * i;
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) wr[i][kk] = o < S ? __ldg(w.wp + (size_t)(k + kk) * S + o) : 0.f;
+            }
+#pragma unroll
+            for (int b = 0; b < TBQ; ++b) {
+                const float4 hv = *reinterpret_cast<const float4 *>(s_h + (size_t)(ty * TBQ + b) * hs + k);
+#pragma unroll
+                for (int i = 0; i < NO; ++i) {
+                    acc[i][b] = fmaf(hv.x, wr[i][0], acc[i][b]);
+                    acc[i][b] = fmaf(hv.y, wr[i][1], acc[i][b]);
+                    acc[i][b] = fmaf(hv.z, wr[i][2], acc[i][b]);
+                    acc[i][b] = fmaf(hv.w, wr[i][3], acc[i][b]);
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < NO; ++i) {
+            const int o = tx + 64 * i;
+            if (o < S) {
+                const float bo = w.bp[o];
+#pragma unroll
+                for (int b = 0; b < TBQ; ++b) s_l[(size_t)(ty * TBQ + b) * ls + o] = acc[i][b] + bo;
+            }
+        }
+    }
+    // value FC1 + ReLU: thread (tx, ty) -> hidden unit tx, boards ty*TBQ .. +TBQ
+    {
+        float acc[TBQ];
+#pragma unroll
+        for (int b = 0; b < TBQ; ++b) acc[b] = 0.f;
+        const int K = 2 * S;
+        for (int k = 0; k < K; ++k) {
+            const float wk = __ldg(w.wv + (size_t)k * 64 + tx);
+#pragma unroll
+            for (int b = 0; b < TBQ; ++b) acc[b] = fmaf(s_h[(size_t)(ty * TBQ + b) * hs + 4 * S + k], wk, acc[b]);
+        }
+        const float bo = w.bv[tx];
+#pragma unroll
+        for (int b = 0; b < TBQ; ++b) s_v[(ty * TBQ + b) * 64 + tx] = fmaxf(acc[b] + bo, 0.f);
+    }
+    __syncthreads();
+    // softmax (exp(log_softmax), policy_value_net_pytorch.py:51,91) and tanh(FC2): one warp per board
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int b = warp; b < nb; b += 8) {
+        const float *l = s_l + (size_t)b * ls;
+        float mx = -3.0e38f;
+        for (int o = lane; o < S; o += 32) mx = fmaxf(mx, l[o]);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+        float sum = 0.f;
+        for (int o = lane; o < S; o += 32) sum += expf(l[o] - mx);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
+        const float inv = 1.f / sum;
+        for (int o = lane; o < S; o += 32) probs[(b0 + b) * S + o] = expf(l[o] - mx) * inv;
+        float acc = s_v[b * 64 + lane] * w.wv2[lane] + s_v[b * 64 + lane + 32] * w.wv2[lane + 32];
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+        if (lane == 0) values[b0 + b] = tanhf(acc + w.bv2[0]);
+    }
+}
+
+// ---- host side --------------------------------------------------------------------------------
+static bool gz_tc_supported(const gz_engine *e)
+{
+    return e->c1 == tc::C1 && e->c2 == tc::C2 && e->c3 == tc::C3 && e->W == e->H && e->W >= 3 && e->W <= 15;
+}
+
+static TcGeom gz_tc_geom(const gz_engine *e)
+{
+    TcGeom g;
+    g.W = e->W; g.S = e->S; g.P = e->W + 1;
+    g.BS = e->W * g.P + g.P + 1;
+    g.NB = 1 + (tc::ROWS - e->W * g.P) / g.BS;
+    return g;
+}
+
+// power-of-two scale that puts max|w| * s into [128, 256)
+static float gz_tc_scale(const std::vector<float> &w)
+{
+    float mx = 0.f;
+    for (float v : w) mx = fmaxf(mx, fabsf(v));
+    if (!(mx > 0.f) || !std::isfinite(mx)) return 1.f;
+    int ex;
+    frexpf(mx, &ex); // mx = m * 2^ex, m in [0.5, 1)
+    return ldexpf(1.f, 8 - ex);
+}
+
+static void gz_tc_split(float v, float &hi_back, __half &hi, __half &lo)
+{
+    hi = __float2half_rn(v);
+    hi_back = __half2float(hi);
+    lo = __float2half_rn(v - hi_back);
+}
+
+// builds the fp16 weight image (see tc:: layout constants) from torch-layout fp32 conv weights
+int gz_tc_prepare_weights(gz_engine *e, std::vector<float> h[16])
+{
+    using namespace tc;
+    std::vector<uint8_t> img(WIMG_BYTES, 0);
+    const float s1 = gz_tc_scale(h[0]), s2 = gz_tc_scale(h[2]), s3 = gz_tc_scale(h[4]);
+    auto put2 = [&](size_t off_hi, size_t off_lo, float v) {
+        float back;
+        __half hi, lo;
+        gz_tc_split(v, back, hi, lo);
+        memcpy(img.data() + off_hi, &hi, 2);
+        memcpy(img.data() + off_lo, &lo, 2);
+    };
+    // conv1: [pass][tap][chunk 2][row 32][8]; chunk 1 is zero.  The A operand carries hi(x) in
+    // elements 0-3 and lo(x) in 4-7, so pass 0 = (w_hi, w_hi) gives x_hi*w_hi + x_lo*w_hi and
+    // pass 1 = (w_lo, 0) gives x_hi*w_lo.
+    for (int t = 0; t < 9; ++t)
+        for (int n = 0; n < C1; ++n)
+            for (int ci = 0; ci < 4; ++ci) {
+                const float v = h[0][((size_t)n * 4 + ci) * 9 + t] * s1;
+                const size_t o = ((size_t)t * 2 * 32 + n) * 16 + ci * 2;
+                put2(o, (size_t)9 * 1024 + o, v);
+                memcpy(img.data() + o + 8, img.data() + o, 2);
+            }
+    // conv2 stage t: [pass][chunk 4][row 64][8]
+    for (int t = 0; t < 9; ++t)
+        for (int n = 0; n < C2; ++n)
+            for (int ci = 0; ci < C1; ++ci) {
+                const float v = h[2][((size_t)n * C1 + ci) * 9 + t] * s2;
+                const size_t base = (size_t)W1_BYTES + (size_t)t * W2_STAGE;
+                const size_t o = ((size_t)(ci / 8) * 64 + n) * 16 + (ci % 8) * 2;
+                put2(base + o, base + 4096 + o, v);
+            }
+    // conv3 stage (t, half): [pass][chunk 4][row 128][8]
+    for (int t = 0; t < 9; ++t)
+        for (int n = 0; n < C3; ++n)
+            for (int ci = 0; ci < C2; ++ci) {
+                const float v = h[4][((size_t)n * C2 + ci) * 9 + t] * s3;
+                const int hf = ci / 32, cc = ci % 32;
+                const size_t base = (size_t)W1_BYTES + (size_t)9 * W2_STAGE + (size_t)(t * 2 + hf) * W3_STAGE;
+                const size_t o = ((size_t)(cc / 8) * 128 + n) * 16 + (cc % 8) * 2;
+                put2(base + o, base + 8192 + o, v);
+            }
+    GZ_TRY(gz_upload(e, &e->wts.tc_img, img));
+    e->wts.tc_inv[0] = 1.f / s1; e->wts.tc_inv[1] = 1.f / s2; e->wts.tc_inv[2] = 1.f / s3;
+    return GZ_OK;
+}
+
+static int gz_tc_ensure_buffers(gz_engine *e, int64_t B, bool want_dbg)
+{
+    if (B > e->tc_cap) {
+        if (e->tc_head) cudaFree(e->tc_head);
+        if (e->tc_dbg) cudaFree(e->tc_dbg);
+        e->tc_head = e->tc_dbg = nullptr;
+        e->tc_cap = 0;
+        e->tc_dbg_cap = 0;
+        GZ_CUDA(e, cudaMalloc(&e->tc_head, (size_t)B * 6 * e->S * sizeof(float)));
+        e->tc_cap = B;
+    }
+    if (want_dbg && B > e->tc_dbg_cap) {
+        if (e->tc_dbg) cudaFree(e->tc_dbg);
+        e->tc_dbg = nullptr;
+        GZ_CUDA(e, cudaMalloc(&e->tc_dbg, (size_t)B * e->S * (tc::C1 + tc::C2 + tc::C3) * sizeof(float)));
+        e->tc_dbg_cap = B;
+    }
+    return GZ_OK;
+}
+
+template <int TB, int NO>
+static int gz_launch_heads_fc(gz_engine *e, const FcWeights &fw, float *d_probs, float *d_values,
+                              const int32_t *d_count, int64_t maxB)
+{
+    const int S = e->S;
+    const size_t smem = ((size_t)TB * ((6 * S + 3) & ~3) + (size_t)TB * (S + 1) + (size_t)TB * 64) * sizeof(float);
+    const unsigned bit = 2u << NO;
+    if (!(e->attr_done & bit)) {
+        GZ_CUDA(e, cudaFuncSetAttribute(heads_fc_kernel<TB, NO>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        e->attr_done |= bit;
+    }
+    heads_fc_kernel<TB, NO><<<(unsigned)((maxB + TB - 1) / TB), 256, smem, e->stream>>>(e->tc_head, fw, d_probs, d_values,
+                                                                                       d_count, maxB, S);
+    return GZ_OK;
+}
+
+static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t *d_count, int64_t maxB,
+                             float *d_probs, float *d_values, bool want_dbg)
+{
+    using namespace tc;
+    if (maxB <= 0) return GZ_OK;
+    if (!gz_tc_supported(e)) { e->err = "tcgen05 net path needs a square board and the 32/64/128 trunk"; return GZ_E_INVALID; }
+    GZ_TRY(gz_tc_ensure_buffers(e, maxB, want_dbg));
+    if (!(e->attr_done & 1u)) {
+        GZ_CUDA(e, cudaFuncSetAttribute(trunk_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        e->attr_done |= 1u;
+    }
+    if (e->n_sm <= 0) {
+        int dev = 0;
+        GZ_CUDA(e, cudaGetDevice(&dev));
+        GZ_CUDA(e, cudaDeviceGetAttribute(&e->n_sm, cudaDevAttrMultiProcessorCount, dev));
+    }
+    const TcGeom g = gz_tc_geom(e);
+    const NetWeights &w = e->wts;
+    const long long groups = (maxB + g.NB - 1) / g.NB;
+    const unsigned grid = (unsigned)(groups < e->n_sm ? groups : e->n_sm);
+    {
+        ProfScope ps(e, PC_CONV3);
+        trunk_tc_kernel<<<grid, THREADS, SMEM_BYTES, e->stream>>>(d_planes, w.tc_img, w.wh, w.bias + w.off_b1,
+                                                                   w.tc_inv[0], w.tc_inv[1], w.tc_inv[2], e->tc_head,
+                                                                   d_count, maxB, g, want_dbg ? e->tc_dbg : nullptr);
+    }
+    FcWeights fw;
+    fw.wp = w.wpfc; fw.bp = w.bias + w.off_bp; fw.wv = w.wvfc; fw.bv = w.bias + w.off_bv;
+    fw.wv2 = w.bias + w.off_wv2; fw.bv2 = w.bias + w.off_bv2;
+    {
+        ProfScope ps(e, PC_HEADS);
+        if (e->S <= 64) GZ_TRY((gz_launch_heads_fc<32, 1>(e, fw, d_probs, d_values, d_count, maxB)));
+        else if (e->S <= 128) GZ_TRY((gz_launch_heads_fc<32, 2>(e, fw, d_probs, d_values, d_count, maxB)));
+        else GZ_TRY((gz_launch_heads_fc<16, 4>(e, fw, d_probs, d_values, d_count, maxB)));
+    }
+    e->launches += 2;
+    GZ_CUDA(e, cudaGetLastError());
+    return GZ_OK;
+}

@@ -106,6 +106,12 @@ int gz_boards_cells(gz_engine *e, int8_t *out /*[G,S]: 0 empty, 1, 2*/);
  * planes float[B,4,W,H]; probs float[B,S] = exp(log_softmax); values float[B] = tanh.    */
 int gz_net_forward(gz_engine *e, const float *planes, int64_t B, float *probs, float *values);
 
+/* Diagnostic for parity tests: runs the tensor-core path and also returns the activations after
+ * each ReLU: act1 [B,S,32], act2 [B,S,64], act3 [B,S,128] (cell-major, channel-minor) and
+ * head [B,6,S] (the two 1x1 head convs, policy_value_net_pytorch.py:49,53).  Any output may be NULL. */
+int gz_debug_net_layers(gz_engine *e, const float *planes, int64_t B, float *act1, float *act2,
+                        float *act3, float *head, float *probs, float *values);
+
 /* ---- search: MCTS.get_move_probs / _playout (mcts_alphaZero.py:113-181) ---------------
  * gz_search runs n_playout waves; each wave = one playout in every active game
  * (select -> net on the gathered leaves -> expand + backup).                             */
