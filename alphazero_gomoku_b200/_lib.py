@@ -100,7 +100,7 @@ _PROTOS = {
     "gz_profile_read": (C.c_int, [_P, _P, _P, C.c_int32]),
     "gz_profile_class_name": (C.c_char_p, [C.c_int32]),
 }
-PROF_CLASSES = 12
+PROF_CLASSES = 14
 
 _lib = None
 

@@ -933,7 +933,7 @@ extern "C" int gz_get_counters(gz_engine *e, gz_counters *out, int32_t reset)
 // ---- per-kernel-class timing ----------------------------------------------------------------------
 static const char *g_prof_names[GZ_PROF_CLASSES] = {"select", "conv1", "conv2", "conv3", "heads", "expand_backup",
                                                     "root_select_move", "selfplay_advance", "pure_expand",
-                                                    "rollout", "backup", "other"};
+                                                    "rollout", "backup", "other", "trunk_tc", "heads_fc"};
 
 extern "C" const char *gz_profile_class_name(int32_t c)
 {

@@ -133,7 +133,7 @@ struct gz_engine {
 };
 
 enum { PC_SELECT = 0, PC_CONV1, PC_CONV2, PC_CONV3, PC_HEADS, PC_EXPAND, PC_MOVE, PC_ADVANCE,
-       PC_PURE_EXPAND, PC_ROLLOUT, PC_BACKUP, PC_OTHER };
+       PC_PURE_EXPAND, PC_ROLLOUT, PC_BACKUP, PC_OTHER, PC_TRUNK_TC, PC_HEADS_FC };
 
 // RAII: records a start event now and a stop event at scope exit (only when profiling is on)
 struct ProfScope {

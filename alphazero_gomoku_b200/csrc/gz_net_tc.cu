@@ -83,18 +83,29 @@ __device__ __forceinline__ void tc_bulk_g2s(uint32_t dst, const void *src, uint3
                  "l"(src), "r"(bytes), "r"(bar)
                  : "memory");
 }
-__device__ __forceinline__ void tc_umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                            uint32_t accumulate)
+// Issued by the whole (converged) MMA warp with `leader` true in exactly one lane (tc_elect()).
+__device__ __forceinline__ uint32_t tc_elect()
 {
-    asm volatile("{\n\t.reg .pred p;\n\t"
+    uint32_t r;
+    asm volatile("{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\tselp.u32 %0, 1, 0, e;\n\t}" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void tc_umma_f16(uint32_t leader, uint32_t d_tmem, uint64_t adesc, uint64_t bdesc,
+                                            uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n\t.reg .pred p, e;\n\t"
+                 "setp.ne.b32 e, %5, 0;\n\t"
                  "setp.ne.b32 p, %4, 0;\n\t"
-                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
-                 "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+                 "@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+                 "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(leader)
                  : "memory");
 }
-__device__ __forceinline__ void tc_umma_commit(uint32_t bar)
+__device__ __forceinline__ void tc_umma_commit(uint32_t leader, uint32_t bar)
 {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+    asm volatile("{\n\t.reg .pred e;\n\t"
+                 "setp.ne.b32 e, %1, 0;\n\t"
+                 "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(bar), "r"(leader)
+                 : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -154,8 +165,9 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
 {
     using namespace tc;
     extern __shared__ __align__(128) uint8_t smem[];
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const long long B = count ? (long long)*count : maxB;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0); // warp-uniform for the compiler
+    const long long B = __shfl_sync(0xffffffffu, count ? (long long)*count : maxB, 0);
     const long long n_groups = (B + g.NB - 1) / g.NB;
     const uint32_t sbase = tc_smem_u32(smem);
     const uint32_t bar_full = sbase + OFF_BAR, bar_empty = sbase + OFF_BAR + 32, bar_mma = sbase + OFF_BAR + 64;
@@ -185,7 +197,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem = *tmem_slot;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
     if (warp == 9) {
         // ---- weight-stage producer: one lane feeds the ring for every group of this CTA -------
@@ -218,9 +230,14 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         const float *s_wh = reinterpret_cast<const float *>(smem + OFF_WH);
         const uint32_t row_off = (uint32_t)(LEAD + r) * 16u;
         uint32_t mma_phase = 0, it = 0;
+        const uint32_t leader = tc_elect(); // one lane per warp; used by the MMA warp only
         int shift[9];
 #pragma unroll
         for (int t = 0; t < 9; ++t) shift[t] = (t / 3 - 1) * g.P + (t % 3 - 1);
+        // descriptor bases; a row shift / chunk / slot offset is an add on the 16-byte address field
+        const uint64_t dA0 = tc_desc(sbase + OFF_A0 + LEAD * 16, CH), dW1 = tc_desc(sbase + OFF_W1, 512);
+        const uint64_t dAct1 = tc_desc(sbase + OFF_ACT1 + LEAD * 16, CH), dAct2 = tc_desc(sbase + OFF_ACT2 + LEAD * 16, CH);
+        const uint64_t dRing2 = tc_desc(sbase + OFF_RING, 1024), dRing3 = tc_desc(sbase + OFF_RING, 2048);
 
         for (long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
             const long long board = grp * g.NB + bq;
@@ -249,18 +266,16 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
 
             // ---- phase 1: conv1 ------------------------------------------------------------------
             if (warp == 8) {
-                if (lane == 0) {
-                    tc_fence_after();
-                    for (int j = 0; j < 2; ++j)
-                        for (int t = 0; t < 9; ++t)
-                            for (int p = 0; p < 2; ++p) {
-                                const uint64_t a = tc_desc(sbase + OFF_A0 + (uint32_t)(LEAD + j * 128 + shift[t]) * 16u, CH);
-                                const uint64_t b = tc_desc(sbase + OFF_W1 + (uint32_t)(p * 9 + t) * 1024u, 512);
-                                tc_umma_f16(tmem + TM_C1 + j * C1, a, b, tc_idesc(C1), (t | p) != 0);
-                            }
-                    tc_umma_commit(bar_mma);
-                }
-                __syncwarp();
+                tc_fence_after();
+#pragma unroll
+                for (int j = 0; j < 2; ++j)
+#pragma unroll
+                    for (int t = 0; t < 9; ++t)
+#pragma unroll
+                        for (int p = 0; p < 2; ++p)
+                            tc_umma_f16(leader, tmem + TM_C1 + j * C1, dA0 + (int64_t)(j * 128 + shift[t]),
+                                        dW1 + (uint32_t)((p * 9 + t) * 64), tc_idesc(C1), (t | p) != 0);
+                tc_umma_commit(leader, bar_mma);
             } else {
                 tc_mbar_wait(bar_mma, mma_phase);
                 tc_fence_after();
@@ -289,27 +304,26 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
 
             // ---- phase 2: conv2 (one ring stage per tap) -----------------------------------------
             if (warp == 8) {
-                if (lane == 0) {
+                tc_fence_after();
+                for (int t = 0; t < 9; ++t, ++it) {
+                    const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
+                    tc_mbar_wait(bar_full + 8 * slot, ph);
                     tc_fence_after();
-                    for (int t = 0; t < 9; ++t, ++it) {
-                        const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
-                        tc_mbar_wait(bar_full + 8 * slot, ph);
-                        tc_fence_after();
-                        const uint32_t wst = sbase + OFF_RING + slot * STAGE_BYTES;
-                        for (int j = 0; j < 2; ++j)
-                            for (int ks = 0; ks < 2; ++ks)
-                                for (int p = 0; p < 3; ++p) {
-                                    const int ap = (p == 1), bp = (p == 2);
-                                    const uint64_t a = tc_desc(sbase + OFF_ACT1 + (uint32_t)(ap * 4 + 2 * ks) * CH +
-                                                                   (uint32_t)(LEAD + j * 128 + shift[t]) * 16u, CH);
-                                    const uint64_t b = tc_desc(wst + (uint32_t)bp * 4096u + (uint32_t)ks * 2048u, 1024);
-                                    tc_umma_f16(tmem + TM_C2 + j * C2, a, b, tc_idesc(C2), (t | ks | p) != 0);
-                                }
-                        tc_umma_commit(bar_empty + 8 * slot);
-                    }
-                    tc_umma_commit(bar_mma);
+                    const uint64_t da = dAct1 + (int64_t)shift[t];
+                    const uint64_t db = dRing2 + slot * (STAGE_BYTES / 16);
+#pragma unroll
+                    for (int j = 0; j < 2; ++j)
+#pragma unroll
+                        for (int ks = 0; ks < 2; ++ks)
+#pragma unroll
+                            for (int p = 0; p < 3; ++p) {
+                                const int ap = (p == 1), bp = (p == 2);
+                                tc_umma_f16(leader, tmem + TM_C2 + j * C2, da + (uint32_t)(((ap * 4 + 2 * ks) * CH) / 16 + j * 128),
+                                            db + (uint32_t)(bp * 256 + ks * 128), tc_idesc(C2), (t | ks | p) != 0);
+                            }
+                    tc_umma_commit(leader, bar_empty + 8 * slot);
                 }
-                __syncwarp();
+                tc_umma_commit(leader, bar_mma);
             } else {
                 tc_mbar_wait(bar_mma, mma_phase);
                 tc_fence_after();
@@ -342,28 +356,27 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
 
             // ---- phase 3: conv3 (two ring stages per tap: input channels 0-31, 32-63) -----------
             if (warp == 8) {
-                if (lane == 0) {
+                tc_fence_after();
+                for (int s = 0; s < 18; ++s, ++it) {
+                    const int t = s >> 1, h = s & 1;
+                    const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
+                    tc_mbar_wait(bar_full + 8 * slot, ph);
                     tc_fence_after();
-                    for (int s = 0; s < 18; ++s, ++it) {
-                        const int t = s >> 1, h = s & 1;
-                        const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
-                        tc_mbar_wait(bar_full + 8 * slot, ph);
-                        tc_fence_after();
-                        const uint32_t wst = sbase + OFF_RING + slot * STAGE_BYTES;
-                        for (int j = 0; j < 2; ++j)
-                            for (int ks = 0; ks < 2; ++ks)
-                                for (int p = 0; p < 3; ++p) {
-                                    const int ap = (p == 1), bp = (p == 2);
-                                    const uint64_t a = tc_desc(sbase + OFF_ACT2 + (uint32_t)(ap * 8 + h * 4 + 2 * ks) * CH +
-                                                                   (uint32_t)(LEAD + j * 128 + shift[t]) * 16u, CH);
-                                    const uint64_t b = tc_desc(wst + (uint32_t)bp * 8192u + (uint32_t)ks * 4096u, 2048);
-                                    tc_umma_f16(tmem + TM_C3 + j * C3, a, b, tc_idesc(C3), (s | ks | p) != 0);
-                                }
-                        tc_umma_commit(bar_empty + 8 * slot);
-                    }
-                    tc_umma_commit(bar_mma);
+                    const uint64_t da = dAct2 + (int64_t)(shift[t] + h * ((4 * CH) / 16));
+                    const uint64_t db = dRing3 + slot * (STAGE_BYTES / 16);
+#pragma unroll
+                    for (int j = 0; j < 2; ++j)
+#pragma unroll
+                        for (int ks = 0; ks < 2; ++ks)
+#pragma unroll
+                            for (int p = 0; p < 3; ++p) {
+                                const int ap = (p == 1), bp = (p == 2);
+                                tc_umma_f16(leader, tmem + TM_C3 + j * C3, da + (uint32_t)(((ap * 8 + 2 * ks) * CH) / 16 + j * 128),
+                                            db + (uint32_t)(bp * 512 + ks * 256), tc_idesc(C3), (s | ks | p) != 0);
+                            }
+                    tc_umma_commit(leader, bar_empty + 8 * slot);
                 }
-                __syncwarp();
+                tc_umma_commit(leader, bar_mma);
             } else {
                 tc_mbar_wait(bar_mma, mma_phase);
                 tc_fence_after();
@@ -448,6 +461,7 @@ heads_fc_kernel(const float *__restrict__ head_in, FcWeights w, float *__restric
 #pragma unroll
             for (int b = 0; b < TBQ; ++b) acc[i][b] = 0.f;
         const int K = 4 * S;
+#pragma unroll 4
         for (int k = 0; k < K; k += 4) {
             float wr[NO][4];
 #pragma unroll
@@ -484,6 +498,7 @@ heads_fc_kernel(const float *__restrict__ head_in, FcWeights w, float *__restric
 #pragma unroll
         for (int b = 0; b < TBQ; ++b) acc[b] = 0.f;
         const int K = 2 * S;
+#pragma unroll 8
         for (int k = 0; k < K; ++k) {
             const float wk = __ldg(w.wv + (size_t)k * 64 + tx);
 #pragma unroll
@@ -653,7 +668,7 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
     const long long groups = (maxB + g.NB - 1) / g.NB;
     const unsigned grid = (unsigned)(groups < e->n_sm ? groups : e->n_sm);
     {
-        ProfScope ps(e, PC_CONV3);
+        ProfScope ps(e, PC_TRUNK_TC);
         trunk_tc_kernel<<<grid, THREADS, SMEM_BYTES, e->stream>>>(d_planes, w.tc_img, w.wh, w.bias + w.off_b1,
                                                                    w.tc_inv[0], w.tc_inv[1], w.tc_inv[2], e->tc_head,
                                                                    d_count, maxB, g, want_dbg ? e->tc_dbg : nullptr);
@@ -662,7 +677,7 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
     fw.wp = w.wpfc; fw.bp = w.bias + w.off_bp; fw.wv = w.wvfc; fw.bv = w.bias + w.off_bv;
     fw.wv2 = w.bias + w.off_wv2; fw.bv2 = w.bias + w.off_bv2;
     {
-        ProfScope ps(e, PC_HEADS);
+        ProfScope ps(e, PC_HEADS_FC);
         if (e->S <= 64) GZ_TRY((gz_launch_heads_fc<32, 1>(e, fw, d_probs, d_values, d_count, maxB)));
         else if (e->S <= 128) GZ_TRY((gz_launch_heads_fc<32, 2>(e, fw, d_probs, d_values, d_count, maxB)));
         else GZ_TRY((gz_launch_heads_fc<16, 4>(e, fw, d_probs, d_values, d_count, maxB)));
