@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(tc::THREADS, 1)
 trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wimg, const float *__restrict__ wh,
                 const float *__restrict__ bias, float inv_s1, float inv_s2, float inv_s3,
                 float *__restrict__ head_out, const int32_t *__restrict__ count, long long maxB, TcGeom g,
-                float *__restrict__ dbg)
+                float *__restrict__ dbg, long long *__restrict__ timeline)
 {
     using namespace tc;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -239,9 +239,15 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         const uint64_t dAct1 = tc_desc(sbase + OFF_ACT1 + LEAD * 16, CH), dAct2 = tc_desc(sbase + OFF_ACT2 + LEAD * 16, CH);
         const uint64_t dRing2 = tc_desc(sbase + OFF_RING, 1024), dRing3 = tc_desc(sbase + OFF_RING, 2048);
 
+        int tl_i = 0;
+#define TC_MARK()                                                                  \
+    do {                                                                           \
+        if (timeline && blockIdx.x == 0 && tid == 0 && tl_i < 512) timeline[tl_i++] = clock64(); \
+    } while (0)
         for (long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
             const long long board = grp * g.NB + bq;
             const bool valid = geo_ok && board < B;
+            TC_MARK(); // 0: group start
 
             // ---- phase 0: input planes -> A0 chunk 0 (fp16 hi in channels 0-3, lo in 4-7) -------
             if (warp < 8) {
@@ -263,6 +269,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             }
             tc_fence_async_smem();
             tc_bar_sync();
+            TC_MARK(); // 1: input planes staged
 
             // ---- phase 1: conv1 ------------------------------------------------------------------
             if (warp == 8) {
@@ -278,6 +285,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                 tc_umma_commit(leader, bar_mma);
             } else {
                 tc_mbar_wait(bar_mma, mma_phase);
+                TC_MARK(); // 2: conv1 MMAs done
                 tc_fence_after();
                 uint32_t v[32];
                 tc_tmem_ld32(tmem + t_lane + TM_C1 + tile * C1, v);
@@ -301,6 +309,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             }
             mma_phase ^= 1u;
             tc_bar_sync();
+            TC_MARK(); // 3: conv1 epilogue done
 
             // ---- phase 2: conv2 (one ring stage per tap) -----------------------------------------
             if (warp == 8) {
@@ -326,6 +335,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                 tc_umma_commit(leader, bar_mma);
             } else {
                 tc_mbar_wait(bar_mma, mma_phase);
+                TC_MARK(); // 4: conv2 MMAs done
                 tc_fence_after();
 #pragma unroll
                 for (int half = 0; half < 2; ++half) {
@@ -353,6 +363,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             }
             mma_phase ^= 1u;
             tc_bar_sync();
+            TC_MARK(); // 5: conv2 epilogue done
 
             // ---- phase 3: conv3 (two ring stages per tap: input channels 0-31, 32-63) -----------
             if (warp == 8) {
@@ -379,6 +390,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                 tc_umma_commit(leader, bar_mma);
             } else {
                 tc_mbar_wait(bar_mma, mma_phase);
+                TC_MARK(); // 6: conv3 MMAs done
                 tc_fence_after();
                 float hacc[6];
 #pragma unroll
@@ -415,7 +427,9 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             }
             mma_phase ^= 1u;
             tc_bar_sync();
+            TC_MARK(); // 7: conv3 epilogue + heads done
         }
+#undef TC_MARK
     }
     __syncthreads();
     if (warp == 0) {
@@ -667,11 +681,31 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
     const NetWeights &w = e->wts;
     const long long groups = (maxB + g.NB - 1) / g.NB;
     const unsigned grid = (unsigned)(groups < e->n_sm ? groups : e->n_sm);
+    // GZ_TC_TIMELINE=<file>: CTA 0 records clock64() at its phase boundaries (8 marks per group,
+    // see TC_MARK) and the host appends them to <file>; a profiling aid, off by default.
+    static const char *tl_path = getenv("GZ_TC_TIMELINE");
+    long long *d_tl = nullptr;
+    if (tl_path) {
+        GZ_CUDA(e, cudaMalloc(&d_tl, 512 * sizeof(long long)));
+        GZ_CUDA(e, cudaMemsetAsync(d_tl, 0, 512 * sizeof(long long), e->stream));
+    }
     {
         ProfScope ps(e, PC_TRUNK_TC);
         trunk_tc_kernel<<<grid, THREADS, SMEM_BYTES, e->stream>>>(d_planes, w.tc_img, w.wh, w.bias + w.off_b1,
                                                                    w.tc_inv[0], w.tc_inv[1], w.tc_inv[2], e->tc_head,
-                                                                   d_count, maxB, g, want_dbg ? e->tc_dbg : nullptr);
+                                                                   d_count, maxB, g, want_dbg ? e->tc_dbg : nullptr, d_tl);
+    }
+    if (d_tl) {
+        std::vector<long long> h(512);
+        GZ_CUDA(e, cudaStreamSynchronize(e->stream));
+        GZ_CUDA(e, cudaMemcpy(h.data(), d_tl, 512 * sizeof(long long), cudaMemcpyDeviceToHost));
+        cudaFree(d_tl);
+        if (FILE *f = fopen(tl_path, "a")) {
+            fprintf(f, "launch B=%lld grid=%u\n", (long long)maxB, grid);
+            for (int i = 0; i < 512 && h[i]; ++i) fprintf(f, "%lld%c", h[i] - h[0], (i % 8 == 7) ? '\n' : ' ');
+            fprintf(f, "\n");
+            fclose(f);
+        }
     }
     FcWeights fw;
     fw.wp = w.wpfc; fw.bp = w.bias + w.off_bp; fw.wv = w.wvfc; fw.bv = w.bias + w.off_bv;

@@ -1,0 +1,155 @@
+"""PolicyValueNet: drop-in for the reference's policy_value_net_pytorch.py (:60-157).
+
+Inference (`policy_value_fn`, `policy_value`) runs through the C ABI (gz_net_forward: the
+tcgen05 fused trunk + FC heads).  `train_step` (reference :117-148, SURVEY 8f-1, off the self-play
+hot path) is a plain PyTorch autograd step on the GPU over a torch copy of the same 16 tensors;
+after every step the new weights are pushed to every engine that uses this net.
+"""
+import pickle
+
+import numpy as np
+
+from .engine import Engine, STATE_DICT_KEYS, weight_shapes
+
+
+def set_learning_rate(optimizer, lr):
+    for param_group in optimizer.param_groups:
+        param_group['lr'] = lr
+
+
+def _default_init(width, height, seed=None):
+    """torch.nn default init of the reference Net (kaiming-uniform a=sqrt(5) == U(+-1/sqrt(fan_in)))."""
+    rng = np.random.RandomState(seed)
+    arrs = []
+    shapes = weight_shapes(width, height)
+    for i in range(0, 16, 2):
+        fan_in = int(np.prod(shapes[i][1:]))
+        bound = 1.0 / np.sqrt(fan_in)
+        arrs.append(rng.uniform(-bound, bound, size=shapes[i]).astype(np.float32))
+        arrs.append(rng.uniform(-bound, bound, size=shapes[i + 1]).astype(np.float32))
+    return arrs
+
+
+def load_model_file(path, width, height):
+    """Reads a torch state_dict (policy_value_net_pytorch.py:76-78) or a Theano/Lasagne pickle of
+    16 arrays (policy_value_net.py:118-121); returns (arrays, layout)."""
+    from . import _lib
+    try:
+        import torch
+        sd = torch.load(path, map_location="cpu")
+        if isinstance(sd, dict) and STATE_DICT_KEYS[0] in sd:
+            return [sd[k].detach().cpu().float().numpy() for k in STATE_DICT_KEYS], _lib.LAYOUT_TORCH
+    except Exception:
+        pass
+    with open(path, "rb") as f:
+        params = pickle.load(f, encoding="bytes")
+    if len(params) != 16:
+        raise Exception("model file %s: expected 16 parameter arrays, got %d" % (path, len(params)))
+    return [np.asarray(p, dtype=np.float32) for p in params], _lib.LAYOUT_THEANO
+
+
+class PolicyValueNet():
+    """policy-value network"""
+
+    def __init__(self, board_width, board_height, model_file=None, use_gpu=True, seed=None):
+        if not use_gpu:
+            raise RuntimeError("alphazero_gomoku_b200 has no CPU path: use_gpu must be True")
+        self.use_gpu = True
+        self.board_width = board_width
+        self.board_height = board_height
+        self.l2_const = 1e-4
+        self.version = 0  # bumped whenever the weights change; MCTS engines re-upload lazily
+        n = min(board_width, board_height, 5)
+        self._engine = Engine(width=board_width, height=board_height, n_in_row=n, n_games=1, n_playout=1,
+                              nodes_per_game=4)
+        from . import _lib
+        if model_file:
+            arrs, layout = load_model_file(model_file, board_width, board_height)
+        else:
+            arrs, layout = _default_init(board_width, board_height, seed), _lib.LAYOUT_TORCH
+        self._engine.set_weights(arrs, layout=layout)
+        self._params = self._engine.get_weights()  # torch layout, host copies
+        self._torch = None  # lazily built training state (module tensors + Adam)
+
+    # ---- inference -----------------------------------------------------------------------------
+    def policy_value(self, state_batch):
+        """:80-94: batch of states -> (act_probs [B,S], values [B,1]) as numpy float32."""
+        x = np.ascontiguousarray(np.asarray(state_batch, dtype=np.float32).reshape(
+            -1, 4, self.board_width, self.board_height))
+        probs, values = self._engine.net_forward(x)
+        return probs, values.reshape(-1, 1)
+
+    def policy_value_fn(self, board):
+        """:96-115: board -> (zip(legal moves, probs), value of the side to move)."""
+        legal_positions = board.availables
+        current_state = np.ascontiguousarray(board.current_state().reshape(
+            -1, 4, self.board_width, self.board_height), dtype=np.float32)
+        probs, values = self._engine.net_forward(current_state)
+        act_probs = zip(legal_positions, probs[0][legal_positions])
+        return act_probs, float(values[0])
+
+    # ---- weights -------------------------------------------------------------------------------
+    def get_policy_param(self):
+        """16 float32 arrays in state_dict order and layout (the reference returns the state_dict)."""
+        return [p.copy() for p in self._params]
+
+    def state_dict(self):
+        import torch
+        return {k: torch.from_numpy(p.copy()) for k, p in zip(STATE_DICT_KEYS, self._params)}
+
+    def set_policy_param(self, arrays, layout=0):
+        self._engine.set_weights(arrays, layout=layout)
+        self._params = self._engine.get_weights()
+        self.version += 1
+        self._torch = None
+
+    def save_model(self, model_file):
+        """:154-157: torch.save(state_dict) -- loadable by the reference's PolicyValueNet."""
+        import torch
+        torch.save(self.state_dict(), model_file)
+
+    # ---- training ----------------------------------------------------------------
+    def _train_state(self):
+        if self._torch is None:
+            import torch
+            dev = torch.device("cuda", self._engine.device)
+            params = [torch.nn.Parameter(torch.from_numpy(p.copy()).to(dev)) for p in self._params]
+            opt = torch.optim.Adam(params, weight_decay=self.l2_const)
+            self._torch = (params, opt)
+        return self._torch
+
+    def _forward_torch(self, p, x):
+        import torch
+        import torch.nn.functional as F
+        x = F.relu(F.conv2d(x, p[0], p[1], padding=1))
+        x = F.relu(F.conv2d(x, p[2], p[3], padding=1))
+        x = F.relu(F.conv2d(x, p[4], p[5], padding=1))
+        a = F.relu(F.conv2d(x, p[6], p[7])).flatten(1)
+        a = F.log_softmax(F.linear(a, p[8], p[9]), dim=1)
+        v = F.relu(F.conv2d(x, p[10], p[11])).flatten(1)
+        v = F.relu(F.linear(v, p[12], p[13]))
+        return a, torch.tanh(F.linear(v, p[14], p[15]))
+
+    def train_step(self, state_batch, mcts_probs, winner_batch, lr):
+        """:117-148: loss = MSE(v, z) - mean(sum(pi * log p)), Adam with weight decay 1e-4."""
+        import torch
+        import torch.nn.functional as F
+        params, opt = self._train_state()
+        dev = params[0].device
+        x = torch.as_tensor(np.asarray(state_batch, dtype=np.float32), device=dev)
+        pi = torch.as_tensor(np.asarray(mcts_probs, dtype=np.float32), device=dev)
+        z = torch.as_tensor(np.asarray(winner_batch, dtype=np.float32), device=dev)
+        opt.zero_grad()
+        set_learning_rate(opt, lr)
+        log_act_probs, value = self._forward_torch(params, x)
+        value_loss = F.mse_loss(value.view(-1), z)
+        policy_loss = -torch.mean(torch.sum(pi * log_act_probs, 1))
+        loss = value_loss + policy_loss
+        loss.backward()
+        opt.step()
+        entropy = -torch.mean(torch.sum(torch.exp(log_act_probs) * log_act_probs, 1))
+        with torch.no_grad():
+            self._engine.set_weights([p.detach() for p in params])
+        self._params = self._engine.get_weights()
+        self.version += 1
+        return loss.item(), entropy.item()

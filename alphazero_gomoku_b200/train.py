@@ -1,0 +1,222 @@
+"""TrainPipeline: drop-in for the self-play side of the reference's train.py (:63-214).
+
+`collect_selfplay_data(n_games)` is the hot-path entry point: the n_games are played
+CONCURRENTLY on the device (one slot each; gz_selfplay_*), not one after another, and the
+finished games come back as packed (state, pi, z) records in game order.  With
+torch.distributed initialised, every rank plays its own games and `sync_selfplay_data` /
+`broadcast_weights` are the only two collectives: an all-gather of the samples and a
+broadcast of the 16 weight tensors after an update.
+"""
+import logging
+import random
+from collections import deque
+
+import numpy as np
+
+from .engine import Engine
+from .game import Board, Game
+from .mcts_alphaZero import MCTSPlayer
+from .policy_value_net import PolicyValueNet
+
+_logger = logging.getLogger(__name__)
+
+# conf/train_config.yaml:11-37 of the reference
+DEFAULT_CONF = {"board_width": 15, "board_height": 15, "n_in_row": 5, "learn_rate": 0.002, "lr_multiplier": 0.2,
+                "temp": 1.0, "n_playout": 600, "c_puct": 5, "buffer_size": 3000, "batch_size": 512, "epochs": 6,
+                "play_batch_size": 1, "kl_targ": 0.02, "check_freq": 20, "pure_mcts_playout_num": 3000,
+                "game_batch_num": 5000}
+
+
+def equi_data(play_data, board_width, board_height):
+    """train.py:116-135: the 8 dihedral images of every (state, pi, z)."""
+    extend_data = []
+    for state, mcts_porb, winner in play_data:
+        for i in [1, 2, 3, 4]:
+            equi_state = np.array([np.rot90(s, i) for s in state])
+            equi_mcts_prob = np.rot90(np.flipud(mcts_porb.reshape(board_height, board_width)), i)
+            extend_data.append((equi_state, np.flipud(equi_mcts_prob).flatten(), winner))
+            equi_state = np.array([np.fliplr(s) for s in equi_state])
+            equi_mcts_prob = np.fliplr(equi_mcts_prob)
+            extend_data.append((equi_state, np.flipud(equi_mcts_prob).flatten(), winner))
+    return extend_data
+
+
+def shard_games(n_games, rank, world):
+    """Games [0, n_games) split over ranks: contiguous, sizes differ by at most one."""
+    base, rem = divmod(int(n_games), int(world))
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def pack_samples(states, pis, zs, game_ids, plies):
+    """One float32 record per sample: [game_id_hi, game_id_lo, ply, z, pi[S], state[4S]]."""
+    n = len(zs)
+    S = pis.shape[1] if n else 0
+    rec = np.zeros((n, 4 + 5 * S), np.float32)
+    if n:
+        gid = np.asarray(game_ids, np.int64)
+        rec[:, 0] = (gid >> 20).astype(np.float32)
+        rec[:, 1] = (gid & ((1 << 20) - 1)).astype(np.float32)
+        rec[:, 2] = plies
+        rec[:, 3] = zs
+        rec[:, 4:4 + S] = pis
+        rec[:, 4 + S:] = states.reshape(n, -1)
+    return rec
+
+
+def unpack_samples(rec, width, height):
+    S = width * height
+    gid = (rec[:, 0].astype(np.int64) << 20) | rec[:, 1].astype(np.int64)
+    return (rec[:, 4 + S:].reshape(-1, 4, width, height), rec[:, 4:4 + S], rec[:, 3], gid, rec[:, 2].astype(np.int32))
+
+
+def all_gather_samples(rec, group=None):
+    """Variable-length all-gather of packed sample records (counts first, then padded rows).
+    Works on NCCL (device tensors) and gloo (host tensors); returns the union ordered by rank."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return rec
+    world = dist.get_world_size(group)
+    dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+    n = torch.tensor([rec.shape[0]], dtype=torch.int64, device=dev)
+    counts = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(counts, n, group=group)
+    counts = [int(c.item()) for c in counts]
+    m = max(max(counts), 1)
+    pad = torch.zeros((m, rec.shape[1]), dtype=torch.float32, device=dev)
+    if rec.shape[0]:
+        pad[:rec.shape[0]] = torch.from_numpy(rec).to(dev)
+    out = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(out, pad, group=group)
+    return np.concatenate([o[:c].cpu().numpy() for o, c in zip(out, counts)], axis=0)
+
+
+def broadcast_weights(arrays, src=0, group=None):
+    """One flat broadcast of the 16 weight tensors (NVLink/NCCL when available)."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return arrays
+    dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+    flat = torch.from_numpy(np.concatenate([np.asarray(a, np.float32).reshape(-1) for a in arrays])).to(dev)
+    dist.broadcast(flat, src=src, group=group)
+    flat = flat.cpu().numpy()
+    out, o = [], 0
+    for a in arrays:
+        out.append(flat[o:o + a.size].reshape(a.shape).copy())
+        o += a.size
+    return out
+
+
+class TrainPipeline():
+    def __init__(self, conf=None, init_model=None, best_model="best_policy.model", seed=0):
+        c = dict(DEFAULT_CONF)
+        c.update(conf or {})
+        self.board_width, self.board_height, self.n_in_row = c['board_width'], c['board_height'], c['n_in_row']
+        self.board = Board(width=self.board_width, height=self.board_height, n_in_row=self.n_in_row)
+        self.game = Game(self.board)
+        self.learn_rate, self.lr_multiplier, self.temp = c['learn_rate'], c['lr_multiplier'], c['temp']
+        self.n_playout, self.c_puct = c['n_playout'], c['c_puct']
+        self.buffer_size, self.batch_size = c['buffer_size'], c['batch_size']
+        self.data_buffer = deque(maxlen=self.buffer_size)
+        self.play_batch_size, self.epochs, self.kl_targ = c['play_batch_size'], c['epochs'], c['kl_targ']
+        self.check_freq, self.game_batch_num = c['check_freq'], c['game_batch_num']
+        self.best_win_ratio = 0.2
+        self.pure_mcts_playout_num = c['pure_mcts_playout_num']
+        self.seed = seed
+        self.policy_value_net = PolicyValueNet(self.board_width, self.board_height, model_file=init_model)
+        self.mcts_player = MCTSPlayer(self.policy_value_net.policy_value_fn, c_puct=self.c_puct,
+                                      n_playout=self.n_playout, is_selfplay=1)
+        self._engine = None
+        self._engine_version = -1
+        self._games_played = 0
+        self.last_games = []
+
+    def get_equi_data(self, play_data):
+        return equi_data(play_data, self.board_width, self.board_height)
+
+    def _selfplay_engine(self, n_slots):
+        if self._engine is None or self._engine.G != n_slots:
+            if self._engine is not None:
+                self._engine.close()
+            rank = _rank()
+            self._engine = Engine(width=self.board_width, height=self.board_height, n_in_row=self.n_in_row,
+                                  n_games=n_slots, n_playout=self.n_playout, c_puct=float(self.c_puct),
+                                  seed=self.seed + rank, game_id_base=(rank << 40))
+            self._engine_version = -1
+        if self._engine_version != self.policy_value_net.version:
+            self._engine.set_weights(self.policy_value_net.get_policy_param())
+            self._engine_version = self.policy_value_net.version
+        return self._engine
+
+    def selfplay_games(self, n_games):
+        """Play n_games concurrently on the device; returns per-game [(state, pi, z), ...] lists
+        (float64 arrays, the reference's dtypes) in slot order plus the move lists."""
+        e = self._selfplay_engine(int(n_games))
+        e.selfplay_begin(temp=float(self.temp), recycle=False)
+        S = self.board_width * self.board_height
+        for _ in range(S):
+            e.selfplay_step(1)
+            if e.selfplay_pending()[2] == 0:
+                break
+        d = e.selfplay_drain()
+        self.last_games = e.selfplay_drain_games()
+        order = np.lexsort((d["plies"], d["game_ids"]))
+        games, cur, last = [], None, None
+        for i in order:
+            if d["game_ids"][i] != last:
+                cur = []
+                games.append(cur)
+                last = d["game_ids"][i]
+            cur.append((d["states"][i].astype(np.float64), d["pis"][i].astype(np.float64), float(d["zs"][i])))
+        for gid, winner, moves in sorted(self.last_games):
+            _logger.warning("{'steps':[%s],'winner':%d}" % (",".join(map(str, moves)), winner))  # game.py:411
+        self._games_played += len(games)
+        return games
+
+    def collect_selfplay_data(self, n_games=1, train_data=[]):
+        """train.py:137-159 (self-play branch): n_games games -> x8 augmentation -> data_buffer."""
+        if len(train_data) != 0:
+            raise NotImplementedError("start_from_train_data (recorded games) is outside the hot path (SURVEY 8f-4)")
+        epi_len = 0
+        for play_data in self.selfplay_games(n_games):
+            epi_len += len(play_data)
+            self.data_buffer.extend(self.get_equi_data(play_data))
+        self.episode_len = epi_len
+        return
+
+    def policy_update(self):
+        """train.py:161-214."""
+        mini_batch = random.sample(self.data_buffer, self.batch_size)
+        state_batch = [data[0] for data in mini_batch]
+        mcts_probs_batch = [data[1] for data in mini_batch]
+        winner_batch = [data[2] for data in mini_batch]
+        old_probs, old_v = self.policy_value_net.policy_value(state_batch)
+        for i in range(self.epochs):
+            loss, entropy = self.policy_value_net.train_step(state_batch, mcts_probs_batch, winner_batch,
+                                                             self.learn_rate * self.lr_multiplier)
+            new_probs, new_v = self.policy_value_net.policy_value(state_batch)
+            kl = np.mean(np.sum(old_probs * (np.log(old_probs + 1e-10) - np.log(new_probs + 1e-10)), axis=1))
+            if kl > self.kl_targ * 4:
+                break
+        if kl > self.kl_targ * 2 and self.lr_multiplier > 0.05:
+            self.lr_multiplier /= 1.5
+        elif kl < self.kl_targ / 2 and self.lr_multiplier < 10:
+            self.lr_multiplier *= 1.5
+        explained_var_old = 1 - np.var(np.array(winner_batch) - old_v.flatten()) / np.var(np.array(winner_batch))
+        explained_var_new = 1 - np.var(np.array(winner_batch) - new_v.flatten()) / np.var(np.array(winner_batch))
+        _logger.info("kl=%4.3f, lr_multiplier=%4.3f, loss=%4.3f, entropy=%4.3f, explained_var_old=%4.3f, "
+                     "explained_var_new=%4.3f" % (kl, self.lr_multiplier, loss, entropy, explained_var_old,
+                                                  explained_var_new))
+        return loss, entropy
+
+
+def _rank():
+    try:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            return dist.get_rank()
+    except Exception:
+        pass
+    return 0

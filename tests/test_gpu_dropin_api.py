@@ -1,0 +1,198 @@
+"""GPU tests of the drop-in Python API (Board / Game / MCTS / MCTSPlayer / PolicyValueNet /
+TrainPipeline.collect_selfplay_data) against the oracle and the committed reference goldens.
+These read like the calls a user of the reference makes."""
+import copy
+import os
+
+import numpy as np
+import pytest
+
+from helpers import GOLDEN, load_golden_weights
+
+pytestmark = pytest.mark.gpu
+
+
+def _save_state_dict(tmp_path, tag):
+    import torch
+    from alphazero_gomoku_b200.engine import STATE_DICT_KEYS
+    arrs = load_golden_weights("weights_" + tag)
+    path = str(tmp_path / ("w_%s.model" % tag))
+    torch.save({k: torch.from_numpy(a.copy()) for k, a in zip(STATE_DICT_KEYS, arrs)}, path)
+    return path, arrs
+
+
+def test_board_protocol_matches_oracle():
+    from alphazero_gomoku_b200 import Board
+    from oracle import orc
+    rng = np.random.RandomState(11)
+    for (w, n) in ((6, 4), (8, 5), (15, 5)):
+        for trial in range(12):
+            b = Board(width=w, height=w, n_in_row=n)
+            b.init_board(trial % 2)
+            ob = orc.Board(w, w, n)
+            ob.init_board(trial % 2)
+            for _ in range(int(rng.randint(0, w * w))):
+                if ob.game_end()[0]:
+                    break
+                m = ob.availables[rng.randint(len(ob.availables))]
+                b.do_move(m); ob.do_move(m)
+            b2 = copy.deepcopy(b)  # mcts_alphaZero.py:162 deep-copies boards
+            assert b2.availables == ob.availables and b2.states == ob.states
+            assert b2.last_move == ob.last_move and b2.current_player == ob.current_player
+            assert b2.game_end() == ob.game_end() and b2.has_a_winner() == ob.has_a_winner()
+            cs = b2.current_state()
+            assert cs.dtype == np.float64 and np.array_equal(cs, ob.current_state())
+            b2.get_move_target(); ob.get_move_target()
+            assert b2.move_target == list(ob.move_target)
+            assert b.location_to_move(b.move_to_location(7)) == 7 and b.location_to_move([w, 0]) == -1
+    with pytest.raises(Exception):
+        Board(width=4, height=4, n_in_row=5).init_board()
+
+
+@pytest.mark.parametrize("tag,w,n", [("6_6_4", 6, 4), ("8_8_5", 8, 5)])
+def test_policy_value_net_and_mcts_vs_reference_golden(tag, w, n, tmp_path):
+    from alphazero_gomoku_b200 import Board, MCTS, PolicyValueNet
+    path, arrs = _save_state_dict(tmp_path, tag)
+    net = PolicyValueNet(w, w, model_file=path)
+    z = np.load(os.path.join(GOLDEN, "net.npz"))
+    probs, vals = net.policy_value(z[tag + "_planes"])
+    assert vals.shape == (len(probs), 1)
+    assert np.abs(probs - z[tag + "_probs"]).max() < 1e-4 and np.abs(vals[:, 0] - z[tag + "_values"]).max() < 1e-4
+    for a, b in zip(net.get_policy_param(), arrs):
+        assert np.array_equal(a, b)
+    # MCTS.get_move_probs vs the reference's visit counts (400 playouts, c_puct 5)
+    g = np.load(os.path.join(GOLDEN, "mcts.npz"))
+    moves, offs = g[tag + "_moves"], g[tag + "_offsets"]
+    for k in range(3):
+        b = Board(width=w, height=w, n_in_row=n)
+        b.init_board()
+        for m in moves[offs[k]:offs[k + 1]]:
+            b.do_move(int(m))
+        mcts = MCTS(net.policy_value_fn, c_puct=5, n_playout=400)
+        acts, pr = mcts.get_move_probs(b, temp=1.0)
+        ref = g[tag + "_visits1"][k]
+        assert list(acts) == np.nonzero(ref >= 0)[0].tolist() == b.availables
+        want = ref[list(acts)] / ref[list(acts)].sum()
+        assert pr.dtype == np.float64 and abs(pr.sum() - 1) < 1e-9
+        assert 0.5 * np.abs(pr - want).sum() <= 0.02
+    # policy_value_fn protocol: ascending legal moves, probabilities of exactly those moves
+    ap, v = net.policy_value_fn(b)
+    ap = list(ap)
+    assert [a for a, _ in ap] == b.availables and -1.0 <= v <= 1.0 and isinstance(v, float)
+    # save_model round trip (torch state_dict, loadable by the reference)
+    out = str(tmp_path / "saved.model")
+    net.save_model(out)
+    net2 = PolicyValueNet(w, w, model_file=out)
+    assert all(np.array_equal(a, b) for a, b in zip(net2.get_policy_param(), arrs))
+
+
+def test_external_evaluator_protocol_matches_oracle():
+    """Any callable honouring policy_value_fn works: the tree must be bit-identical to the
+    oracle's MCTS driven by the same callable."""
+    from alphazero_gomoku_b200 import Board, MCTS
+    from oracle import orc
+
+    def evaluator(board):
+        av = list(board.availables)
+        s = sum(board.states.keys()) + 3 * len(board.states) + board.current_player
+        w = np.array([((m * 7 + s) % 13) + 1 for m in av], dtype=np.float32)
+        return zip(av, w / w.sum()), float(((s * 37) % 21 - 10) / 10.0)
+
+    w, n, P = 6, 4, 120
+    b = Board(width=w, height=w, n_in_row=n)
+    b.init_board()
+    ob = orc.Board(w, w, n)
+    ob.init_board(0)
+    for m in (14, 15, 20, 21):
+        b.do_move(m); ob.do_move(m)
+    acts, pr = MCTS(evaluator, c_puct=5, n_playout=P).get_move_probs(b, temp=1.0)
+
+    # oracle side: the C restatement of the reference loop calling the same evaluator
+    om = orc.MCTS(5, P, orc.EVAL_CALLBACK, callback=_oracle_callback(evaluator, w, n))
+    oacts, ovis, _, _ = om.search(ob)
+    assert list(acts) == list(oacts)
+    from alphazero_gomoku_b200.mcts_alphaZero import softmax
+    want = softmax(np.log(np.asarray(ovis, np.float64) + 1e-10))  # mcts_alphaZero.py:179 at temp 1
+    assert np.array_equal(pr, want)  # identical visit counts -> identical probabilities
+
+
+def _oracle_callback(evaluator, w, n):
+    """Adapts a python evaluator to the oracle's C callback (CBoard*, float* priors, float* value)."""
+    class _B(object):
+        pass
+
+    def cb(cboard, priors, value):
+        c = cboard.contents
+        bb = _B()
+        S = c.width * c.height
+        bb.width, bb.height, bb.n_in_row = c.width, c.height, c.n_in_row
+        bb.states = {m: c.states[m] for m in range(S) if c.states[m] > 0}
+        bb.availables = [c.availables[i] for i in range(c.n_avail)]
+        bb.current_player = c.current_player
+        ap, v = evaluator(bb)
+        for i, (a, p) in enumerate(ap):  # probs[i] belongs to availables[i] (ascending moves)
+            assert a == bb.availables[i]
+            priors[i] = p
+        value[0] = v
+    return cb
+
+
+def test_selfplay_game_and_player_protocol(tmp_path):
+    """Game.start_self_play with the drop-in MCTSPlayer: a legal finished game, winners_z per
+    game.py:396-399, states equal to replaying the moves, noise-free pi that sums to 1."""
+    from alphazero_gomoku_b200 import Board, Game, MCTSPlayer, PolicyValueNet
+    from oracle import orc
+    path, _ = _save_state_dict(tmp_path, "6_6_4")
+    net = PolicyValueNet(6, 6, model_file=path)
+    player = MCTSPlayer(net.policy_value_fn, c_puct=5, n_playout=60, is_selfplay=1)
+    np.random.seed(0)
+    game = Game(Board(width=6, height=6, n_in_row=4))
+    winner, data = game.start_self_play(player, temp=1.0)
+    data = list(data)
+    assert winner in (1, 2, -1) and 7 <= len(data) <= 36
+    ob = orc.Board(6, 6, 4)
+    ob.init_board(0)
+    moves = list(game.board.states.keys())
+    for (state, pi, z), mv in zip(data, moves):
+        assert np.array_equal(state, ob.current_state())
+        assert abs(pi.sum() - 1) < 1e-9 and pi[mv] > 0 and all(pi[m] == 0 for m in ob.states)
+        assert z == (0.0 if winner == -1 else (1.0 if ob.current_player == winner else -1.0))
+        ob.do_move(mv)
+    assert ob.game_end() == (True, winner)
+    # match play: AlphaZero player vs the pure-MCTS rollout player (train.py:216-276)
+    from alphazero_gomoku_b200 import MCTS_Pure
+    az = MCTSPlayer(net.policy_value_fn, c_puct=5, n_playout=80)
+    pure = MCTS_Pure(c_puct=5, n_playout=200, seed=3)
+    w2 = Game(Board(width=6, height=6, n_in_row=4)).start_play(az, pure, start_player=1, is_shown=0)
+    assert w2 in (1, 2, -1)
+
+
+def test_collect_selfplay_data_batched():
+    """TrainPipeline.collect_selfplay_data(n_games): games played concurrently on the device,
+    8x augmentation, reference buffer item types; then one policy_update."""
+    from alphazero_gomoku_b200 import TrainPipeline
+    conf = {"board_width": 6, "board_height": 6, "n_in_row": 4, "n_playout": 40, "buffer_size": 10000,
+            "batch_size": 64, "epochs": 2}
+    tp = TrainPipeline(conf, seed=1)
+    tp.collect_selfplay_data(n_games=12)
+    assert len(tp.last_games) == 12
+    plies = sum(len(m) for _, _, m in tp.last_games)
+    assert tp.episode_len == plies and len(tp.data_buffer) == 8 * plies
+    s, p, z = tp.data_buffer[0]
+    assert s.shape == (4, 6, 6) and s.dtype == np.float64 and p.shape == (36,) and z in (-1.0, 0.0, 1.0)
+    from oracle import orc
+    for gid, winner, moves in tp.last_games:  # every recorded game is a legal, finished game
+        ob = orc.Board(6, 6, 4)
+        ob.init_board(0)
+        for m in moves[:-1]:
+            ob.do_move(m)
+            assert not ob.game_end()[0]
+        ob.do_move(moves[-1])
+        assert ob.game_end() == (True, winner)
+    before = [a.copy() for a in tp.policy_value_net.get_policy_param()]
+    loss, entropy = tp.policy_update()
+    after = tp.policy_value_net.get_policy_param()
+    assert np.isfinite(loss) and np.isfinite(entropy)
+    assert any(not np.array_equal(a, b) for a, b in zip(before, after))
+    tp.collect_selfplay_data(n_games=4)  # the engine picks up the updated weights
+    assert len(tp.last_games) == 4
