@@ -40,15 +40,15 @@ constexpr int NSTAGE = 4, STAGE_BYTES = 16384;
 constexpr int OFF_RING = OFF_W1 + W1_BYTES;
 constexpr int OFF_WH = OFF_RING + NSTAGE * STAGE_BYTES; // 1x1 head weights fp32 [128][8]
 constexpr int OFF_BIAS = OFF_WH + 4096;   // b1[32] b2[64] b3[128] bh[8]
-constexpr int OFF_BAR = OFF_BIAS + 1024;  // full[4] empty[4] mma_done, tmem base
+constexpr int OFF_BAR = OFF_BIAS + 1024;  // full[4] empty[4] mma_done, tmem base, mma3_done, c3_free
 constexpr int SMEM_BYTES = OFF_BAR + 128;
 constexpr int W2_STAGE = 8192;            // one tap: [pass][chunk 4][64][8]
 constexpr int W3_STAGE = 16384;           // half a tap: [pass][chunk 4][128][8]
 constexpr int N_STAGES_PER_GROUP = 9 + 18;
 constexpr size_t WIMG_BYTES = (size_t)W1_BYTES + 9 * W2_STAGE + 18 * W3_STAGE;
 constexpr int TM_C1 = 0, TM_C2 = 64, TM_C3 = 256; // TMEM column bases of the three accumulators
-constexpr int THREADS = 320;              // 8 epilogue warps, 1 MMA warp, 1 copy warp
-constexpr int SYNC_THREADS = 288;         // everyone but the copy warp
+constexpr int THREADS = 576;              // 8 front epilogue warps, MMA warp, copy warp, 8 back epilogue warps
+constexpr int SYNC_THREADS = 288;         // front warps + MMA warp (phase barrier)
 } // namespace tc
 
 struct TcGeom {
@@ -171,6 +171,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
     const long long n_groups = (B + g.NB - 1) / g.NB;
     const uint32_t sbase = tc_smem_u32(smem);
     const uint32_t bar_full = sbase + OFF_BAR, bar_empty = sbase + OFF_BAR + 32, bar_mma = sbase + OFF_BAR + 64;
+    const uint32_t bar_mma3 = sbase + OFF_BAR + 104, bar_c3free = sbase + OFF_BAR + 112;
     volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(smem + OFF_BAR + 96);
 
     // ---- one-time setup ----------------------------------------------------------------------
@@ -185,6 +186,8 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             tc_mbar_init(bar_empty + 8 * s, 1);
         }
         tc_mbar_init(bar_mma, 1);
+        tc_mbar_init(bar_mma3, 1);
+        tc_mbar_init(bar_c3free, 8); // one arrival per back-end warp
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -215,183 +218,26 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                 }
             }
         }
-    } else {
-        // ---- per-thread constants --------------------------------------------------------------
-        // epilogue thread <-> output row r = tile * 128 + lane-of-tile; TMEM lane = r % 128
-        const int tile = warp >> 2;              // warps 0-3 -> tile 0, 4-7 -> tile 1 (warp 8: unused)
-        const int r = tid;                        // rows 0..255 for warps 0-7
+    } else if (warp >= 10) {
+        // ---- back end (8 warps): conv3 epilogue + both 1x1 head convs, overlapped with the next
+        // group's staging / conv1 / conv2.  TMEM lane quarter of a warp is warp % 4.
+        const int tile = (warp - 10) >> 2, q = warp & 3;
+        const int r = tile * 128 + q * 32 + lane;
         const int bq = r / g.BS, rr = r % g.BS;
         const int ci = rr / g.P, cj = rr % g.P;
-        const bool geo_ok = warp < 8 && bq < g.NB && ci < g.W && cj < g.W;
+        const bool geo_ok = bq < g.NB && ci < g.W && cj < g.W;
         const int cell = ci * g.W + cj;
-        const uint32_t t_lane = ((uint32_t)((warp & 3) * 32)) << 16;
-        const float *s_b1 = reinterpret_cast<const float *>(smem + OFF_BIAS);
-        const float *s_b2 = s_b1 + C1, *s_b3 = s_b2 + C2, *s_bh = s_b3 + C3;
+        const uint32_t t_lane = ((uint32_t)(q * 32)) << 16;
+        const float *s_b3 = reinterpret_cast<const float *>(smem + OFF_BIAS) + C1 + C2, *s_bh = s_b3 + C3;
         const float *s_wh = reinterpret_cast<const float *>(smem + OFF_WH);
-        const uint32_t row_off = (uint32_t)(LEAD + r) * 16u;
-        uint32_t mma_phase = 0, it = 0;
-        const uint32_t leader = tc_elect(); // one lane per warp; used by the MMA warp only
-        int shift[9];
-#pragma unroll
-        for (int t = 0; t < 9; ++t) shift[t] = (t / 3 - 1) * g.P + (t % 3 - 1);
-        // descriptor bases; a row shift / chunk / slot offset is an add on the 16-byte address field
-        const uint64_t dA0 = tc_desc(sbase + OFF_A0 + LEAD * 16, CH), dW1 = tc_desc(sbase + OFF_W1, 512);
-        const uint64_t dAct1 = tc_desc(sbase + OFF_ACT1 + LEAD * 16, CH), dAct2 = tc_desc(sbase + OFF_ACT2 + LEAD * 16, CH);
-        const uint64_t dRing2 = tc_desc(sbase + OFF_RING, 1024), dRing3 = tc_desc(sbase + OFF_RING, 2048);
-
-        int tl_i = 0;
-#define TC_MARK()                                                                  \
-    do {                                                                           \
-        if (timeline && blockIdx.x == 0 && tid == 0 && tl_i < 512) timeline[tl_i++] = clock64(); \
-    } while (0)
+        uint32_t ph3 = 0;
         for (long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
             const long long board = grp * g.NB + bq;
             const bool valid = geo_ok && board < B;
-            TC_MARK(); // 0: group start
-
-            // ---- phase 0: input planes -> A0 chunk 0 (fp16 hi in channels 0-3, lo in 4-7) -------
-            if (warp < 8) {
-                uint4 v = make_uint4(0, 0, 0, 0);
-                if (valid) {
-                    // channels 0-3 = hi(plane), 4-7 = lo(plane): exact for {0,1} boards, fp32-grade
-                    // for the arbitrary float states policy_value(state_batch) may be given
-                    const float *pp = planes + board * 4 * g.S + cell;
-                    const float x0 = pp[0], x1 = pp[g.S], x2 = pp[2 * g.S], x3 = pp[3 * g.S];
-                    const __half2 a = __floats2half2_rn(x0, x1), b = __floats2half2_rn(x2, x3);
-                    const float2 fa = __half22float2(a), fb = __half22float2(b);
-                    const __half2 la = __floats2half2_rn(x0 - fa.x, x1 - fa.y), lb = __floats2half2_rn(x2 - fb.x, x3 - fb.y);
-                    v.x = *reinterpret_cast<const uint32_t *>(&a);
-                    v.y = *reinterpret_cast<const uint32_t *>(&b);
-                    v.z = *reinterpret_cast<const uint32_t *>(&la);
-                    v.w = *reinterpret_cast<const uint32_t *>(&lb);
-                }
-                *reinterpret_cast<uint4 *>(smem + OFF_A0 + row_off) = v;
-            }
-            tc_fence_async_smem();
-            tc_bar_sync();
-            TC_MARK(); // 1: input planes staged
-
-            // ---- phase 1: conv1 ------------------------------------------------------------------
-            if (warp == 8) {
-                tc_fence_after();
-#pragma unroll
-                for (int j = 0; j < 2; ++j)
-#pragma unroll
-                    for (int t = 0; t < 9; ++t)
-#pragma unroll
-                        for (int p = 0; p < 2; ++p)
-                            tc_umma_f16(leader, tmem + TM_C1 + j * C1, dA0 + (int64_t)(j * 128 + shift[t]),
-                                        dW1 + (uint32_t)((p * 9 + t) * 64), tc_idesc(C1), (t | p) != 0);
-                tc_umma_commit(leader, bar_mma);
-            } else {
-                tc_mbar_wait(bar_mma, mma_phase);
-                TC_MARK(); // 2: conv1 MMAs done
-                tc_fence_after();
-                uint32_t v[32];
-                tc_tmem_ld32(tmem + t_lane + TM_C1 + tile * C1, v);
-                float f[32];
-#pragma unroll
-                for (int c = 0; c < 32; ++c) f[c] = valid ? fmaxf(fmaf(__uint_as_float(v[c]), inv_s1, s_b1[c]), 0.f) : 0.f;
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    uint4 hi, lo;
-                    tc_split8(f + 8 * c, hi, lo);
-                    *reinterpret_cast<uint4 *>(smem + OFF_ACT1 + c * CH + row_off) = hi;
-                    *reinterpret_cast<uint4 *>(smem + OFF_ACT1 + (4 + c) * CH + row_off) = lo;
-                }
-                if (dbg && valid) {
-                    float *d = dbg + ((size_t)board * g.S + cell) * C1;
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) d[c] = f[c];
-                }
-                tc_fence_async_smem();
-                tc_fence_before();
-            }
-            mma_phase ^= 1u;
-            tc_bar_sync();
-            TC_MARK(); // 3: conv1 epilogue done
-
-            // ---- phase 2: conv2 (one ring stage per tap) -----------------------------------------
-            if (warp == 8) {
-                tc_fence_after();
-                for (int t = 0; t < 9; ++t, ++it) {
-                    const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
-                    tc_mbar_wait(bar_full + 8 * slot, ph);
-                    tc_fence_after();
-                    const uint64_t da = dAct1 + (int64_t)shift[t];
-                    const uint64_t db = dRing2 + slot * (STAGE_BYTES / 16);
-#pragma unroll
-                    for (int j = 0; j < 2; ++j)
-#pragma unroll
-                        for (int ks = 0; ks < 2; ++ks)
-#pragma unroll
-                            for (int p = 0; p < 3; ++p) {
-                                const int ap = (p == 1), bp = (p == 2);
-                                tc_umma_f16(leader, tmem + TM_C2 + j * C2, da + (uint32_t)(((ap * 4 + 2 * ks) * CH) / 16 + j * 128),
-                                            db + (uint32_t)(bp * 256 + ks * 128), tc_idesc(C2), (t | ks | p) != 0);
-                            }
-                    tc_umma_commit(leader, bar_empty + 8 * slot);
-                }
-                tc_umma_commit(leader, bar_mma);
-            } else {
-                tc_mbar_wait(bar_mma, mma_phase);
-                TC_MARK(); // 4: conv2 MMAs done
-                tc_fence_after();
-#pragma unroll
-                for (int half = 0; half < 2; ++half) {
-                    uint32_t v[32];
-                    tc_tmem_ld32(tmem + t_lane + TM_C2 + tile * C2 + half * 32, v);
-                    float f[32];
-#pragma unroll
-                    for (int c = 0; c < 32; ++c)
-                        f[c] = valid ? fmaxf(fmaf(__uint_as_float(v[c]), inv_s2, s_b2[half * 32 + c]), 0.f) : 0.f;
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        uint4 hi, lo;
-                        tc_split8(f + 8 * c, hi, lo);
-                        *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (half * 4 + c) * CH + row_off) = hi;
-                        *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (8 + half * 4 + c) * CH + row_off) = lo;
-                    }
-                    if (dbg && valid) {
-                        float *d = dbg + (size_t)maxB * g.S * C1 + ((size_t)board * g.S + cell) * C2 + half * 32;
-#pragma unroll
-                        for (int c = 0; c < 32; ++c) d[c] = f[c];
-                    }
-                }
-                tc_fence_async_smem();
-                tc_fence_before();
-            }
-            mma_phase ^= 1u;
-            tc_bar_sync();
-            TC_MARK(); // 5: conv2 epilogue done
-
-            // ---- phase 3: conv3 (two ring stages per tap: input channels 0-31, 32-63) -----------
-            if (warp == 8) {
-                tc_fence_after();
-                for (int s = 0; s < 18; ++s, ++it) {
-                    const int t = s >> 1, h = s & 1;
-                    const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
-                    tc_mbar_wait(bar_full + 8 * slot, ph);
-                    tc_fence_after();
-                    const uint64_t da = dAct2 + (int64_t)(shift[t] + h * ((4 * CH) / 16));
-                    const uint64_t db = dRing3 + slot * (STAGE_BYTES / 16);
-#pragma unroll
-                    for (int j = 0; j < 2; ++j)
-#pragma unroll
-                        for (int ks = 0; ks < 2; ++ks)
-#pragma unroll
-                            for (int p = 0; p < 3; ++p) {
-                                const int ap = (p == 1), bp = (p == 2);
-                                tc_umma_f16(leader, tmem + TM_C3 + j * C3, da + (uint32_t)(((ap * 8 + 2 * ks) * CH) / 16 + j * 128),
-                                            db + (uint32_t)(bp * 512 + ks * 256), tc_idesc(C3), (s | ks | p) != 0);
-                            }
-                    tc_umma_commit(leader, bar_empty + 8 * slot);
-                }
-                tc_umma_commit(leader, bar_mma);
-            } else {
-                tc_mbar_wait(bar_mma, mma_phase);
-                TC_MARK(); // 6: conv3 MMAs done
-                tc_fence_after();
+            tc_mbar_wait(bar_mma3, ph3);
+            ph3 ^= 1u;
+            tc_fence_after();
+            {
                 float hacc[6];
 #pragma unroll
                 for (int q = 0; q < 6; ++q) hacc[q] = s_bh[q];
@@ -423,11 +269,223 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
 #pragma unroll
                     for (int q = 0; q < 6; ++q) o[(size_t)q * g.S] = fmaxf(hacc[q], 0.f);
                 }
-                tc_fence_before();
             }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_c3free) : "memory");
+        }
+    } else {
+        // ---- front end (warps 0-7: staging, conv1 / conv2 epilogues) and the MMA warp (8) ----------
+        // Software pipeline over the groups of this CTA: while conv3 of group g runs on the tensor
+        // pipe, the front warps stage group g+1 and run its conv1 epilogue (conv1(g+1) is issued in
+        // the middle of conv3(g)'s MMA stream), and the back-end warps drain conv3(g-1).
+        const int tile = warp >> 2;               // warps 0-3 -> M-tile 0, 4-7 -> M-tile 1
+        const int r = tid;                        // output row of an epilogue thread; TMEM lane = r % 128
+        const int bq = r / g.BS, rr = r % g.BS;
+        const int ci = rr / g.P, cj = rr % g.P;
+        const bool geo_ok = warp < 8 && bq < g.NB && ci < g.W && cj < g.W;
+        const int cell = ci * g.W + cj;
+        const uint32_t t_lane = ((uint32_t)((warp & 3) * 32)) << 16;
+        const float *s_b1 = reinterpret_cast<const float *>(smem + OFF_BIAS);
+        const float *s_b2 = s_b1 + C1;
+        const uint32_t row_off = (uint32_t)(LEAD + r) * 16u;
+        uint32_t mma_phase = 0, it = 0, c3_phase = 0;
+        bool first_group = true;
+        const uint32_t leader = tc_elect(); // one lane per warp; used by the MMA warp only
+        int shift[9];
+#pragma unroll
+        for (int t = 0; t < 9; ++t) shift[t] = (t / 3 - 1) * g.P + (t % 3 - 1);
+        // descriptor bases; a row shift / chunk / slot offset is an add on the 16-byte address field
+        const uint64_t dA0 = tc_desc(sbase + OFF_A0 + LEAD * 16, CH), dW1 = tc_desc(sbase + OFF_W1, 512);
+        const uint64_t dAct1 = tc_desc(sbase + OFF_ACT1 + LEAD * 16, CH), dAct2 = tc_desc(sbase + OFF_ACT2 + LEAD * 16, CH);
+        const uint64_t dRing2 = tc_desc(sbase + OFF_RING, 1024), dRing3 = tc_desc(sbase + OFF_RING, 2048);
+        int tl_i = 0;
+#define TC_MARK()                                                                  \
+    do {                                                                           \
+        if (timeline && blockIdx.x == 0 && tid == 0 && tl_i < 512) timeline[tl_i++] = clock64(); \
+    } while (0)
+
+        // input planes -> A0 chunk 0 (fp16 hi in channels 0-3, lo in 4-7); front warps
+        auto stage_in = [&](long long board, bool valid) {
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (valid) {
+                // exact for {0,1} boards, fp32-grade for the arbitrary float states
+                // policy_value(state_batch) may be given
+                const float *pp = planes + board * 4 * g.S + cell;
+                const float x0 = pp[0], x1 = pp[g.S], x2 = pp[2 * g.S], x3 = pp[3 * g.S];
+                const __half2 a = __floats2half2_rn(x0, x1), b = __floats2half2_rn(x2, x3);
+                const float2 fa = __half22float2(a), fb = __half22float2(b);
+                const __half2 la = __floats2half2_rn(x0 - fa.x, x1 - fa.y), lb = __floats2half2_rn(x2 - fb.x, x3 - fb.y);
+                v.x = *reinterpret_cast<const uint32_t *>(&a);
+                v.y = *reinterpret_cast<const uint32_t *>(&b);
+                v.z = *reinterpret_cast<const uint32_t *>(&la);
+                v.w = *reinterpret_cast<const uint32_t *>(&lb);
+            }
+            *reinterpret_cast<uint4 *>(smem + OFF_A0 + row_off) = v;
+            tc_fence_async_smem();
+        };
+        // MMA warp: conv1 of the staged group, completion -> bar_mma
+        auto issue_conv1 = [&]() {
+            tc_fence_after();
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int t = 0; t < 9; ++t)
+#pragma unroll
+                    for (int p = 0; p < 2; ++p)
+                        tc_umma_f16(leader, tmem + TM_C1 + j * C1, dA0 + (int64_t)(j * 128 + shift[t]),
+                                    dW1 + (uint32_t)((p * 9 + t) * 64), tc_idesc(C1), (t | p) != 0);
+            tc_umma_commit(leader, bar_mma);
+        };
+        // front warps: conv1 accumulators -> bias, ReLU, hi/lo split -> act1
+        auto ep1 = [&](long long board, bool valid) {
+            tc_mbar_wait(bar_mma, mma_phase);
             mma_phase ^= 1u;
+            tc_fence_after();
+            uint32_t v[32];
+            tc_tmem_ld32(tmem + t_lane + TM_C1 + tile * C1, v);
+            float f[32];
+#pragma unroll
+            for (int c = 0; c < 32; ++c) f[c] = valid ? fmaxf(fmaf(__uint_as_float(v[c]), inv_s1, s_b1[c]), 0.f) : 0.f;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                uint4 hi, lo;
+                tc_split8(f + 8 * c, hi, lo);
+                *reinterpret_cast<uint4 *>(smem + OFF_ACT1 + c * CH + row_off) = hi;
+                *reinterpret_cast<uint4 *>(smem + OFF_ACT1 + (4 + c) * CH + row_off) = lo;
+            }
+            if (dbg && valid) {
+                float *d = dbg + ((size_t)board * g.S + cell) * C1;
+#pragma unroll
+                for (int c = 0; c < 32; ++c) d[c] = f[c];
+            }
+            tc_fence_async_smem();
+            tc_fence_before();
+        };
+        // MMA warp: conv2, one ring stage per tap, completion -> bar_mma
+        auto issue_conv2 = [&]() {
+            tc_fence_after();
+            for (int t = 0; t < 9; ++t, ++it) {
+                const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
+                tc_mbar_wait(bar_full + 8 * slot, ph);
+                tc_fence_after();
+                const uint64_t da = dAct1 + (int64_t)shift[t];
+                const uint64_t db = dRing2 + slot * (STAGE_BYTES / 16);
+#pragma unroll
+                for (int j = 0; j < 2; ++j)
+#pragma unroll
+                    for (int ks = 0; ks < 2; ++ks)
+#pragma unroll
+                        for (int p = 0; p < 3; ++p) {
+                            const int ap = (p == 1), bp = (p == 2);
+                            tc_umma_f16(leader, tmem + TM_C2 + j * C2, da + (uint32_t)(((ap * 4 + 2 * ks) * CH) / 16 + j * 128),
+                                        db + (uint32_t)(bp * 256 + ks * 128), tc_idesc(C2), (t | ks | p) != 0);
+                        }
+                tc_umma_commit(leader, bar_empty + 8 * slot);
+            }
+            tc_umma_commit(leader, bar_mma);
+        };
+        // front warps: conv2 accumulators -> act2
+        auto ep2 = [&](long long board, bool valid) {
+            tc_mbar_wait(bar_mma, mma_phase);
+            mma_phase ^= 1u;
+            tc_fence_after();
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                uint32_t v[32];
+                tc_tmem_ld32(tmem + t_lane + TM_C2 + tile * C2 + half * 32, v);
+                float f[32];
+#pragma unroll
+                for (int c = 0; c < 32; ++c)
+                    f[c] = valid ? fmaxf(fmaf(__uint_as_float(v[c]), inv_s2, s_b2[half * 32 + c]), 0.f) : 0.f;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    uint4 hi, lo;
+                    tc_split8(f + 8 * c, hi, lo);
+                    *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (half * 4 + c) * CH + row_off) = hi;
+                    *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (8 + half * 4 + c) * CH + row_off) = lo;
+                }
+                if (dbg && valid) {
+                    float *d = dbg + (size_t)maxB * g.S * C1 + ((size_t)board * g.S + cell) * C2 + half * 32;
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) d[c] = f[c];
+                }
+            }
+            tc_fence_async_smem();
+            tc_fence_before();
+        };
+        // MMA warp: conv3 ring stages [s0, s1): two per tap (input channels 0-31, 32-63)
+        auto issue_conv3 = [&](int s0, int s1) {
+            for (int s = s0; s < s1; ++s, ++it) {
+                const int t = s >> 1, h = s & 1;
+                const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
+                tc_mbar_wait(bar_full + 8 * slot, ph);
+                tc_fence_after();
+                const uint64_t da = dAct2 + (int64_t)(shift[t] + h * ((4 * CH) / 16));
+                const uint64_t db = dRing3 + slot * (STAGE_BYTES / 16);
+#pragma unroll
+                for (int j = 0; j < 2; ++j)
+#pragma unroll
+                    for (int ks = 0; ks < 2; ++ks)
+#pragma unroll
+                        for (int p = 0; p < 3; ++p) {
+                            const int ap = (p == 1), bp = (p == 2);
+                            tc_umma_f16(leader, tmem + TM_C3 + j * C3, da + (uint32_t)(((ap * 8 + 2 * ks) * CH) / 16 + j * 128),
+                                        db + (uint32_t)(bp * 512 + ks * 256), tc_idesc(C3), (s | ks | p) != 0);
+                        }
+                tc_umma_commit(leader, bar_empty + 8 * slot);
+            }
+        };
+
+        // ---- prologue: stage + conv1 + its epilogue for this CTA's first group -------------------
+        long long grp = blockIdx.x;
+        if (grp < n_groups) {
+            const long long board = grp * g.NB + bq;
+            const bool valid = geo_ok && board < B;
+            if (warp < 8) stage_in(board, valid);
             tc_bar_sync();
-            TC_MARK(); // 7: conv3 epilogue + heads done
+            if (warp == 8) issue_conv1();
+            else ep1(board, valid);
+            tc_bar_sync();
+        }
+        for (; grp < n_groups; grp += gridDim.x) {
+            const long long board = grp * g.NB + bq;
+            const bool valid = geo_ok && board < B;
+            const long long nxt = grp + gridDim.x;
+            const bool has_next = nxt < n_groups;
+            const long long nboard = nxt * g.NB + bq;
+            const bool nvalid = geo_ok && has_next && nboard < B;
+            TC_MARK(); // 0: act1 of this group ready
+            if (warp == 8) {
+                issue_conv2();
+                tc_bar_sync(); // A: act2 written
+                if (!first_group) { // the back end must have drained the previous conv3 accumulators
+                    tc_mbar_wait(bar_c3free, c3_phase);
+                    c3_phase ^= 1u;
+                }
+                first_group = false;
+                tc_fence_after();
+                issue_conv3(0, 4);
+                if (has_next) {
+                    tc_bar_sync(); // B: next group's planes staged
+                    issue_conv1();
+                }
+                issue_conv3(4, 18);
+                tc_umma_commit(leader, bar_mma3);
+                if (has_next) tc_bar_sync(); // C: next group's act1 written
+            } else {
+                ep2(board, valid);
+                TC_MARK(); // 1: conv2 done + epilogue
+                tc_bar_sync(); // A
+                if (has_next) {
+                    stage_in(nboard, nvalid);
+                    tc_bar_sync(); // B
+                    TC_MARK(); // 2: next group staged
+                    ep1(nboard, nvalid);
+                    TC_MARK(); // 3: next group's conv1 done + epilogue
+                    tc_bar_sync(); // C
+                }
+            }
         }
 #undef TC_MARK
     }
@@ -681,7 +739,7 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
     const NetWeights &w = e->wts;
     const long long groups = (maxB + g.NB - 1) / g.NB;
     const unsigned grid = (unsigned)(groups < e->n_sm ? groups : e->n_sm);
-    // GZ_TC_TIMELINE=<file>: CTA 0 records clock64() at its phase boundaries (8 marks per group,
+    // GZ_TC_TIMELINE=<file>: CTA 0 records clock64() at its phase boundaries (4 marks per group,
     // see TC_MARK) and the host appends them to <file>; a profiling aid, off by default.
     static const char *tl_path = getenv("GZ_TC_TIMELINE");
     long long *d_tl = nullptr;
@@ -702,7 +760,7 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
         cudaFree(d_tl);
         if (FILE *f = fopen(tl_path, "a")) {
             fprintf(f, "launch B=%lld grid=%u\n", (long long)maxB, grid);
-            for (int i = 0; i < 512 && h[i]; ++i) fprintf(f, "%lld%c", h[i] - h[0], (i % 8 == 7) ? '\n' : ' ');
+            for (int i = 0; i < 512 && h[i]; ++i) fprintf(f, "%lld%c", h[i] - h[0], (i % 4 == 3) ? '\n' : ' ');
             fprintf(f, "\n");
             fclose(f);
         }

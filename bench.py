@@ -170,10 +170,11 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * dt / max(args.steps, 1),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(args, wname, games=threads),
+            "config": workload_config(args, wname, games=args.games),
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
-                             "sample": "each step: %d host threads x 1 ply x %d playouts (oracle/ C port of the "
-                                       "reference's CPU path; the Python reference cannot travel to this box)"
+                             "sample": "bounded sample of the same workload: each step = %d host threads (one game each) x 1 ply "
+                                       "x %d playouts (oracle/ C port of the reference's CPU path; the Python reference "
+                                       "cannot travel to this box)"
                                        % (threads, args.playouts)},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}

@@ -25,15 +25,15 @@ xp = torch.from_numpy(planes).cuda()
 for _ in range(3):
     e.net_forward(xp)
 e.sync()
-names = ["stage_in", "conv1_mma", "ep1", "conv2_mma", "ep2", "conv3_mma", "ep3", "next"]
+names = ["conv2_mma+ep2", "stage_next", "conv1_next+ep1", "wait_conv3_issue"]
 rows = []
 for blk in open(out).read().split("launch")[1:]:
     lines = [l for l in blk.strip().splitlines()[1:] if l.strip()]
-    t = np.array([[int(x) for x in l.split()] for l in lines if len(l.split()) == 8])
+    t = np.array([[int(x) for x in l.split()] for l in lines if len(l.split()) == 4])
     rows.append(t)
 t = rows[-1]
 d = np.diff(t.reshape(-1))
-d = np.append(d, 0).reshape(-1, 8)[:-1]  # drop the last (partial) group
+d = np.append(d, 0).reshape(-1, 4)[:-1]  # drop the last (partial) group
 print("groups", len(t), "cycles/group", (t[-1, 0] - t[0, 0]) / (len(t) - 1))
 for i, n in enumerate(names):
     print("%-10s mean %8.0f  min %8.0f  max %8.0f" % (n, d[1:, i].mean(), d[1:, i].min(), d[1:, i].max()))
