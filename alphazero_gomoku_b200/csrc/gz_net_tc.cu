@@ -31,22 +31,23 @@ constexpr int ROWS = 256;                 // output rows per group (2 M-tiles of
 constexpr int LEAD = 24;                  // zero rows before row 0 (>= P + 1)
 constexpr int RALLOC = 304;               // LEAD + ROWS + 24 trailing rows
 constexpr int CH = RALLOC * 16;           // bytes of one 8-channel chunk plane
-constexpr int OFF_A0 = 0;                 // input planes: chunk 0 = hi(4 planes) | lo(4 planes), chunk 1 = zeros
-constexpr int OFF_ACT1 = OFF_A0 + 2 * CH; // conv1 output: 4 hi planes, 4 lo planes
+constexpr int OFF_A0 = 0;                 // input planes: one chunk plane = hi(4 planes) | lo(4 planes) per row
+constexpr int OFF_ACT1 = OFF_A0 + CH;     // conv1 output: 4 hi planes, 4 lo planes
 constexpr int OFF_ACT2 = OFF_ACT1 + 8 * CH; // conv2 output: 8 hi planes, 8 lo planes
-constexpr int OFF_W1 = OFF_ACT2 + 16 * CH;  // conv1 weights, resident: [pass][tap][chunk 2][32][8]
-constexpr int W1_BYTES = 2 * 9 * 2 * 32 * 16;
+constexpr int OFF_W1 = OFF_ACT2 + 16 * CH;  // conv1 weights, resident: [pass][tap pair 5][chunk 2][32][8]
+constexpr int W1_BYTES = 2 * 5 * 2 * 32 * 16;
 constexpr int NSTAGE = 4, STAGE_BYTES = 16384;
 constexpr int OFF_RING = OFF_W1 + W1_BYTES;
 constexpr int OFF_WH = OFF_RING + NSTAGE * STAGE_BYTES; // 1x1 head weights fp32 [128][8]
 constexpr int OFF_BIAS = OFF_WH + 4096;   // b1[32] b2[64] b3[128] bh[8]
 constexpr int OFF_BAR = OFF_BIAS + 1024;  // full[4] empty[4] mma_done, tmem base, mma3_done, c3_free
 constexpr int SMEM_BYTES = OFF_BAR + 128;
-constexpr int W2_STAGE = 8192;            // one tap: [pass][chunk 4][64][8]
+constexpr int W2_STAGE = 8192;            // one tap: [chunk 4][128 rows: 64 hi | 64 lo][8]
 constexpr int W3_STAGE = 16384;           // half a tap: [pass][chunk 4][128][8]
 constexpr int N_STAGES_PER_GROUP = 9 + 18;
 constexpr size_t WIMG_BYTES = (size_t)W1_BYTES + 9 * W2_STAGE + 18 * W3_STAGE;
-constexpr int TM_C1 = 0, TM_C2 = 64, TM_C3 = 256; // TMEM column bases of the three accumulators
+constexpr int TM_C1 = 0, TM_C2 = 0, TM_C3 = 256;  // TMEM column bases; conv2 (2 x 128 stacked columns) reuses conv1's
+                                                  // columns: conv1's epilogue is over before conv2 of the same group starts
 constexpr int THREADS = 576;              // 8 front epilogue warps, MMA warp, copy warp, 8 back epilogue warps
 constexpr int SYNC_THREADS = 288;         // front warps + MMA warp (phase barrier)
 } // namespace tc
@@ -211,8 +212,10 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                     const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
                     tc_mbar_wait(bar_empty + 8 * slot, ph ^ 1u);
                     const uint32_t bytes = s < 9 ? W2_STAGE : W3_STAGE;
+                    // conv3 stages are consumed h-major: 9 taps of input channels 0-31, then 32-63
                     const size_t off = (size_t)W1_BYTES + (s < 9 ? (size_t)s * W2_STAGE
-                                                                 : (size_t)9 * W2_STAGE + (size_t)(s - 9) * W3_STAGE);
+                                                                 : (size_t)9 * W2_STAGE +
+                                                                       (size_t)(((s - 9) % 9) * 2 + (s - 9) / 9) * W3_STAGE);
                     tc_mbar_expect_tx(bar_full + 8 * slot, bytes);
                     tc_bulk_g2s(sbase + OFF_RING + slot * STAGE_BYTES, wimg + off, bytes, bar_full + 8 * slot);
                 }
@@ -296,9 +299,9 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
 #pragma unroll
         for (int t = 0; t < 9; ++t) shift[t] = (t / 3 - 1) * g.P + (t % 3 - 1);
         // descriptor bases; a row shift / chunk / slot offset is an add on the 16-byte address field
-        const uint64_t dA0 = tc_desc(sbase + OFF_A0 + LEAD * 16, CH), dW1 = tc_desc(sbase + OFF_W1, 512);
+        const uint64_t dW1 = tc_desc(sbase + OFF_W1, 512);
         const uint64_t dAct1 = tc_desc(sbase + OFF_ACT1 + LEAD * 16, CH), dAct2 = tc_desc(sbase + OFF_ACT2 + LEAD * 16, CH);
-        const uint64_t dRing2 = tc_desc(sbase + OFF_RING, 1024), dRing3 = tc_desc(sbase + OFF_RING, 2048);
+        const uint64_t dRing2 = tc_desc(sbase + OFF_RING, 2048), dRing3 = tc_desc(sbase + OFF_RING, 2048);
         int tl_i = 0;
 #define TC_MARK()                                                                  \
     do {                                                                           \
@@ -324,17 +327,24 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             *reinterpret_cast<uint4 *>(smem + OFF_A0 + row_off) = v;
             tc_fence_async_smem();
         };
-        // MMA warp: conv1 of the staged group, completion -> bar_mma
+        // MMA warp: conv1 of the staged group, completion -> bar_mma.  One K = 16 MMA covers two
+        // filter taps: the second 8-element K chunk is the same plane read `LBO` bytes further,
+        // i.e. the descriptor's leading-dimension offset carries the row shift between the taps
+        // (pairs (0,1) (2,3) (4,5) (6,7); tap 8 is paired with zero weights).
         auto issue_conv1 = [&]() {
             tc_fence_after();
 #pragma unroll
             for (int j = 0; j < 2; ++j)
 #pragma unroll
-                for (int t = 0; t < 9; ++t)
+                for (int q = 0; q < 5; ++q) {
+                    const int t0 = 2 * q;
+                    const uint32_t lbo = (q == 4) ? 16u : (uint32_t)(shift[t0 + 1] - shift[t0]) * 16u;
+                    const uint64_t da = tc_desc(sbase + OFF_A0 + (uint32_t)(LEAD + j * 128 + shift[t0]) * 16u, lbo);
 #pragma unroll
                     for (int p = 0; p < 2; ++p)
-                        tc_umma_f16(leader, tmem + TM_C1 + j * C1, dA0 + (int64_t)(j * 128 + shift[t]),
-                                    dW1 + (uint32_t)((p * 9 + t) * 64), tc_idesc(C1), (t | p) != 0);
+                        tc_umma_f16(leader, tmem + TM_C1 + j * C1, da, dW1 + (uint32_t)((p * 5 + q) * 64), tc_idesc(C1),
+                                    (q | p) != 0);
+                }
             tc_umma_commit(leader, bar_mma);
         };
         // front warps: conv1 accumulators -> bias, ReLU, hi/lo split -> act1
@@ -374,50 +384,46 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
 #pragma unroll
                 for (int j = 0; j < 2; ++j)
 #pragma unroll
-                    for (int ks = 0; ks < 2; ++ks)
-#pragma unroll
-                        for (int p = 0; p < 3; ++p) {
-                            const int ap = (p == 1), bp = (p == 2);
-                            tc_umma_f16(leader, tmem + TM_C2 + j * C2, da + (uint32_t)(((ap * 4 + 2 * ks) * CH) / 16 + j * 128),
-                                        db + (uint32_t)(bp * 256 + ks * 128), tc_idesc(C2), (t | ks | p) != 0);
-                        }
+                    for (int ks = 0; ks < 2; ++ks) {
+                        // x_hi * [w_hi | w_lo] in one N = 128 MMA (A read once), then x_lo * w_hi (N = 64)
+                        tc_umma_f16(leader, tmem + TM_C2 + j * 128, da + (uint32_t)(((2 * ks) * CH) / 16 + j * 128),
+                                    db + (uint32_t)(ks * 256), tc_idesc(128), (t | ks) != 0);
+                        tc_umma_f16(leader, tmem + TM_C2 + j * 128, da + (uint32_t)(((4 + 2 * ks) * CH) / 16 + j * 128),
+                                    db + (uint32_t)(ks * 256), tc_idesc(64), 1u);
+                    }
                 tc_umma_commit(leader, bar_empty + 8 * slot);
             }
             tc_umma_commit(leader, bar_mma);
         };
-        // front warps: conv2 accumulators -> act2
-        auto ep2 = [&](long long board, bool valid) {
-            tc_mbar_wait(bar_mma, mma_phase);
-            mma_phase ^= 1u;
-            tc_fence_after();
+        // front warps: conv2 accumulators (hi*hi + lo*hi in columns 0-63, hi*lo in 64-127) -> act2,
+        // one 32-channel half at a time so conv3 can start on channels 0-31
+        auto ep2 = [&](long long board, bool valid, int half) {
+            uint32_t v[32], v2[32];
+            tc_tmem_ld32(tmem + t_lane + TM_C2 + tile * 128 + half * 32, v);
+            tc_tmem_ld32(tmem + t_lane + TM_C2 + tile * 128 + 64 + half * 32, v2);
+            float f[32];
 #pragma unroll
-            for (int half = 0; half < 2; ++half) {
-                uint32_t v[32];
-                tc_tmem_ld32(tmem + t_lane + TM_C2 + tile * C2 + half * 32, v);
-                float f[32];
+            for (int c = 0; c < 32; ++c)
+                f[c] = valid ? fmaxf(fmaf(__uint_as_float(v[c]) + __uint_as_float(v2[c]), inv_s2, s_b2[half * 32 + c]), 0.f) : 0.f;
 #pragma unroll
-                for (int c = 0; c < 32; ++c)
-                    f[c] = valid ? fmaxf(fmaf(__uint_as_float(v[c]), inv_s2, s_b2[half * 32 + c]), 0.f) : 0.f;
+            for (int c = 0; c < 4; ++c) {
+                uint4 hi, lo;
+                tc_split8(f + 8 * c, hi, lo);
+                *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (half * 4 + c) * CH + row_off) = hi;
+                *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (8 + half * 4 + c) * CH + row_off) = lo;
+            }
+            if (dbg && valid) {
+                float *d = dbg + (size_t)maxB * g.S * C1 + ((size_t)board * g.S + cell) * C2 + half * 32;
 #pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    uint4 hi, lo;
-                    tc_split8(f + 8 * c, hi, lo);
-                    *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (half * 4 + c) * CH + row_off) = hi;
-                    *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (8 + half * 4 + c) * CH + row_off) = lo;
-                }
-                if (dbg && valid) {
-                    float *d = dbg + (size_t)maxB * g.S * C1 + ((size_t)board * g.S + cell) * C2 + half * 32;
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) d[c] = f[c];
-                }
+                for (int c = 0; c < 32; ++c) d[c] = f[c];
             }
             tc_fence_async_smem();
             tc_fence_before();
         };
-        // MMA warp: conv3 ring stages [s0, s1): two per tap (input channels 0-31, 32-63)
+        // MMA warp: conv3 ring stages [s0, s1), h-major: 9 taps of input channels 0-31, then of 32-63
         auto issue_conv3 = [&](int s0, int s1) {
             for (int s = s0; s < s1; ++s, ++it) {
-                const int t = s >> 1, h = s & 1;
+                const int t = s % 9, h = s / 9;
                 const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
                 tc_mbar_wait(bar_full + 8 * slot, ph);
                 tc_fence_after();
@@ -458,7 +464,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             TC_MARK(); // 0: act1 of this group ready
             if (warp == 8) {
                 issue_conv2();
-                tc_bar_sync(); // A: act2 written
+                tc_bar_sync(); // A: act2 channels 0-31 written
                 if (!first_group) { // the back end must have drained the previous conv3 accumulators
                     tc_mbar_wait(bar_c3free, c3_phase);
                     c3_phase ^= 1u;
@@ -466,21 +472,24 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                 first_group = false;
                 tc_fence_after();
                 issue_conv3(0, 4);
-                if (has_next) {
-                    tc_bar_sync(); // B: next group's planes staged
-                    issue_conv1();
-                }
+                tc_bar_sync(); // B: act2 channels 32-63 written, next group's planes staged
+                tc_fence_after();
+                if (has_next) issue_conv1();
                 issue_conv3(4, 18);
                 tc_umma_commit(leader, bar_mma3);
                 if (has_next) tc_bar_sync(); // C: next group's act1 written
             } else {
-                ep2(board, valid);
-                TC_MARK(); // 1: conv2 done + epilogue
+                tc_mbar_wait(bar_mma, mma_phase);
+                mma_phase ^= 1u;
+                tc_fence_after();
+                TC_MARK(); // 1: conv2 MMAs done
+                ep2(board, valid, 0);
                 tc_bar_sync(); // A
+                ep2(board, valid, 1);
+                if (has_next) stage_in(nboard, nvalid);
+                tc_bar_sync(); // B
+                TC_MARK(); // 2: conv2 epilogue done, next group staged
                 if (has_next) {
-                    stage_in(nboard, nvalid);
-                    tc_bar_sync(); // B
-                    TC_MARK(); // 2: next group staged
                     ep1(nboard, nvalid);
                     TC_MARK(); // 3: next group's conv1 done + epilogue
                     tc_bar_sync(); // C
@@ -648,25 +657,25 @@ int gz_tc_prepare_weights(gz_engine *e, std::vector<float> h[16])
         memcpy(img.data() + off_hi, &hi, 2);
         memcpy(img.data() + off_lo, &lo, 2);
     };
-    // conv1: [pass][tap][chunk 2][row 32][8]; chunk 1 is zero.  The A operand carries hi(x) in
-    // elements 0-3 and lo(x) in 4-7, so pass 0 = (w_hi, w_hi) gives x_hi*w_hi + x_lo*w_hi and
-    // pass 1 = (w_lo, 0) gives x_hi*w_lo.
+    // conv1: [pass][tap pair q][chunk 2][row 32][8]; chunk 0 = tap 2q, chunk 1 = tap 2q+1 (zero for
+    // q = 4).  The A operand carries hi(x) in elements 0-3 and lo(x) in 4-7 of a chunk, so pass 0 =
+    // (w_hi, w_hi) gives x_hi*w_hi + x_lo*w_hi and pass 1 = (w_lo, 0) gives x_hi*w_lo.
     for (int t = 0; t < 9; ++t)
         for (int n = 0; n < C1; ++n)
             for (int ci = 0; ci < 4; ++ci) {
                 const float v = h[0][((size_t)n * 4 + ci) * 9 + t] * s1;
-                const size_t o = ((size_t)t * 2 * 32 + n) * 16 + ci * 2;
-                put2(o, (size_t)9 * 1024 + o, v);
+                const size_t o = (((size_t)(t / 2) * 2 + (t % 2)) * 32 + n) * 16 + ci * 2;
+                put2(o, (size_t)5 * 1024 + o, v);
                 memcpy(img.data() + o + 8, img.data() + o, 2);
             }
-    // conv2 stage t: [pass][chunk 4][row 64][8]
+    // conv2 stage t: [chunk 4][row 128: w_hi rows 0-63, w_lo rows 64-127][8]
     for (int t = 0; t < 9; ++t)
         for (int n = 0; n < C2; ++n)
             for (int ci = 0; ci < C1; ++ci) {
                 const float v = h[2][((size_t)n * C1 + ci) * 9 + t] * s2;
                 const size_t base = (size_t)W1_BYTES + (size_t)t * W2_STAGE;
-                const size_t o = ((size_t)(ci / 8) * 64 + n) * 16 + (ci % 8) * 2;
-                put2(base + o, base + 4096 + o, v);
+                const size_t o = ((size_t)(ci / 8) * 128 + n) * 16 + (ci % 8) * 2;
+                put2(base + o, base + o + 64 * 16, v);
             }
     // conv3 stage (t, half): [pass][chunk 4][row 128][8]
     for (int t = 0; t < 9; ++t)

@@ -25,7 +25,7 @@ xp = torch.from_numpy(planes).cuda()
 for _ in range(3):
     e.net_forward(xp)
 e.sync()
-names = ["conv2_mma+ep2", "stage_next", "conv1_next+ep1", "wait_conv3_issue"]
+names = ["conv2_mma", "ep2+stage_next", "conv1_next+ep1", "wait_conv3_issue"]
 rows = []
 for blk in open(out).read().split("launch")[1:]:
     lines = [l for l in blk.strip().splitlines()[1:] if l.strip()]
