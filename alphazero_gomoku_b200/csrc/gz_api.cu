@@ -212,7 +212,7 @@ extern "C" void gz_destroy(gz_engine *e)
                     e->sel_probs, e->out_states, e->out_pi, e->out_z, e->out_gid, e->out_ply, e->out_count,
                     e->gout_moves, e->gout_len, e->gout_winner, e->gout_gid, e->gout_count, e->counters,
                     e->roll_results, e->wts.w1, e->wts.w2, e->wts.w3, e->wts.wh, e->wts.wpfc, e->wts.wvfc,
-                    e->wts.bias, e->wts.tc_img, e->tc_head, e->tc_dbg};
+                    e->wts.bias, e->wts.tc_img, e->wts.wpfc4, e->tc_head, e->tc_dbg};
     for (void *p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 16; ++i) if (e->wts.raw[i]) cudaFree(e->wts.raw[i]);
     for (int c = 0; c < GZ_PROF_CLASSES; ++c) for (cudaEvent_t ev : e->prof_ev[c]) cudaEventDestroy(ev);
@@ -574,11 +574,17 @@ extern "C" int gz_debug_net_layers(gz_engine *e, const float *planes, int64_t B,
 }
 
 // ---- search -----------------------------------------------------------------------------------
-static int gz_wave(gz_engine *e)
+// n playouts in every active game.  One wave = select -> net on the gathered leaves -> expand +
+// backup; the expand/backup of wave k and the select of wave k+1 run as one fused kernel.
+static int gz_waves(gz_engine *e, int n)
 {
+    if (n <= 0) return GZ_OK;
     GZ_TRY(gzk_select(e, false));
-    GZ_TRY(gzk_net_forward(e, e->leaf_planes, e->leaf_count, e->G, e->net_probs, e->net_values));
-    GZ_TRY(gzk_expand_backup(e, e->net_probs, e->net_values, true));
+    for (int i = 0; i < n; ++i) {
+        GZ_TRY(gzk_net_forward(e, e->leaf_planes, e->leaf_count, e->G, e->net_probs, e->net_values));
+        if (i + 1 < n) GZ_TRY(gzk_expand_select(e, e->net_probs, e->net_values));
+        else GZ_TRY(gzk_expand_backup(e, e->net_probs, e->net_values, true));
+    }
     return GZ_OK;
 }
 
@@ -588,7 +594,7 @@ extern "C" int gz_search(gz_engine *e, int32_t n_playout)
     if (!e->wts.loaded) { e->err = "gz_set_weights has not been called"; return GZ_E_NOWEIGHTS; }
     if (e->W != e->H) { e->err = "the net needs a square board"; return GZ_E_INVALID; }
     GZ_CUDA(e, cudaSetDevice(e->cfg.device));
-    for (int i = 0; i < n_playout; ++i) GZ_TRY(gz_wave(e));
+    GZ_TRY(gz_waves(e, n_playout));
     return GZ_OK;
 }
 
@@ -742,7 +748,7 @@ extern "C" int gz_selfplay_step(gz_engine *e, int32_t n_plies)
     if (!e->sp_begun) { e->err = "gz_selfplay_begin has not been called"; return GZ_E_INVALID; }
     GZ_CUDA(e, cudaSetDevice(e->cfg.device));
     for (int p = 0; p < n_plies; ++p) {
-        for (int i = 0; i < e->cfg.n_playout; ++i) GZ_TRY(gz_wave(e));
+        GZ_TRY(gz_waves(e, e->cfg.n_playout));
         GZ_TRY(gzk_root_select_move(e, e->sp_temp, 1, e->sel_moves, e->sel_probs, false));
         GZ_TRY(gzk_selfplay_advance(e));
     }

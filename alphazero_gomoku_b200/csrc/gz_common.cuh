@@ -50,13 +50,30 @@ __host__ __device__ __forceinline__ int bb_bit(int move, int width)
 {
     return (move / width) * 16 + (move % width);
 }
+// word select / update written as select chains so a BB always stays in registers (a dynamic
+// index into w[] would push it to local memory)
 __host__ __device__ __forceinline__ bool bb_test(const BB &a, int bit)
 {
-    return (a.w[bit >> 6] >> (bit & 63)) & 1ull;
+    const int i = bit >> 6;
+    const uint64_t w = (i == 0) ? a.w[0] : (i == 1) ? a.w[1] : (i == 2) ? a.w[2] : a.w[3];
+    return (w >> (bit & 63)) & 1ull;
 }
-__host__ __device__ __forceinline__ void bb_set(BB &a, int bit)
+__host__ __device__ __forceinline__ void bb_set_if(BB &a, int bit, bool cond)
 {
-    a.w[bit >> 6] |= 1ull << (bit & 63);
+    const int i = bit >> 6;
+    const uint64_t m = cond ? (1ull << (bit & 63)) : 0ull;
+    a.w[0] |= (i == 0) ? m : 0ull;
+    a.w[1] |= (i == 1) ? m : 0ull;
+    a.w[2] |= (i == 2) ? m : 0ull;
+    a.w[3] |= (i == 3) ? m : 0ull;
+}
+__host__ __device__ __forceinline__ void bb_set(BB &a, int bit) { bb_set_if(a, bit, true); }
+__host__ __device__ __forceinline__ BB bb_pick(const BB &a, const BB &b, bool first)
+{
+    BB r;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) r.w[i] = first ? a.w[i] : b.w[i];
+    return r;
 }
 __device__ __forceinline__ int bb_popc(const BB &a)
 {

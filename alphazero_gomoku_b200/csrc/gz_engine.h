@@ -43,6 +43,7 @@ struct NetWeights {
     float *w3 = nullptr;   // conv3 [tap][ci][c3]
     float *wh = nullptr;   // heads 1x1 [c3][8] (cols 0..3 policy, 4..5 value, 6..7 zero)
     float *wpfc = nullptr; // policy fc transposed [4S][S]
+    float *wpfc4 = nullptr; // same with rows padded to a multiple of 4 floats (tcgen05 path's FC kernel)
     float *wvfc = nullptr; // value fc1 transposed [2S][64]
     float *bias = nullptr; // packed: b1 | b2 | b3 | bh[8] | bp[S] | bv[64] | wv2[64] | bv2[1]
     int off_b1 = 0, off_b2 = 0, off_b3 = 0, off_bh = 0, off_bp = 0, off_bv = 0, off_wv2 = 0, off_bv2 = 0;
@@ -185,6 +186,7 @@ int gzk_boards_query(gz_engine *e, int8_t *d_ended, int8_t *d_winner, int8_t *d_
 int gzk_tree_reset(gz_engine *e);
 int gzk_select(gz_engine *e, bool pure);
 int gzk_expand_backup(gz_engine *e, const float *d_priors, const float *d_values, bool compacted);
+int gzk_expand_select(gz_engine *e, const float *d_priors, const float *d_values);
 int gzk_pure_expand_rollout_backup(gz_engine *e, uint32_t search_id, uint32_t playout_idx);
 int gzk_root_visits(gz_engine *e, int32_t *d_visits, double *d_q, int32_t *d_rootn);
 int gzk_update_with_move(gz_engine *e, const int32_t *d_moves);

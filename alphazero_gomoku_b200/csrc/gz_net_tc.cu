@@ -512,82 +512,137 @@ struct FcWeights {
     const float *wp, *bp, *wv, *bv, *wv2, *bv2;
 };
 
-template <int TB, int NO>
+// Thread tile = 4 outputs x NBT boards.  The FC weights are staged through shared memory in tiles
+// of 16 k-rows (each element is fetched from L2 once per CTA; without the staging every warp of
+// every CTA asks L2 for the same lines at the same moment and the kernel serialises on a few L2
+// slices).  Per 4 k-steps a thread issues 4 LDS.128 (weights of its 4 outputs), 4 LDS.128 (board
+// activations, warp-broadcast) and 64 FMAs.  QT = threads along the output quads (power of two
+// >= ceil(S/4)), 256/QT board groups of 4 boards -> TB = 1024/QT boards per CTA.
+// wp is [4S][S4] with S4 = S rounded up to 4 (16-byte rows); wv is [2S][64].
+constexpr int FC_KT = 16; // k-rows per staged weight tile
+
+template <int QT, int NBT>
+__device__ __forceinline__ void fc_gemm_tile_loop(const float *__restrict__ wg, int K, int ncol /*floats per row*/,
+                                                  const float *hb, int hs, float *s_w /*[2][FC_KT*ncol]*/, int tq,
+                                                  bool active, float (&acc)[NBT][4])
+{
+    const int tid = threadIdx.x;
+    const int tile_f4 = FC_KT * ncol / 4;           // float4s per full tile
+    const int ntiles = (K + FC_KT - 1) / FC_KT;
+    float4 stage[4];
+    auto gload = [&](int t) {
+        const int rows = min(FC_KT, K - t * FC_KT);
+        const float4 *src = reinterpret_cast<const float4 *>(wg + (size_t)t * FC_KT * ncol);
+        const int n = rows * ncol / 4;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int idx = tid + i * 256;
+            stage[i] = (idx < n) ? __ldg(src + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    };
+    auto sstore = [&](int buf) {
+        float4 *dst = reinterpret_cast<float4 *>(s_w + (size_t)buf * FC_KT * ncol);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int idx = tid + i * 256;
+            if (idx < tile_f4) dst[idx] = stage[i];
+        }
+    };
+    gload(0);
+    sstore(0);
+    __syncthreads();
+    for (int t = 0; t < ntiles; ++t) {
+        const int buf = t & 1;
+        if (t + 1 < ntiles) gload(t + 1);
+        if (active) {
+            const float *wt = s_w + (size_t)buf * FC_KT * ncol + tq * 4;
+            const float *hk = hb + t * FC_KT;
+#pragma unroll
+            for (int k4 = 0; k4 < FC_KT; k4 += 4) {
+                float4 wr[4], hv[NBT];
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) wr[kk] = *reinterpret_cast<const float4 *>(wt + (size_t)(k4 + kk) * ncol);
+#pragma unroll
+                for (int b = 0; b < NBT; ++b) hv[b] = *reinterpret_cast<const float4 *>(hk + (size_t)b * hs + k4);
+#pragma unroll
+                for (int b = 0; b < NBT; ++b) {
+                    const float h4[4] = {hv[b].x, hv[b].y, hv[b].z, hv[b].w};
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk) {
+                        acc[b][0] = fmaf(h4[kk], wr[kk].x, acc[b][0]);
+                        acc[b][1] = fmaf(h4[kk], wr[kk].y, acc[b][1]);
+                        acc[b][2] = fmaf(h4[kk], wr[kk].z, acc[b][2]);
+                        acc[b][3] = fmaf(h4[kk], wr[kk].w, acc[b][3]);
+                    }
+                }
+            }
+        }
+        if (t + 1 < ntiles) sstore(buf ^ 1);
+        __syncthreads();
+    }
+}
+
+template <int QT, int NBT>
 __global__ void __launch_bounds__(256)
 heads_fc_kernel(const float *__restrict__ head_in, FcWeights w, float *__restrict__ probs, float *__restrict__ values,
                 const int32_t *__restrict__ count, long long maxB, int S)
 {
-    constexpr int TBQ = TB / 4;
+    constexpr int BG = 256 / QT, TB = BG * NBT;
     extern __shared__ __align__(16) float fsm[];
-    const int hs = (6 * S + 3) & ~3;   // row stride of s_h (16-byte aligned rows)
-    const int ls = S + 1;
+    const int S4 = (S + 3) & ~3;
+    const int hs = ((6 * S + 3) & ~3) + FC_KT; // row stride of s_h: 16-byte aligned, zero tail for the last k tile
+    const int ls = S4 + 4;
     float *s_h = fsm;                   // [TB][hs]
     float *s_l = s_h + (size_t)TB * hs; // [TB][ls] logits
     float *s_v = s_l + (size_t)TB * ls; // [TB][64]
+    float *s_w = s_v + (size_t)TB * 64; // [2][FC_KT * max(S4, 64)] staged weights
     const long long B = count ? (long long)*count : maxB;
     const long long b0 = (long long)blockIdx.x * TB;
     if (b0 >= B) return;
     const int nb = (int)((B - b0) < TB ? (B - b0) : TB);
-    const int tid = threadIdx.x, tx = tid & 63, ty = tid >> 6;
-    for (int i = tid; i < TB * 6 * S; i += 256) {
-        const int b = i / (6 * S), k = i % (6 * S);
-        s_h[(size_t)b * hs + k] = b < nb ? head_in[(b0 + b) * 6 * S + k] : 0.f;
+    const int tid = threadIdx.x, tq = tid % QT, bg = tid / QT;
+    {
+        const int row = 6 * S; // floats per board; boards are contiguous in head_in
+        const float *src = head_in + b0 * row;
+        for (int b = 0; b < TB; ++b) {
+            float *dst = s_h + (size_t)b * hs;
+            for (int k = tid; k < hs; k += 256) dst[k] = (b < nb && k < row) ? src[(size_t)b * row + k] : 0.f;
+        }
     }
     __syncthreads();
-    // policy FC: thread (tx, ty) -> outputs tx + 64*i, boards ty*TBQ .. +TBQ
-    {
-        float acc[NO][TBQ];
+    const float *hb = s_h + (size_t)(bg * NBT) * hs;
+    float acc[NBT][4];
+    // policy FC (K = 4S, a multiple of 4; the last tile may be short: its missing rows are zero weights)
 #pragma unroll
-        for (int i = 0; i < NO; ++i)
+    for (int b = 0; b < NBT; ++b)
 #pragma unroll
-            for (int b = 0; b < TBQ; ++b) acc[i][b] = 0.f;
-        const int K = 4 * S;
-#pragma unroll 4
-        for (int k = 0; k < K; k += 4) {
-            float wr[NO][4];
+        for (int o = 0; o < 4; ++o) acc[b][o] = 0.f;
+    fc_gemm_tile_loop<QT, NBT>(w.wp, 4 * S, S4, hb, hs, s_w, tq, tq * 4 < S4, acc);
 #pragma unroll
-            for (int i = 0; i < NO; ++i) {
-                const int o = tx + 64 * i;
+    for (int o = 0; o < 4; ++o) {
+        const int oo = tq * 4 + o;
+        if (oo < S) {
+            const float bo = w.bp[oo];
 #pragma unroll
-                for (int kk = 0; kk < 4; ++kk) wr[i][kk] = o < S ? __ldg(w.wp + (size_t)(k + kk) * S + o) : 0.f;
-            }
-#pragma unroll
-            for (int b = 0; b < TBQ; ++b) {
-                const float4 hv = *reinterpret_cast<const float4 *>(s_h + (size_t)(ty * TBQ + b) * hs + k);
-#pragma unroll
-                for (int i = 0; i < NO; ++i) {
-                    acc[i][b] = fmaf(hv.x, wr[i][0], acc[i][b]);
-                    acc[i][b] = fmaf(hv.y, wr[i][1], acc[i][b]);
-                    acc[i][b] = fmaf(hv.z, wr[i][2], acc[i][b]);
-                    acc[i][b] = fmaf(hv.w, wr[i][3], acc[i][b]);
-                }
-            }
-        }
-#pragma unroll
-        for (int i = 0; i < NO; ++i) {
-            const int o = tx + 64 * i;
-            if (o < S) {
-                const float bo = w.bp[o];
-#pragma unroll
-                for (int b = 0; b < TBQ; ++b) s_l[(size_t)(ty * TBQ + b) * ls + o] = acc[i][b] + bo;
-            }
+            for (int b = 0; b < NBT; ++b) s_l[(size_t)(bg * NBT + b) * ls + oo] = acc[b][o] + bo;
         }
     }
-    // value FC1 + ReLU: thread (tx, ty) -> hidden unit tx, boards ty*TBQ .. +TBQ
-    {
-        float acc[TBQ];
+    // value FC1 + ReLU: 64 hidden units = 16 quads, K = 2S (zero-padded to the tile by s_h's tail / zero rows)
 #pragma unroll
-        for (int b = 0; b < TBQ; ++b) acc[b] = 0.f;
-        const int K = 2 * S;
-#pragma unroll 8
-        for (int k = 0; k < K; ++k) {
-            const float wk = __ldg(w.wv + (size_t)k * 64 + tx);
+    for (int b = 0; b < NBT; ++b)
 #pragma unroll
-            for (int b = 0; b < TBQ; ++b) acc[b] = fmaf(s_h[(size_t)(ty * TBQ + b) * hs + 4 * S + k], wk, acc[b]);
+        for (int o = 0; o < 4; ++o) acc[b][o] = 0.f;
+    fc_gemm_tile_loop<QT, NBT>(w.wv, 2 * S, 64, hb + 4 * S, hs, s_w, tq, tq < 16, acc);
+    if (tq < 16) {
+        const float4 bo = *reinterpret_cast<const float4 *>(w.bv + tq * 4);
+#pragma unroll
+        for (int b = 0; b < NBT; ++b) {
+            float *o = s_v + (bg * NBT + b) * 64 + tq * 4;
+            o[0] = fmaxf(acc[b][0] + bo.x, 0.f);
+            o[1] = fmaxf(acc[b][1] + bo.y, 0.f);
+            o[2] = fmaxf(acc[b][2] + bo.z, 0.f);
+            o[3] = fmaxf(acc[b][3] + bo.w, 0.f);
         }
-        const float bo = w.bv[tx];
-#pragma unroll
-        for (int b = 0; b < TBQ; ++b) s_v[(ty * TBQ + b) * 64 + tx] = fmaxf(acc[b] + bo, 0.f);
     }
     __syncthreads();
     // softmax (exp(log_softmax), policy_value_net_pytorch.py:51,91) and tanh(FC2): one warp per board
@@ -604,10 +659,10 @@ heads_fc_kernel(const float *__restrict__ head_in, FcWeights w, float *__restric
         for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
         const float inv = 1.f / sum;
         for (int o = lane; o < S; o += 32) probs[(b0 + b) * S + o] = expf(l[o] - mx) * inv;
-        float acc = s_v[b * 64 + lane] * w.wv2[lane] + s_v[b * 64 + lane + 32] * w.wv2[lane + 32];
+        float acc2 = s_v[b * 64 + lane] * w.wv2[lane] + s_v[b * 64 + lane + 32] * w.wv2[lane + 32];
 #pragma unroll
-        for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
-        if (lane == 0) values[b0 + b] = tanhf(acc + w.bv2[0]);
+        for (int off = 16; off > 0; off >>= 1) acc2 += __shfl_xor_sync(0xffffffffu, acc2, off);
+        if (lane == 0) values[b0 + b] = tanhf(acc2 + w.bv2[0]);
     }
 }
 
@@ -688,6 +743,13 @@ int gz_tc_prepare_weights(gz_engine *e, std::vector<float> h[16])
                 put2(base + o, base + 8192 + o, v);
             }
     GZ_TRY(gz_upload(e, &e->wts.tc_img, img));
+    {   // policy FC transposed with rows padded to 4 floats: [4S][S4]
+        const int S = e->S, S4 = (S + 3) & ~3;
+        std::vector<float> t((size_t)4 * S * S4, 0.f);
+        for (int o = 0; o < S; ++o)
+            for (int k = 0; k < 4 * S; ++k) t[(size_t)k * S4 + o] = h[8][(size_t)o * 4 * S + k];
+        GZ_TRY(gz_upload(e, &e->wts.wpfc4, t));
+    }
     e->wts.tc_inv[0] = 1.f / s1; e->wts.tc_inv[1] = 1.f / s2; e->wts.tc_inv[2] = 1.f / s3;
     return GZ_OK;
 }
@@ -712,19 +774,21 @@ static int gz_tc_ensure_buffers(gz_engine *e, int64_t B, bool want_dbg)
     return GZ_OK;
 }
 
-template <int TB, int NO>
+template <int QT, int NBT>
 static int gz_launch_heads_fc(gz_engine *e, const FcWeights &fw, float *d_probs, float *d_values,
                               const int32_t *d_count, int64_t maxB)
 {
-    const int S = e->S;
-    const size_t smem = ((size_t)TB * ((6 * S + 3) & ~3) + (size_t)TB * (S + 1) + (size_t)TB * 64) * sizeof(float);
-    const unsigned bit = 2u << NO;
+    constexpr int TB = (256 / QT) * NBT;
+    const int S = e->S, S4 = (S + 3) & ~3;
+    const size_t smem = ((size_t)TB * (((6 * S + 3) & ~3) + FC_KT) + (size_t)TB * (S4 + 4) + (size_t)TB * 64 +
+                         (size_t)2 * FC_KT * (S4 > 64 ? S4 : 64)) * sizeof(float);
+    const unsigned bit = 2u * QT;
     if (!(e->attr_done & bit)) {
-        GZ_CUDA(e, cudaFuncSetAttribute(heads_fc_kernel<TB, NO>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        GZ_CUDA(e, cudaFuncSetAttribute(heads_fc_kernel<QT, NBT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         e->attr_done |= bit;
     }
-    heads_fc_kernel<TB, NO><<<(unsigned)((maxB + TB - 1) / TB), 256, smem, e->stream>>>(e->tc_head, fw, d_probs, d_values,
-                                                                                       d_count, maxB, S);
+    heads_fc_kernel<QT, NBT><<<(unsigned)((maxB + TB - 1) / TB), 256, smem, e->stream>>>(e->tc_head, fw, d_probs, d_values,
+                                                                                   d_count, maxB, S);
     return GZ_OK;
 }
 
@@ -775,13 +839,14 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
         }
     }
     FcWeights fw;
-    fw.wp = w.wpfc; fw.bp = w.bias + w.off_bp; fw.wv = w.wvfc; fw.bv = w.bias + w.off_bv;
+    fw.wp = w.wpfc4; fw.bp = w.bias + w.off_bp; fw.wv = w.wvfc; fw.bv = w.bias + w.off_bv;
     fw.wv2 = w.bias + w.off_wv2; fw.bv2 = w.bias + w.off_bv2;
     {
         ProfScope ps(e, PC_HEADS_FC);
-        if (e->S <= 64) GZ_TRY((gz_launch_heads_fc<32, 1>(e, fw, d_probs, d_values, d_count, maxB)));
-        else if (e->S <= 128) GZ_TRY((gz_launch_heads_fc<32, 2>(e, fw, d_probs, d_values, d_count, maxB)));
-        else GZ_TRY((gz_launch_heads_fc<16, 4>(e, fw, d_probs, d_values, d_count, maxB)));
+        const int nq = (e->S + 3) / 4;
+        if (nq <= 16) GZ_TRY((gz_launch_heads_fc<16, 2>(e, fw, d_probs, d_values, d_count, maxB)));
+        else if (nq <= 32) GZ_TRY((gz_launch_heads_fc<32, 4>(e, fw, d_probs, d_values, d_count, maxB)));
+        else GZ_TRY((gz_launch_heads_fc<64, 4>(e, fw, d_probs, d_values, d_count, maxB)));
     }
     e->launches += 2;
     GZ_CUDA(e, cudaGetLastError());

@@ -42,102 +42,160 @@ __device__ __forceinline__ void warp_argmax(double &s, int &i)
     }
 }
 
-template <bool PURE>
-__global__ void __launch_bounds__(128) select_kernel(TreeParams p)
+// n-in-a-row test of one colour in one direction (shift 1 / 16 / 17 / 15), see bb_has_line
+__device__ __forceinline__ bool bb_has_line_dir(const BB &b, int n, int s)
 {
-    const int lane = threadIdx.x & 31;
-    const int wib = threadIdx.x >> 5;
-    const int g = blockIdx.x * (blockDim.x >> 5) + wib;
-    __shared__ unsigned int s_levels, s_children, s_playouts;
-    if (threadIdx.x == 0) { s_levels = 0; s_children = 0; s_playouts = 0; }
-    __syncthreads();
-    if (g < p.G) {
-        if (!p.active[g]) {
-            if (lane == 0) { p.leaf_state[g] = 2; p.path_len[g] = 0; }
-        } else {
-            GameMeta m = p.meta[g];
-            BB st[2];
-            st[0] = load_bb(p.boards[g].stones[0]);
-            st[1] = load_bb(p.boards[g].stones[1]);
-            int player = (m.start_player + m.n_stones) & 1;
-            int ns = m.n_stones, last = m.last_move;
-            int node = p.root_node[g];
-            uint32_t Np = p.root_N[g];
-            int depth = 0;
-            unsigned int nchild = 0;
-            const size_t nbase = (size_t)g * p.cap;
-            while (node >= 0) {
-                NodeView v = gz_node_view(p.pool, nbase + node, p.Sp);
-                const double sq = sqrt((double)Np);
-                double best = -1.0e300;
-                int besti = 0x7fffffff;
-                for (int i = lane; i < p.Sp; i += GZ_WARP) {
-                    float pr = v.P[i];
-                    if (pr >= 0.f) {
-                        uint32_t n = v.N[i];
-                        double q = v.Q[i];
-                        double cp = PURE ? ((double)p.c_puct * (1.0 / (double)pr))
-                                         : (double)(p.c_puct * pr);
-                        double s = q + cp * sq / (double)(1u + n);
-                        if (s > best) { best = s; besti = i; }
-                        ++nchild;
-                    }
-                }
-                warp_argmax(best, besti);
-                const int mv = besti;
-                if (lane == 0) p.path[(size_t)g * p.S + depth] = (uint32_t)node * p.Sp + mv;
-                ++depth;
-                bb_set(st[player], bb_bit(mv, p.W));
-                player ^= 1;
-                last = mv;
-                ++ns;
-                Np = v.N[mv];
-                node = v.child[mv];
-                // a terminal child is never expanded, so child stays -1 and we stop here
-            }
-            int win;
-            bool hw;
-            bool end = bb_game_end(st[0], st[1], ns, p.W, p.H, p.n_in_row, &win, &hw);
-            if (lane == 0) {
-                p.path_len[g] = depth;
-                GameMeta lm;
-                lm.n_stones = ns; lm.last_move = last; lm.start_player = m.start_player; lm.flags = 0;
-                p.leaf_meta[g] = lm;
-                store_bb(p.leaf_board[g].stones[0], st[0]);
-                store_bb(p.leaf_board[g].stones[1], st[1]);
-            }
-            if (end) {
-                // mcts_alphaZero.py:140-145: 0 on a tie, else +1/-1 for the side to move
-                if (lane == 0) {
-                    p.leaf_state[g] = 1;
-                    p.leaf_value[g] = (win == -1) ? 0.0 : ((win == player + 1) ? 1.0 : -1.0);
-                }
-            } else {
-                int slot = 0;
-                if (lane == 0) {
-                    slot = atomicAdd(p.leaf_count, 1);
-                    p.leaf_state[g] = 0;
-                    p.leaf_slot[g] = slot;
-                }
-                slot = __shfl_sync(0xffffffffu, slot, 0);
-                if (!PURE)
-                    gz_write_planes(st[player], st[player ^ 1], last, ns, p.W, p.H,
-                                    p.leaf_planes + (size_t)slot * 4 * p.S, lane);
-            }
-            nchild = __reduce_add_sync(0xffffffffu, nchild);
-            if (lane == 0) {
-                atomicAdd(&s_levels, (unsigned)depth);
-                atomicAdd(&s_children, nchild);
-                atomicAdd(&s_playouts, 1u);
+    BB t = b;
+    for (int k = 1; k < n; ++k) t = bb_and(b, bb_shr(t, s));
+    return bb_any(t);
+}
+
+// per-block statistics without a trailing barrier: warps add into shared counters and the last
+// warp to finish flushes them to the device counters
+struct SelStats {
+    unsigned int levels, children, playouts, done;
+};
+__device__ __forceinline__ void gz_stats_finish(SelStats *ss, DevCounters *ctr, int lane, unsigned levels,
+                                                unsigned children, unsigned playouts)
+{
+    if (lane == 0) {
+        if (playouts) {
+            atomicAdd(&ss->levels, levels);
+            atomicAdd(&ss->children, children);
+            atomicAdd(&ss->playouts, playouts);
+        }
+        __threadfence_block();
+        const unsigned nw = blockDim.x >> 5;
+        if (atomicAdd(&ss->done, 1u) == nw - 1u) {
+            __threadfence_block();
+            const unsigned pl = atomicAdd(&ss->playouts, 0u);
+            if (pl) {
+                atomicAdd(&ctr->select_levels, (unsigned long long)atomicAdd(&ss->levels, 0u));
+                atomicAdd(&ctr->select_children, (unsigned long long)atomicAdd(&ss->children, 0u));
+                atomicAdd(&ctr->playouts, (unsigned long long)pl);
             }
         }
     }
-    __syncthreads();
-    if (threadIdx.x == 0 && s_playouts) {
-        atomicAdd(&p.ctr->select_levels, (unsigned long long)s_levels);
-        atomicAdd(&p.ctr->select_children, (unsigned long long)s_children);
-        atomicAdd(&p.ctr->playouts, (unsigned long long)s_playouts);
+}
+
+// K1 for one game (one warp): root -> leaf, leaf position, terminal test, leaf batch slot + planes
+template <bool PURE>
+__device__ __forceinline__ void gz_select_game(const TreeParams &p, int g, int lane, unsigned &levels_out,
+                                               unsigned &children_out, unsigned &playouts_out)
+{
+    levels_out = children_out = playouts_out = 0;
+    if (!p.active[g]) {
+        if (lane == 0) { p.leaf_state[g] = 2; p.path_len[g] = 0; }
+        return;
     }
+    GameMeta m = p.meta[g];
+    BB s0 = load_bb(p.boards[g].stones[0]), s1 = load_bb(p.boards[g].stones[1]);
+    int player = (m.start_player + m.n_stones) & 1;
+    int ns = m.n_stones, last = m.last_move;
+    int node = p.root_node[g];
+    uint32_t Np = p.root_N[g];
+    int depth = 0;
+    unsigned int nchild = 0;
+    const size_t nbase = (size_t)g * p.cap;
+    while (node >= 0) {
+        NodeView v = gz_node_view(p.pool, nbase + node, p.Sp);
+        const double sq = sqrt((double)Np);
+        double best = -1.0e300;
+        int besti = 0x7fffffff, bestc = -1;
+        uint32_t bestn = 0u;
+        for (int i0 = lane; i0 < p.Sp; i0 += 2 * GZ_WARP) {
+            // two child slots per lane per trip, all eight loads in flight before any use
+            const int i1 = i0 + GZ_WARP;
+            const bool two = i1 < p.Sp;
+            const float pr0 = v.P[i0], pr1 = two ? v.P[i1] : -1.f;
+            const uint32_t n0 = v.N[i0], n1 = two ? v.N[i1] : 0u;
+            const double q0 = v.Q[i0], q1 = two ? v.Q[i1] : 0.0;
+            const int c0 = v.child[i0], c1 = two ? v.child[i1] : -1;
+            if (pr0 >= 0.f) {
+                const double cp = PURE ? ((double)p.c_puct * (1.0 / (double)pr0)) : (double)(p.c_puct * pr0);
+                const double s = q0 + cp * sq / (double)(1u + n0);
+                if (s > best) { best = s; besti = i0; bestn = n0; bestc = c0; }
+                ++nchild;
+            }
+            if (pr1 >= 0.f) {
+                const double cp = PURE ? ((double)p.c_puct * (1.0 / (double)pr1)) : (double)(p.c_puct * pr1);
+                const double s = q1 + cp * sq / (double)(1u + n1);
+                if (s > best) { best = s; besti = i1; bestn = n1; bestc = c1; }
+                ++nchild;
+            }
+        }
+        warp_argmax(best, besti);
+        const int mv = besti;
+        const int owner = mv & (GZ_WARP - 1); // lane whose local best is the global best
+        Np = __shfl_sync(0xffffffffu, bestn, owner);
+        const int next = __shfl_sync(0xffffffffu, bestc, owner);
+        if (lane == 0) p.path[(size_t)g * p.S + depth] = (uint32_t)node * p.Sp + mv;
+        ++depth;
+        {
+            const int bit = bb_bit(mv, p.W);
+            bb_set_if(s0, bit, player == 0);
+            bb_set_if(s1, bit, player == 1);
+        }
+        player ^= 1;
+        last = mv;
+        ++ns;
+        node = next; // a terminal child is never expanded, so child stays -1 and we stop here
+    }
+    // game_end at the leaf (game.py:162-169): lanes 0-7 each test one (colour, direction)
+    bool w0 = false, w1 = false;
+    if (ns >= p.n_in_row + 2) {
+        const int d4 = lane & 3;
+        const int dir = (d4 == 0) ? 1 : (d4 == 1) ? 16 : (d4 == 2) ? 17 : 15;
+        bool line = false;
+        if (lane < 8) line = bb_has_line_dir(bb_pick(s0, s1, lane < 4), p.n_in_row, dir);
+        const unsigned b = __ballot_sync(0xffffffffu, line);
+        w0 = (b & 0x0Fu) != 0u;
+        w1 = (b & 0xF0u) != 0u;
+    }
+    const int win = w0 ? 1 : (w1 ? 2 : -1);
+    const bool end = (w0 || w1) || ns >= p.W * p.H;
+    if (lane == 0) {
+        p.path_len[g] = depth;
+        GameMeta lm;
+        lm.n_stones = ns; lm.last_move = last; lm.start_player = m.start_player; lm.flags = 0;
+        p.leaf_meta[g] = lm;
+        store_bb(p.leaf_board[g].stones[0], s0);
+        store_bb(p.leaf_board[g].stones[1], s1);
+    }
+    if (end) {
+        // mcts_alphaZero.py:140-145: 0 on a tie, else +1/-1 for the side to move
+        if (lane == 0) {
+            p.leaf_state[g] = 1;
+            p.leaf_value[g] = (win == -1) ? 0.0 : ((win == player + 1) ? 1.0 : -1.0);
+        }
+    } else {
+        int slot = 0;
+        if (lane == 0) {
+            slot = atomicAdd(p.leaf_count, 1);
+            p.leaf_state[g] = 0;
+            p.leaf_slot[g] = slot;
+        }
+        slot = __shfl_sync(0xffffffffu, slot, 0);
+        if (!PURE)
+            gz_write_planes(bb_pick(s0, s1, player == 0), bb_pick(s1, s0, player == 0), last, ns, p.W, p.H,
+                            p.leaf_planes + (size_t)slot * 4 * p.S, lane);
+    }
+    levels_out = (unsigned)depth;
+    children_out = __reduce_add_sync(0xffffffffu, nchild);
+    playouts_out = 1u;
+}
+
+template <bool PURE>
+__global__ void __launch_bounds__(128, 8) select_kernel(TreeParams p)
+{
+    const int lane = threadIdx.x & 31;
+    const int g = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    __shared__ SelStats ss;
+    if (threadIdx.x == 0) { ss.levels = 0; ss.children = 0; ss.playouts = 0; ss.done = 0; }
+    __syncthreads();
+    unsigned lv = 0, ch = 0, pl = 0;
+    if (g < p.G) gz_select_game<PURE>(p, g, lane, lv, ch, pl);
+    gz_stats_finish(&ss, p.ctr, lane, lv, ch, pl);
 }
 
 // backup along the recorded path (lanes = levels), then the root
@@ -191,14 +249,12 @@ __device__ __forceinline__ void gz_link_node(const TreeParams &p, int g, int d, 
     }
 }
 
-// K2 (AlphaZero): expand with the evaluator's priors (mcts_alphaZero.py:38-45, :137) + backup.
-__global__ void __launch_bounds__(128)
-expand_backup_kernel(TreeParams p, const float *__restrict__ priors, const float *__restrict__ values,
-                     int compacted)
+// K2 (AlphaZero) for one game: expand with the evaluator's priors (mcts_alphaZero.py:38-45, :137)
+// + backup.
+__device__ __forceinline__ void gz_expand_backup_game(const TreeParams &p, int g, int lane,
+                                                      const float *__restrict__ priors,
+                                                      const float *__restrict__ values, int compacted)
 {
-    const int lane = threadIdx.x & 31;
-    const int g = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (g >= p.G) return;
     const int st = p.leaf_state[g];
     if (st == 2) return;
     const int d = p.path_len[g];
@@ -231,6 +287,35 @@ expand_backup_kernel(TreeParams p, const float *__restrict__ priors, const float
         v = p.leaf_value[g];
     }
     gz_backup(p, g, d, v, lane);
+}
+
+__global__ void __launch_bounds__(128)
+expand_backup_kernel(TreeParams p, const float *__restrict__ priors, const float *__restrict__ values,
+                     int compacted)
+{
+    const int lane = threadIdx.x & 31;
+    const int g = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (g >= p.G) return;
+    gz_expand_backup_game(p, g, lane, priors, values, compacted);
+}
+
+// Wave boundary fused: expand + backup of playout k, then select of playout k+1, by the same warp
+// of the same game (the path nodes it just updated are still in cache).
+__global__ void __launch_bounds__(128, 6)
+expand_select_kernel(TreeParams p, const float *__restrict__ priors, const float *__restrict__ values)
+{
+    const int lane = threadIdx.x & 31;
+    const int g = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    __shared__ SelStats ss;
+    if (threadIdx.x == 0) { ss.levels = 0; ss.children = 0; ss.playouts = 0; ss.done = 0; }
+    __syncthreads();
+    unsigned lv = 0, ch = 0, pl = 0;
+    if (g < p.G) {
+        gz_expand_backup_game(p, g, lane, priors, values, 1);
+        __syncwarp(); // the tree writes of this warp are ordered before the reads of the next descent
+        gz_select_game<false>(p, g, lane, lv, ch, pl);
+    }
+    gz_stats_finish(&ss, p.ctr, lane, lv, ch, pl);
 }
 
 __global__ void tree_reset_kernel(TreeParams p)
@@ -361,6 +446,16 @@ int gzk_expand_backup(gz_engine *e, const float *d_priors, const float *d_values
     ProfScope ps(e, PC_EXPAND);
     expand_backup_kernel<<<gz_warp_blocks(e->G, 4), 128, 0, e->stream>>>(gz_tree_params(e), d_priors,
                                                                           d_values, compacted ? 1 : 0);
+    e->launches++;
+    GZ_CUDA(e, cudaGetLastError());
+    return GZ_OK;
+}
+
+int gzk_expand_select(gz_engine *e, const float *d_priors, const float *d_values)
+{
+    GZ_CUDA(e, cudaMemsetAsync(e->leaf_count, 0, sizeof(int32_t), e->stream));
+    ProfScope ps(e, PC_SELECT);
+    expand_select_kernel<<<gz_warp_blocks(e->G, 4), 128, 0, e->stream>>>(gz_tree_params(e), d_priors, d_values);
     e->launches++;
     GZ_CUDA(e, cudaGetLastError());
     return GZ_OK;
