@@ -212,7 +212,7 @@ extern "C" void gz_destroy(gz_engine *e)
                     e->sel_probs, e->out_states, e->out_pi, e->out_z, e->out_gid, e->out_ply, e->out_count,
                     e->gout_moves, e->gout_len, e->gout_winner, e->gout_gid, e->gout_count, e->counters,
                     e->roll_results, e->wts.w1, e->wts.w2, e->wts.w3, e->wts.wh, e->wts.wpfc, e->wts.wvfc,
-                    e->wts.bias, e->wts.tc_img, e->wts.wpfc4, e->tc_head, e->tc_dbg};
+                    e->wts.bias, e->wts.tc_img, e->wts.tc_fcimg, e->tc_head, e->tc_dbg};
     for (void *p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 16; ++i) if (e->wts.raw[i]) cudaFree(e->wts.raw[i]);
     for (int c = 0; c < GZ_PROF_CLASSES; ++c) for (cudaEvent_t ev : e->prof_ev[c]) cudaEventDestroy(ev);
@@ -559,14 +559,14 @@ extern "C" int gz_debug_net_layers(gz_engine *e, const float *planes, int64_t B,
     if (!dpr) { GZ_CUDA(e, cudaMalloc(&tp, N * S * sizeof(float))); dpr = tp; }
     if (!dv) { GZ_CUDA(e, cudaMalloc(&tv, N * sizeof(float))); dv = tv; }
     int rc = gz_tc_ensure_buffers(e, B, true);
-    if (rc == GZ_OK) GZ_CUDA(e, cudaMemsetAsync(e->tc_dbg, 0, N * S * 224 * sizeof(float), e->stream));
+    if (rc == GZ_OK) GZ_CUDA(e, cudaMemsetAsync(e->tc_dbg, 0, N * S * 230 * sizeof(float), e->stream));
     if (rc == GZ_OK) rc = gz_net_forward_tc(e, dp, nullptr, B, dpr, dv, true);
     if (rc == GZ_OK) rc = a.finish();
     if (rc == GZ_OK) {
         if (act1) GZ_CUDA(e, cudaMemcpy(act1, e->tc_dbg, N * S * 32 * 4, cudaMemcpyDefault));
         if (act2) GZ_CUDA(e, cudaMemcpy(act2, e->tc_dbg + N * S * 32, N * S * 64 * 4, cudaMemcpyDefault));
         if (act3) GZ_CUDA(e, cudaMemcpy(act3, e->tc_dbg + N * S * 96, N * S * 128 * 4, cudaMemcpyDefault));
-        if (head) GZ_CUDA(e, cudaMemcpy(head, e->tc_head, N * 6 * S * 4, cudaMemcpyDefault));
+        if (head) GZ_CUDA(e, cudaMemcpy(head, e->tc_dbg + N * S * 224, N * 6 * S * 4, cudaMemcpyDefault));
     }
     if (tp) cudaFree(tp);
     if (tv) cudaFree(tv);

@@ -43,12 +43,12 @@ struct NetWeights {
     float *w3 = nullptr;   // conv3 [tap][ci][c3]
     float *wh = nullptr;   // heads 1x1 [c3][8] (cols 0..3 policy, 4..5 value, 6..7 zero)
     float *wpfc = nullptr; // policy fc transposed [4S][S]
-    float *wpfc4 = nullptr; // same with rows padded to a multiple of 4 floats (tcgen05 path's FC kernel)
+    uint8_t *tc_fcimg = nullptr; // fp16 hi/lo image of both FC-head weight matrices (tcgen05 path)
     float *wvfc = nullptr; // value fc1 transposed [2S][64]
     float *bias = nullptr; // packed: b1 | b2 | b3 | bh[8] | bp[S] | bv[64] | wv2[64] | bv2[1]
     int off_b1 = 0, off_b2 = 0, off_b3 = 0, off_bh = 0, off_bp = 0, off_bv = 0, off_wv2 = 0, off_bv2 = 0;
     uint8_t *tc_img = nullptr; // tcgen05 path: fp16 hi/lo conv weight image (gz_net_tc.cu layout)
-    float tc_inv[3] = {1.f, 1.f, 1.f}; // 1 / power-of-two weight scale of conv1..3
+    float tc_inv[5] = {1.f, 1.f, 1.f, 1.f, 1.f}; // 1 / power-of-two weight scale of conv1..3, policy FC, value FC1
     bool loaded = false;
 };
 
@@ -88,7 +88,7 @@ struct gz_engine {
     NetWeights wts;
     float *act1, *act2, *act3; // NHWC activations for the fp32 path
     int64_t act_cap;           // boards the activation buffers hold
-    float *tc_head;            // tcgen05 path: ReLU(1x1 head convs) [B][6][S]
+    float *tc_head;            // tcgen05 path: ReLU(1x1 head convs), fp16 hi/lo image (see trunk_tc_kernel)
     float *tc_dbg;             // optional per-layer dump for parity tests
     int64_t tc_cap, tc_dbg_cap;
     int n_sm;

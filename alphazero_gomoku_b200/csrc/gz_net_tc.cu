@@ -41,7 +41,9 @@ constexpr int OFF_RING = OFF_W1 + W1_BYTES;
 constexpr int OFF_WH = OFF_RING + NSTAGE * STAGE_BYTES; // 1x1 head weights fp32 [128][8]
 constexpr int OFF_BIAS = OFF_WH + 4096;   // b1[32] b2[64] b3[128] bh[8]
 constexpr int OFF_BAR = OFF_BIAS + 1024;  // full[4] empty[4] mma_done, tmem base, mma3_done, c3_free
-constexpr int SMEM_BYTES = OFF_BAR + 128;
+constexpr int OFF_HST = OFF_BAR + 128;    // head activations of one group, fp16: [board][pass hi|lo][16 J halves]
+constexpr int HST_BYTES = 8192;           // NB * J * 64 bytes <= 5632 for every supported board
+constexpr int SMEM_BYTES = OFF_HST + HST_BYTES;
 constexpr int W2_STAGE = 8192;            // one tap: [chunk 4][128 rows: 64 hi | 64 lo][8]
 constexpr int W3_STAGE = 16384;           // half a tap: [pass][chunk 4][128][8]
 constexpr int N_STAGES_PER_GROUP = 9 + 18;
@@ -54,6 +56,7 @@ constexpr int SYNC_THREADS = 288;         // front warps + MMA warp (phase barri
 
 struct TcGeom {
     int W, S, P, BS, NB; // board side, cells, row pitch W+1, board stride in rows, boards per group
+    int Jp, J;           // FC-head operand: K = 16 steps of the policy section / of policy + value sections
 };
 
 // ---- PTX wrappers -----------------------------------------------------------------------------
@@ -156,12 +159,15 @@ __device__ __forceinline__ void tc_split8(const float *f, uint4 &hi, uint4 &lo)
 // ---- fused trunk ------------------------------------------------------------------------------
 // planes  [B][4][S] fp32 in {0,1};  wimg = conv1 image | 9 conv2 stages | 18 conv3 stages (fp16);
 // wh [128][8] fp32 (cols 0-3 policy conv, 4-5 value conv);  bias = b1 | b2 | b3 | bh[8];
-// head_out [B][6][S] fp32 = ReLU(1x1 convs);  dbg (optional) = act1 [B][S][32] | act2 [B][S][64] |
-// act3 [B][S][128] fp32 for parity tests.
+// head_act = ReLU(1x1 convs) split into fp16 hi/lo and written directly as the A operand of
+// heads_tc_kernel: [tile of 128 boards][K step][pass hi|lo][8-k chunk 2][board 128][8 halves],
+// k = c*S + cell inside the policy section (steps 0..Jp-1) and the value section (steps Jp..J-1).
+// dbg (optional) = act1 [B][S][32] | act2 [B][S][64] | act3 [B][S][128] | head [B][6][S] fp32 for
+// parity tests.
 __global__ void __launch_bounds__(tc::THREADS, 1)
 trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wimg, const float *__restrict__ wh,
                 const float *__restrict__ bias, float inv_s1, float inv_s2, float inv_s3,
-                float *__restrict__ head_out, const int32_t *__restrict__ count, long long maxB, TcGeom g,
+                __half *__restrict__ head_act, const int32_t *__restrict__ count, long long maxB, TcGeom g,
                 float *__restrict__ dbg, long long *__restrict__ timeline)
 {
     using namespace tc;
@@ -181,6 +187,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         reinterpret_cast<uint4 *>(smem + OFF_W1)[i] = reinterpret_cast<const uint4 *>(wimg)[i];
     for (int i = tid; i < C3 * 8; i += THREADS) reinterpret_cast<float *>(smem + OFF_WH)[i] = wh[i];
     for (int i = tid; i < C1 + C2 + C3 + 8; i += THREADS) reinterpret_cast<float *>(smem + OFF_BIAS)[i] = bias[i];
+    for (int i = tid; i < HST_BYTES / 16; i += THREADS) reinterpret_cast<uint4 *>(smem + OFF_HST)[i] = make_uint4(0, 0, 0, 0);
     if (tid == 0) {
         for (int s = 0; s < NSTAGE; ++s) {
             tc_mbar_init(bar_full + 8 * s, 1);
@@ -233,6 +240,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         const uint32_t t_lane = ((uint32_t)(q * 32)) << 16;
         const float *s_b3 = reinterpret_cast<const float *>(smem + OFF_BIAS) + C1 + C2, *s_bh = s_b3 + C3;
         const float *s_wh = reinterpret_cast<const float *>(smem + OFF_WH);
+        __half *s_hst = reinterpret_cast<__half *>(smem + OFF_HST);
         uint32_t ph3 = 0;
         for (long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
             const long long board = grp * g.NB + bq;
@@ -267,15 +275,38 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                         for (int c = 0; c < 32; ++c) d[c] = f[c];
                     }
                 }
-                if (valid) {
-                    float *o = head_out + (size_t)board * 6 * g.S + cell;
+                // stage hi/lo halves of this group's head activations: [board][pass][k], k padded per section
+                if (geo_ok) {
+                    __half *hs = s_hst + (size_t)bq * 32 * g.J;
 #pragma unroll
-                    for (int q = 0; q < 6; ++q) o[(size_t)q * g.S] = fmaxf(hacc[q], 0.f);
+                    for (int q = 0; q < 6; ++q) {
+                        const float x = fmaxf(hacc[q], 0.f);
+                        const int k = (q < 4 ? q * g.S : 16 * g.Jp + (q - 4) * g.S) + cell;
+                        const __half hi = __float2half_rn(x);
+                        hs[k] = hi;
+                        hs[16 * g.J + k] = __float2half_rn(x - __half2float(hi));
+                        if (dbg && valid) dbg[(size_t)maxB * g.S * (C1 + C2 + C3) + ((size_t)board * 6 + q) * g.S + cell] = x;
+                    }
                 }
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_c3free) : "memory");
+            // copy out as 16-byte chunks of heads_tc_kernel's A operand: step j = [pass 2][chunk 2][board 128][8]
+            asm volatile("bar.sync 2, 256;" ::: "memory");
+            {
+                const int per_board = 4 * g.J; // 2 passes x 2 J chunks
+                for (int idx = tid - 320; idx < g.NB * per_board; idx += 256) {
+                    const int b = idx / per_board, rem = idx - b * per_board;
+                    const int p = rem / (2 * g.J), c = rem - p * 2 * g.J;
+                    const long long brd = grp * g.NB + b;
+                    if (brd < B)
+                        *reinterpret_cast<uint4 *>(head_act + (size_t)(brd >> 7) * g.J * 4096 +
+                                                   (size_t)((c >> 1) * 4 + p * 2 + (c & 1)) * 1024 + (size_t)(brd & 127) * 8) =
+                            *reinterpret_cast<const uint4 *>(s_hst + (size_t)idx * 8);
+                }
+            }
+            asm volatile("bar.sync 2, 256;" ::: "memory");
         }
     } else {
         // ---- front end (warps 0-7: staging, conv1 / conv2 epilogues) and the MMA warp (8) ----------
@@ -506,163 +537,168 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
 }
 
 // ---- FC heads ---------------------------------------------------------------------------------
-// head_in [B][6][S] (rows 0-3 policy planes, 4-5 value planes; flatten order k = c*S + cell as in
-// policy_value_net_pytorch.py:50,54).  wp [4S][S], wv [2S][64] are the transposed FC weights.
-struct FcWeights {
-    const float *wp, *bp, *wv, *bv, *wv2, *bv2;
+// Policy FC + softmax and value FC1 + ReLU + FC2 + tanh (policy_value_net_pytorch.py:48-57) as two
+// tcgen05 GEMMs over a tile of 128 boards: D_policy[128 x Np] = A[:, policy section] * Wp^T and
+// D_value[128 x 64] = A[:, value section] * Wv1^T, same hi/lo three-pass scheme as the trunk.  The A
+// operand is the fp16 image the trunk's back end wrote (already in UMMA layout), so a stage is two
+// plain bulk copies: 16 KB of activations (two K = 16 steps, hi and lo) and the matching weight
+// slice [step 2][pass 2][chunk 2][N][8].  Epilogue: one thread per board reads its accumulator row
+// from TMEM three times (max, sum of exp, normalised write) - no shared-memory round trip.
+namespace fct {
+constexpr int THREADS = 192;     // warps 0-3 epilogue (TMEM lane quarters), warp 4 MMA, warp 5 bulk copies
+constexpr int A_STAGE = 16384;   // [step 2][pass 2][chunk 2][128][8] halves
+constexpr int MAX_NS = 8;
+constexpr int OFF_BAR = 0;       // full[8] @0, empty[8] @64, done @128, tmem slot @136
+constexpr int OFF_BIAS = 192;    // bp[256] bv[64] wv2[64] bv2[1]
+constexpr int OFF_RING = 2048;
+constexpr int TM_P = 0, TM_V = 256;
+} // namespace fct
+
+struct FcTc {
+    const uint8_t *wimg;                 // policy stages (128*Np bytes each) then value stages (8192 bytes each)
+    const float *bp, *bv, *wv2, *bv2;
+    float inv_p, inv_v;                  // 1 / weight pre-scale
+    int S, Np, stages_p, stages_v, ns;   // Np = S rounded up to 16; ns = ring depth
 };
 
-// Thread tile = 4 outputs x NBT boards.  The FC weights are staged through shared memory in tiles
-// of 16 k-rows (each element is fetched from L2 once per CTA; without the staging every warp of
-// every CTA asks L2 for the same lines at the same moment and the kernel serialises on a few L2
-// slices).  Per 4 k-steps a thread issues 4 LDS.128 (weights of its 4 outputs), 4 LDS.128 (board
-// activations, warp-broadcast) and 64 FMAs.  QT = threads along the output quads (power of two
-// >= ceil(S/4)), 256/QT board groups of 4 boards -> TB = 1024/QT boards per CTA.
-// wp is [4S][S4] with S4 = S rounded up to 4 (16-byte rows); wv is [2S][64].
-constexpr int FC_KT = 16; // k-rows per staged weight tile
-
-template <int QT, int NBT>
-__device__ __forceinline__ void fc_gemm_tile_loop(const float *__restrict__ wg, int K, int ncol /*floats per row*/,
-                                                  const float *hb, int hs, float *s_w /*[2][FC_KT*ncol]*/, int tq,
-                                                  bool active, float (&acc)[NBT][4])
+__global__ void __launch_bounds__(fct::THREADS, 1)
+heads_tc_kernel(const uint8_t *__restrict__ head_act, FcTc w, float *__restrict__ probs, float *__restrict__ values,
+                const int32_t *__restrict__ count, long long maxB)
 {
-    const int tid = threadIdx.x;
-    const int tile_f4 = FC_KT * ncol / 4;           // float4s per full tile
-    const int ntiles = (K + FC_KT - 1) / FC_KT;
-    float4 stage[4];
-    auto gload = [&](int t) {
-        const int rows = min(FC_KT, K - t * FC_KT);
-        const float4 *src = reinterpret_cast<const float4 *>(wg + (size_t)t * FC_KT * ncol);
-        const int n = rows * ncol / 4;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int idx = tid + i * 256;
-            stage[i] = (idx < n) ? __ldg(src + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+    using namespace fct;
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    const long long B = __shfl_sync(0xffffffffu, count ? (long long)*count : maxB, 0);
+    const long long T = blockIdx.x;
+    if (T * 128 >= B) return;
+    const uint32_t sbase = tc_smem_u32(smem);
+    const uint32_t bar_full = sbase + OFF_BAR, bar_empty = sbase + OFF_BAR + 64, bar_done = sbase + OFF_BAR + 128;
+    volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(smem + OFF_BAR + 136);
+    float *s_bp = reinterpret_cast<float *>(smem + OFF_BIAS), *s_bv = s_bp + 256, *s_wv2 = s_bv + 64, *s_bv2 = s_wv2 + 64;
+    const int S = w.S, Np = w.Np, nst = w.stages_p + w.stages_v;
+    const uint32_t wslot = 128u * (uint32_t)(Np > 64 ? Np : 64), slot_bytes = A_STAGE + wslot;
+
+    for (int i = tid; i < 256; i += THREADS) s_bp[i] = i < S ? w.bp[i] : 0.f;
+    if (tid < 64) { s_bv[tid] = w.bv[tid]; s_wv2[tid] = w.wv2[tid]; }
+    if (tid == 0) {
+        s_bv2[0] = w.bv2[0];
+        for (int s = 0; s < MAX_NS; ++s) {
+            tc_mbar_init(bar_full + 8 * s, 1);
+            tc_mbar_init(bar_empty + 8 * s, 1);
         }
-    };
-    auto sstore = [&](int buf) {
-        float4 *dst = reinterpret_cast<float4 *>(s_w + (size_t)buf * FC_KT * ncol);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int idx = tid + i * 256;
-            if (idx < tile_f4) dst[idx] = stage[i];
-        }
-    };
-    gload(0);
-    sstore(0);
+        tc_mbar_init(bar_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sbase + OFF_BAR + 136),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
     __syncthreads();
-    for (int t = 0; t < ntiles; ++t) {
-        const int buf = t & 1;
-        if (t + 1 < ntiles) gload(t + 1);
-        if (active) {
-            const float *wt = s_w + (size_t)buf * FC_KT * ncol + tq * 4;
-            const float *hk = hb + t * FC_KT;
+    tc_fence_after();
+    const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+
+    if (warp == 5) {
+        if (lane == 0) {
+            const uint8_t *asrc = head_act + (size_t)T * nst * A_STAGE;
+            for (int s = 0; s < nst; ++s) {
+                const uint32_t slot = (uint32_t)s % (uint32_t)w.ns, ph = ((uint32_t)s / (uint32_t)w.ns) & 1u;
+                tc_mbar_wait(bar_empty + 8 * slot, ph ^ 1u);
+                const bool pol = s < w.stages_p;
+                const uint32_t wb = pol ? 128u * (uint32_t)Np : 8192u;
+                const size_t woff = pol ? (size_t)s * 128 * Np : (size_t)w.stages_p * 128 * Np + (size_t)(s - w.stages_p) * 8192;
+                const uint32_t dst = sbase + OFF_RING + slot * slot_bytes;
+                tc_mbar_expect_tx(bar_full + 8 * slot, A_STAGE + wb);
+                tc_bulk_g2s(dst, asrc + (size_t)s * A_STAGE, A_STAGE, bar_full + 8 * slot);
+                tc_bulk_g2s(dst + A_STAGE, w.wimg + woff, wb, bar_full + 8 * slot);
+            }
+        }
+    } else if (warp == 4) {
+        const uint32_t leader = tc_elect();
+        for (int s = 0; s < nst; ++s) {
+            const uint32_t slot = (uint32_t)s % (uint32_t)w.ns, ph = ((uint32_t)s / (uint32_t)w.ns) & 1u;
+            tc_mbar_wait(bar_full + 8 * slot, ph);
+            tc_fence_after();
+            const bool pol = s < w.stages_p;
+            const uint32_t N = pol ? (uint32_t)Np : 64u;
+            const uint32_t d = tmem + (pol ? TM_P : TM_V);
+            const uint32_t idesc = tc_idesc((int)N);
+            const uint32_t a0 = sbase + OFF_RING + slot * slot_bytes, w0 = a0 + A_STAGE;
 #pragma unroll
-            for (int k4 = 0; k4 < FC_KT; k4 += 4) {
-                float4 wr[4], hv[NBT];
+            for (int step = 0; step < 2; ++step) {
+                const uint64_t a_hi = tc_desc(a0 + step * 8192, 2048), a_lo = tc_desc(a0 + step * 8192 + 4096, 2048);
+                const uint64_t w_hi = tc_desc(w0 + step * 64 * N, 16 * N), w_lo = tc_desc(w0 + step * 64 * N + 32 * N, 16 * N);
+                const uint32_t first = (step == 0 && (s == 0 || s == w.stages_p)) ? 0u : 1u;
+                tc_umma_f16(leader, d, a_hi, w_hi, idesc, first);
+                tc_umma_f16(leader, d, a_lo, w_hi, idesc, 1u);
+                tc_umma_f16(leader, d, a_hi, w_lo, idesc, 1u);
+            }
+            tc_umma_commit(leader, bar_empty + 8 * slot);
+        }
+        tc_umma_commit(leader, bar_done);
+    } else {
+        const long long board = T * 128 + tid;
+        const bool valid = board < B;
+        const uint32_t t_lane = ((uint32_t)(warp * 32)) << 16;
+        tc_mbar_wait(bar_done, 0);
+        tc_fence_after();
+        const int nchunk = (S + 31) >> 5;
+        float mx = -3.0e38f;
+        for (int ch = 0; ch < nchunk; ++ch) {
+            uint32_t v[32];
+            tc_tmem_ld32(tmem + t_lane + TM_P + ch * 32, v);
 #pragma unroll
-                for (int kk = 0; kk < 4; ++kk) wr[kk] = *reinterpret_cast<const float4 *>(wt + (size_t)(k4 + kk) * ncol);
+            for (int c = 0; c < 32; ++c)
+                if (ch * 32 + c < S) mx = fmaxf(mx, fmaf(__uint_as_float(v[c]), w.inv_p, s_bp[ch * 32 + c]));
+        }
+        float sum = 0.f;
+        for (int ch = 0; ch < nchunk; ++ch) {
+            uint32_t v[32];
+            tc_tmem_ld32(tmem + t_lane + TM_P + ch * 32, v);
 #pragma unroll
-                for (int b = 0; b < NBT; ++b) hv[b] = *reinterpret_cast<const float4 *>(hk + (size_t)b * hs + k4);
+            for (int c = 0; c < 32; ++c)
+                if (ch * 32 + c < S) sum += expf(fmaf(__uint_as_float(v[c]), w.inv_p, s_bp[ch * 32 + c]) - mx);
+        }
+        const float inv = 1.f / sum;
+        float *prow = probs + board * S;
+        const bool vec = (S & 3) == 0 && (reinterpret_cast<uintptr_t>(probs) & 15) == 0;
+        for (int ch = 0; ch < nchunk; ++ch) {
+            uint32_t v[32];
+            tc_tmem_ld32(tmem + t_lane + TM_P + ch * 32, v);
+            float p[32];
 #pragma unroll
-                for (int b = 0; b < NBT; ++b) {
-                    const float h4[4] = {hv[b].x, hv[b].y, hv[b].z, hv[b].w};
+            for (int c = 0; c < 32; ++c) p[c] = expf(fmaf(__uint_as_float(v[c]), w.inv_p, s_bp[ch * 32 + c]) - mx) * inv;
+            if (valid) {
+                if (vec) {
 #pragma unroll
-                    for (int kk = 0; kk < 4; ++kk) {
-                        acc[b][0] = fmaf(h4[kk], wr[kk].x, acc[b][0]);
-                        acc[b][1] = fmaf(h4[kk], wr[kk].y, acc[b][1]);
-                        acc[b][2] = fmaf(h4[kk], wr[kk].z, acc[b][2]);
-                        acc[b][3] = fmaf(h4[kk], wr[kk].w, acc[b][3]);
-                    }
+                    for (int c = 0; c < 32; c += 4)
+                        if (ch * 32 + c < S) *reinterpret_cast<float4 *>(prow + ch * 32 + c) = make_float4(p[c], p[c + 1], p[c + 2], p[c + 3]);
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 32; ++c)
+                        if (ch * 32 + c < S) prow[ch * 32 + c] = p[c];
                 }
             }
         }
-        if (t + 1 < ntiles) sstore(buf ^ 1);
-        __syncthreads();
-    }
-}
-
-template <int QT, int NBT>
-__global__ void __launch_bounds__(256)
-heads_fc_kernel(const float *__restrict__ head_in, FcWeights w, float *__restrict__ probs, float *__restrict__ values,
-                const int32_t *__restrict__ count, long long maxB, int S)
-{
-    constexpr int BG = 256 / QT, TB = BG * NBT;
-    extern __shared__ __align__(16) float fsm[];
-    const int S4 = (S + 3) & ~3;
-    const int hs = ((6 * S + 3) & ~3) + FC_KT; // row stride of s_h: 16-byte aligned, zero tail for the last k tile
-    const int ls = S4 + 4;
-    float *s_h = fsm;                   // [TB][hs]
-    float *s_l = s_h + (size_t)TB * hs; // [TB][ls] logits
-    float *s_v = s_l + (size_t)TB * ls; // [TB][64]
-    float *s_w = s_v + (size_t)TB * 64; // [2][FC_KT * max(S4, 64)] staged weights
-    const long long B = count ? (long long)*count : maxB;
-    const long long b0 = (long long)blockIdx.x * TB;
-    if (b0 >= B) return;
-    const int nb = (int)((B - b0) < TB ? (B - b0) : TB);
-    const int tid = threadIdx.x, tq = tid % QT, bg = tid / QT;
-    {
-        const int row = 6 * S; // floats per board; boards are contiguous in head_in
-        const float *src = head_in + b0 * row;
-        for (int b = 0; b < TB; ++b) {
-            float *dst = s_h + (size_t)b * hs;
-            for (int k = tid; k < hs; k += 256) dst[k] = (b < nb && k < row) ? src[(size_t)b * row + k] : 0.f;
+        float acc2 = s_bv2[0];
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch) {
+            uint32_t v[32];
+            tc_tmem_ld32(tmem + t_lane + TM_V + ch * 32, v);
+#pragma unroll
+            for (int c = 0; c < 32; ++c)
+                acc2 = fmaf(fmaxf(fmaf(__uint_as_float(v[c]), w.inv_v, s_bv[ch * 32 + c]), 0.f), s_wv2[ch * 32 + c], acc2);
         }
+        if (valid) values[board] = tanhf(acc2);
+        tc_fence_before();
     }
     __syncthreads();
-    const float *hb = s_h + (size_t)(bg * NBT) * hs;
-    float acc[NBT][4];
-    // policy FC (K = 4S, a multiple of 4; the last tile may be short: its missing rows are zero weights)
-#pragma unroll
-    for (int b = 0; b < NBT; ++b)
-#pragma unroll
-        for (int o = 0; o < 4; ++o) acc[b][o] = 0.f;
-    fc_gemm_tile_loop<QT, NBT>(w.wp, 4 * S, S4, hb, hs, s_w, tq, tq * 4 < S4, acc);
-#pragma unroll
-    for (int o = 0; o < 4; ++o) {
-        const int oo = tq * 4 + o;
-        if (oo < S) {
-            const float bo = w.bp[oo];
-#pragma unroll
-            for (int b = 0; b < NBT; ++b) s_l[(size_t)(bg * NBT + b) * ls + oo] = acc[b][o] + bo;
-        }
-    }
-    // value FC1 + ReLU: 64 hidden units = 16 quads, K = 2S (zero-padded to the tile by s_h's tail / zero rows)
-#pragma unroll
-    for (int b = 0; b < NBT; ++b)
-#pragma unroll
-        for (int o = 0; o < 4; ++o) acc[b][o] = 0.f;
-    fc_gemm_tile_loop<QT, NBT>(w.wv, 2 * S, 64, hb + 4 * S, hs, s_w, tq, tq < 16, acc);
-    if (tq < 16) {
-        const float4 bo = *reinterpret_cast<const float4 *>(w.bv + tq * 4);
-#pragma unroll
-        for (int b = 0; b < NBT; ++b) {
-            float *o = s_v + (bg * NBT + b) * 64 + tq * 4;
-            o[0] = fmaxf(acc[b][0] + bo.x, 0.f);
-            o[1] = fmaxf(acc[b][1] + bo.y, 0.f);
-            o[2] = fmaxf(acc[b][2] + bo.z, 0.f);
-            o[3] = fmaxf(acc[b][3] + bo.w, 0.f);
-        }
-    }
-    __syncthreads();
-    // softmax (exp(log_softmax), policy_value_net_pytorch.py:51,91) and tanh(FC2): one warp per board
-    const int warp = tid >> 5, lane = tid & 31;
-    for (int b = warp; b < nb; b += 8) {
-        const float *l = s_l + (size_t)b * ls;
-        float mx = -3.0e38f;
-        for (int o = lane; o < S; o += 32) mx = fmaxf(mx, l[o]);
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-        float sum = 0.f;
-        for (int o = lane; o < S; o += 32) sum += expf(l[o] - mx);
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
-        const float inv = 1.f / sum;
-        for (int o = lane; o < S; o += 32) probs[(b0 + b) * S + o] = expf(l[o] - mx) * inv;
-        float acc2 = s_v[b * 64 + lane] * w.wv2[lane] + s_v[b * 64 + lane + 32] * w.wv2[lane + 32];
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) acc2 += __shfl_xor_sync(0xffffffffu, acc2, off);
-        if (lane == 0) values[b0 + b] = tanhf(acc2 + w.bv2[0]);
+    if (warp == 0) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
     }
 }
 
@@ -678,6 +714,8 @@ static TcGeom gz_tc_geom(const gz_engine *e)
     g.W = e->W; g.S = e->S; g.P = e->W + 1;
     g.BS = e->W * g.P + g.P + 1;
     g.NB = 1 + (tc::ROWS - e->W * g.P) / g.BS;
+    g.Jp = 2 * ((4 * e->S + 31) / 32); // both FC sections are padded to whole stages of K = 32
+    g.J = g.Jp + 2 * ((2 * e->S + 31) / 32);
     return g;
 }
 
@@ -743,12 +781,26 @@ int gz_tc_prepare_weights(gz_engine *e, std::vector<float> h[16])
                 put2(base + o, base + 8192 + o, v);
             }
     GZ_TRY(gz_upload(e, &e->wts.tc_img, img));
-    {   // policy FC transposed with rows padded to 4 floats: [4S][S4]
-        const int S = e->S, S4 = (S + 3) & ~3;
-        std::vector<float> t((size_t)4 * S * S4, 0.f);
-        for (int o = 0; o < S; ++o)
-            for (int k = 0; k < 4 * S; ++k) t[(size_t)k * S4 + o] = h[8][(size_t)o * 4 * S + k];
-        GZ_TRY(gz_upload(e, &e->wts.wpfc4, t));
+    {   // FC image: per K = 16 step [pass hi|lo][8-k chunk 2][N rows][8 halves]; policy steps (N = Np)
+        // first, then value FC1 steps (N = 64).  Rows / k beyond the real matrix stay zero.
+        const int S = e->S, Np = (S + 15) & ~15;
+        const TcGeom g = gz_tc_geom(e);
+        const float sp = gz_tc_scale(h[8]), sv = gz_tc_scale(h[12]);
+        std::vector<uint8_t> fimg((size_t)g.Jp * 64 * Np + (size_t)(g.J - g.Jp) * 64 * 64, 0);
+        auto putf = [&](size_t base, int N, int n, int k, float v) {
+            float back;
+            __half hi, lo;
+            gz_tc_split(v, back, hi, lo);
+            const size_t o = base + (size_t)(k >> 4) * 64 * N + ((size_t)((k >> 3) & 1) * N + n) * 16 + (k & 7) * 2;
+            memcpy(fimg.data() + o, &hi, 2);
+            memcpy(fimg.data() + o + (size_t)32 * N, &lo, 2);
+        };
+        for (int n = 0; n < S; ++n)
+            for (int k = 0; k < 4 * S; ++k) putf(0, Np, n, k, h[8][(size_t)n * 4 * S + k] * sp);
+        for (int n = 0; n < 64; ++n)
+            for (int k = 0; k < 2 * S; ++k) putf((size_t)g.Jp * 64 * Np, 64, n, k, h[12][(size_t)n * 2 * S + k] * sv);
+        GZ_TRY(gz_upload(e, &e->wts.tc_fcimg, fimg));
+        e->wts.tc_inv[3] = 1.f / sp; e->wts.tc_inv[4] = 1.f / sv;
     }
     e->wts.tc_inv[0] = 1.f / s1; e->wts.tc_inv[1] = 1.f / s2; e->wts.tc_inv[2] = 1.f / s3;
     return GZ_OK;
@@ -762,33 +814,19 @@ static int gz_tc_ensure_buffers(gz_engine *e, int64_t B, bool want_dbg)
         e->tc_head = e->tc_dbg = nullptr;
         e->tc_cap = 0;
         e->tc_dbg_cap = 0;
-        GZ_CUDA(e, cudaMalloc(&e->tc_head, (size_t)B * 6 * e->S * sizeof(float)));
+        // fp16 hi/lo head activations in heads_tc_kernel's operand layout; zeroed once so that the
+        // K padding and the rows of a partial last tile are finite
+        const size_t bytes = (size_t)((B + 127) / 128) * gz_tc_geom(e).J * 8192;
+        GZ_CUDA(e, cudaMalloc(&e->tc_head, bytes));
+        GZ_CUDA(e, cudaMemsetAsync(e->tc_head, 0, bytes, e->stream));
         e->tc_cap = B;
     }
     if (want_dbg && B > e->tc_dbg_cap) {
         if (e->tc_dbg) cudaFree(e->tc_dbg);
         e->tc_dbg = nullptr;
-        GZ_CUDA(e, cudaMalloc(&e->tc_dbg, (size_t)B * e->S * (tc::C1 + tc::C2 + tc::C3) * sizeof(float)));
+        GZ_CUDA(e, cudaMalloc(&e->tc_dbg, (size_t)B * e->S * (tc::C1 + tc::C2 + tc::C3 + 6) * sizeof(float)));
         e->tc_dbg_cap = B;
     }
-    return GZ_OK;
-}
-
-template <int QT, int NBT>
-static int gz_launch_heads_fc(gz_engine *e, const FcWeights &fw, float *d_probs, float *d_values,
-                              const int32_t *d_count, int64_t maxB)
-{
-    constexpr int TB = (256 / QT) * NBT;
-    const int S = e->S, S4 = (S + 3) & ~3;
-    const size_t smem = ((size_t)TB * (((6 * S + 3) & ~3) + FC_KT) + (size_t)TB * (S4 + 4) + (size_t)TB * 64 +
-                         (size_t)2 * FC_KT * (S4 > 64 ? S4 : 64)) * sizeof(float);
-    const unsigned bit = 2u * QT;
-    if (!(e->attr_done & bit)) {
-        GZ_CUDA(e, cudaFuncSetAttribute(heads_fc_kernel<QT, NBT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        e->attr_done |= bit;
-    }
-    heads_fc_kernel<QT, NBT><<<(unsigned)((maxB + TB - 1) / TB), 256, smem, e->stream>>>(e->tc_head, fw, d_probs, d_values,
-                                                                                   d_count, maxB, S);
     return GZ_OK;
 }
 
@@ -823,7 +861,8 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
     {
         ProfScope ps(e, PC_TRUNK_TC);
         trunk_tc_kernel<<<grid, THREADS, SMEM_BYTES, e->stream>>>(d_planes, w.tc_img, w.wh, w.bias + w.off_b1,
-                                                                   w.tc_inv[0], w.tc_inv[1], w.tc_inv[2], e->tc_head,
+                                                                   w.tc_inv[0], w.tc_inv[1], w.tc_inv[2],
+                                                                   reinterpret_cast<__half *>(e->tc_head),
                                                                    d_count, maxB, g, want_dbg ? e->tc_dbg : nullptr, d_tl);
     }
     if (d_tl) {
@@ -838,15 +877,23 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
             fclose(f);
         }
     }
-    FcWeights fw;
-    fw.wp = w.wpfc4; fw.bp = w.bias + w.off_bp; fw.wv = w.wvfc; fw.bv = w.bias + w.off_bv;
+    FcTc fw;
+    fw.wimg = w.tc_fcimg; fw.bp = w.bias + w.off_bp; fw.bv = w.bias + w.off_bv;
     fw.wv2 = w.bias + w.off_wv2; fw.bv2 = w.bias + w.off_bv2;
+    fw.inv_p = w.tc_inv[3]; fw.inv_v = w.tc_inv[4];
+    fw.S = e->S; fw.Np = (e->S + 15) & ~15; fw.stages_p = g.Jp / 2; fw.stages_v = (g.J - g.Jp) / 2;
+    const int slot_bytes = fct::A_STAGE + 128 * (fw.Np > 64 ? fw.Np : 64);
+    fw.ns = (200 * 1024 - fct::OFF_RING) / slot_bytes;
+    if (fw.ns > fct::MAX_NS) fw.ns = fct::MAX_NS;
+    if (fw.ns > fw.stages_p + fw.stages_v) fw.ns = fw.stages_p + fw.stages_v;
     {
         ProfScope ps(e, PC_HEADS_FC);
-        const int nq = (e->S + 3) / 4;
-        if (nq <= 16) GZ_TRY((gz_launch_heads_fc<16, 2>(e, fw, d_probs, d_values, d_count, maxB)));
-        else if (nq <= 32) GZ_TRY((gz_launch_heads_fc<32, 4>(e, fw, d_probs, d_values, d_count, maxB)));
-        else GZ_TRY((gz_launch_heads_fc<64, 4>(e, fw, d_probs, d_values, d_count, maxB)));
+        if (!(e->attr_done & 2u)) {
+            GZ_CUDA(e, cudaFuncSetAttribute(heads_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            e->attr_done |= 2u;
+        }
+        heads_tc_kernel<<<(unsigned)((maxB + 127) / 128), fct::THREADS, fct::OFF_RING + (size_t)fw.ns * slot_bytes, e->stream>>>(
+            reinterpret_cast<const uint8_t *>(e->tc_head), fw, d_probs, d_values, d_count, maxB);
     }
     e->launches += 2;
     GZ_CUDA(e, cudaGetLastError());

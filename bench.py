@@ -329,7 +329,7 @@ def run_ours(args):
             "gpu_launches": int(tot_launch),
             "clocks": clocks,
             "roofline": roof,
-            "net": {"impl": ("tcgen05 fused trunk (fp16 hi/lo split, 3 MMA passes, fp32 accumulate in TMEM) + fp32 FC heads"
+            "net": {"impl": ("tcgen05 fused trunk (fp16 hi/lo split, 3 MMA passes, fp32 accumulate in TMEM) + tcgen05 FC heads (same split)"
                              if tc else "fp32 CUDA-core (FFMA) implicit GEMM"), "leaf_evals": int(tot_leaf),
                     "leaf_evals_per_s": tot_leaf / (ms_max * 1e-3),
                     "algorithmic_tflops": ctr["leaf_evals"] * fl["total"] / max(net_ms * 1e-3, 1e-12) / 1e12,
