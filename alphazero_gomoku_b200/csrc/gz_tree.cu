@@ -299,6 +299,248 @@ expand_backup_kernel(TreeParams p, const float *__restrict__ priors, const float
     gz_expand_backup_game(p, g, lane, priors, values, compacted);
 }
 
+// Fused wave boundary for boards of up to 64 cells (NSL = Sp / 32 child slots per lane), written
+// around the number of dependent memory round trips, which is what bounds these kernels:
+//   trip 1  everything addressed by the game index alone (flags, path length, leaf slot, root,
+//           free-list top, both positions, this lane's path entry)
+//   trip 2  everything addressed by trip 1's values: the evaluator's value and priors, the free
+//           node index, this lane's path statistics (N, Q) and the whole root block
+//   then    expand / link / backup from registers, patch the prefetched root block with the one
+//           edge the backup changed, and descend: one trip per level below the root.
+// Same arithmetic, in the same order per node, as gz_expand_backup_game + gz_select_game.
+template <int NSL>
+__device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g, int lane,
+                                                      const float *__restrict__ priors,
+                                                      const float *__restrict__ values, unsigned &levels_out,
+                                                      unsigned &children_out, unsigned &playouts_out)
+{
+    constexpr int SP = 32 * NSL;
+    levels_out = children_out = playouts_out = 0;
+    const size_t nbase = (size_t)g * p.cap;
+    // ---- trip 1
+    const int active = p.active[g];
+    const int st = p.leaf_state[g];
+    const int d = p.path_len[g];
+    const int slot = p.leaf_slot[g];
+    const int top = p.free_top[g];
+    int root = p.root_node[g];
+    uint32_t rootN = p.root_N[g];
+    const double rootQ = p.root_Q[g];
+    const double lval = p.leaf_value[g];
+    const GameMeta m = p.meta[g];
+    BB s0 = load_bb(p.boards[g].stones[0]), s1 = load_bb(p.boards[g].stones[1]);
+    const BB occ = bb_or(load_bb(p.leaf_board[g].stones[0]), load_bb(p.leaf_board[g].stones[1]));
+    const uint32_t e_mine = p.path[(size_t)g * p.S + (lane < p.S ? lane : 0)];
+    // ---- trip 2
+    const bool do_exp = st == 0, do_bk = st != 2;
+    float vnet = 0.f, prr[NSL];
+    int newn = -1;
+    if (do_exp) {
+        vnet = values[slot];
+#pragma unroll
+        for (int j = 0; j < NSL; ++j) {
+            const int i = lane + 32 * j;
+            prr[j] = i < p.S ? priors[(size_t)slot * p.S + i] : 0.f;
+        }
+        if (top > 0) newn = p.free_stack[nbase + top - 1];
+    }
+    const bool has_e = do_bk && lane < d;
+    NodeView ev = gz_node_view(p.pool, nbase + (has_e ? e_mine / SP : 0u), SP);
+    const int cell_e = (int)(e_mine % SP);
+    uint32_t n_e = 0u;
+    double q_e = 0.0;
+    if (has_e) { n_e = ev.N[cell_e]; q_e = ev.Q[cell_e]; }
+    float rP[NSL];
+    uint32_t rN[NSL];
+    double rQ[NSL];
+    int rC[NSL];
+    if (root >= 0) {
+        NodeView rv = gz_node_view(p.pool, nbase + root, SP);
+#pragma unroll
+        for (int j = 0; j < NSL; ++j) {
+            const int i = lane + 32 * j;
+            rP[j] = rv.P[i]; rN[j] = rv.N[i]; rQ[j] = rv.Q[i]; rC[j] = rv.child[i];
+        }
+    }
+    // ---- expand (mcts_alphaZero.py:38-45) and link
+    if (do_exp) {
+        if (newn >= 0) {
+            NodeView nv = gz_node_view(p.pool, nbase + newn, SP);
+            unsigned cnt = 0;
+#pragma unroll
+            for (int j = 0; j < NSL; ++j) {
+                const int i = lane + 32 * j;
+                const bool leg = (i < p.S) && !bb_test(occ, bb_bit(i, p.W));
+                const float pv = leg ? prr[j] : -1.f;
+                nv.P[i] = pv; nv.N[i] = 0u; nv.Q[i] = 0.0; nv.child[i] = -1;
+                cnt += leg;
+                if (d == 0) { rP[j] = pv; rN[j] = 0u; rQ[j] = 0.0; rC[j] = -1; } // the new node is the root
+            }
+            if (d == 0) {
+                root = newn;
+                if (lane == 0) p.root_node[g] = newn;
+            } else if (d <= 32) {
+                if (lane == d - 1) ev.child[cell_e] = newn;
+            } else if (lane == 0) {
+                const uint32_t e = p.path[(size_t)g * p.S + d - 1];
+                gz_node_view(p.pool, nbase + e / SP, SP).child[e % SP] = newn;
+            }
+            cnt = __reduce_add_sync(0xffffffffu, cnt);
+            if (lane == 0) {
+                p.free_top[g] = top - 1;
+                atomicAdd(&p.ctr->expanded_children, (unsigned long long)cnt);
+                atomicAdd(&p.ctr->leaf_evals, 1ull);
+            }
+        } else if (lane == 0) {
+            atomicAdd(&p.ctr->pool_overflows, 1ull);
+        }
+    }
+    // ---- backup (mcts_alphaZero.py:62-79): lanes = levels, then the root
+    if (do_bk) {
+        const double v = do_exp ? (double)vnet : lval;
+        uint32_t n_new = 0u;
+        double q_new = 0.0;
+        if (has_e) {
+            const double val = ((d - (lane + 1)) & 1) ? v : -v; // leaf node gets -v, alternating upwards
+            n_new = n_e + 1u;
+            q_new = q_e + 1.0 * (val - q_e) / (double)n_new;
+            ev.N[cell_e] = n_new;
+            ev.Q[cell_e] = q_new;
+        }
+        for (int k = lane + 32; k < d; k += 32) { // paths deeper than a warp: the plain way
+            const uint32_t e = p.path[(size_t)g * p.S + k];
+            NodeView nv = gz_node_view(p.pool, nbase + e / SP, SP);
+            const int cell = (int)(e % SP);
+            const double val = ((d - (k + 1)) & 1) ? v : -v;
+            const uint32_t n = nv.N[cell] + 1u;
+            nv.N[cell] = n;
+            const double q = nv.Q[cell];
+            nv.Q[cell] = q + 1.0 * (val - q) / (double)n;
+        }
+        {
+            const double val = (d & 1) ? v : -v;
+            rootN += 1u;
+            if (lane == 0) {
+                p.root_N[g] = rootN;
+                p.root_Q[g] = rootQ + 1.0 * (val - rootQ) / (double)rootN;
+            }
+        }
+        if (d >= 1) { // path entry 0 is an edge of the (prefetched) root block: patch it
+            const int c0 = __shfl_sync(0xffffffffu, cell_e, 0);
+            const uint32_t nn = __shfl_sync(0xffffffffu, n_new, 0);
+            const double qq = __shfl_sync(0xffffffffu, q_new, 0);
+#pragma unroll
+            for (int j = 0; j < NSL; ++j)
+                if (lane + 32 * j == c0) {
+                    rN[j] = nn; rQ[j] = qq;
+                    if (d == 1 && newn >= 0) rC[j] = newn;
+                }
+        }
+    }
+    __syncwarp(); // this warp's tree writes are ordered before the reads of the descent below
+    // ---- select (mcts_alphaZero.py:47-60, 118-129)
+    if (!active) {
+        if (lane == 0) { p.leaf_state[g] = 2; p.path_len[g] = 0; }
+        return;
+    }
+    int player = (m.start_player + m.n_stones) & 1;
+    int ns = m.n_stones, last = m.last_move;
+    int node = root;
+    uint32_t Np = rootN;
+    int depth = 0;
+    unsigned int nchild = 0;
+    while (node >= 0) {
+        const double sq = sqrt((double)Np);
+        double best = -1.0e300;
+        int besti = 0x7fffffff, bestc = -1;
+        uint32_t bestn = 0u;
+#pragma unroll
+        for (int j = 0; j < NSL; ++j) {
+            if (rP[j] >= 0.f) {
+                const double cp = (double)(p.c_puct * rP[j]);
+                const double sc = rQ[j] + cp * sq / (double)(1u + rN[j]);
+                if (sc > best) { best = sc; besti = lane + 32 * j; bestn = rN[j]; bestc = rC[j]; }
+                ++nchild;
+            }
+        }
+        warp_argmax(best, besti);
+        const int mv = besti;
+        const int owner = mv & (GZ_WARP - 1);
+        Np = __shfl_sync(0xffffffffu, bestn, owner);
+        const int next = __shfl_sync(0xffffffffu, bestc, owner);
+        if (lane == 0) p.path[(size_t)g * p.S + depth] = (uint32_t)node * SP + mv;
+        ++depth;
+        if (next >= 0) { // next level's block: issue the loads before the board bookkeeping
+            NodeView v = gz_node_view(p.pool, nbase + next, SP);
+#pragma unroll
+            for (int j = 0; j < NSL; ++j) {
+                const int i = lane + 32 * j;
+                rP[j] = v.P[i]; rN[j] = v.N[i]; rQ[j] = v.Q[i]; rC[j] = v.child[i];
+            }
+        }
+        {
+            const int bit = bb_bit(mv, p.W);
+            bb_set_if(s0, bit, player == 0);
+            bb_set_if(s1, bit, player == 1);
+        }
+        player ^= 1;
+        last = mv;
+        ++ns;
+        node = next;
+    }
+    bool w0 = false, w1 = false;
+    if (ns >= p.n_in_row + 2) {
+        const int d4 = lane & 3;
+        const int dir = (d4 == 0) ? 1 : (d4 == 1) ? 16 : (d4 == 2) ? 17 : 15;
+        bool line = false;
+        if (lane < 8) line = bb_has_line_dir(bb_pick(s0, s1, lane < 4), p.n_in_row, dir);
+        const unsigned b = __ballot_sync(0xffffffffu, line);
+        w0 = (b & 0x0Fu) != 0u;
+        w1 = (b & 0xF0u) != 0u;
+    }
+    const int win = w0 ? 1 : (w1 ? 2 : -1);
+    const bool end = (w0 || w1) || ns >= p.W * p.H;
+    int nslot = 0;
+    if (lane == 0) {
+        if (!end) nslot = atomicAdd(p.leaf_count, 1);
+        p.path_len[g] = depth;
+        GameMeta lm;
+        lm.n_stones = ns; lm.last_move = last; lm.start_player = m.start_player; lm.flags = 0;
+        p.leaf_meta[g] = lm;
+        store_bb(p.leaf_board[g].stones[0], s0);
+        store_bb(p.leaf_board[g].stones[1], s1);
+        if (end) {
+            p.leaf_state[g] = 1;
+            p.leaf_value[g] = (win == -1) ? 0.0 : ((win == player + 1) ? 1.0 : -1.0);
+        } else {
+            p.leaf_state[g] = 0;
+            p.leaf_slot[g] = nslot;
+        }
+    }
+    if (!end) {
+        nslot = __shfl_sync(0xffffffffu, nslot, 0);
+        gz_write_planes(bb_pick(s0, s1, player == 0), bb_pick(s1, s0, player == 0), last, ns, p.W, p.H,
+                        p.leaf_planes + (size_t)nslot * 4 * p.S, lane);
+    }
+    levels_out = (unsigned)depth;
+    children_out = __reduce_add_sync(0xffffffffu, nchild);
+    playouts_out = 1u;
+}
+
+template <int NSL>
+__global__ void __launch_bounds__(128, 5)
+expand_select_small_kernel(TreeParams p, const float *__restrict__ priors, const float *__restrict__ values)
+{
+    const int lane = threadIdx.x & 31;
+    const int g = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    __shared__ SelStats ss;
+    if (threadIdx.x == 0) { ss.levels = 0; ss.children = 0; ss.playouts = 0; ss.done = 0; }
+    __syncthreads();
+    unsigned lv = 0, ch = 0, pl = 0;
+    if (g < p.G) gz_expand_select_game<NSL>(p, g, lane, priors, values, lv, ch, pl);
+    gz_stats_finish(&ss, p.ctr, lane, lv, ch, pl);
+}
+
 // Wave boundary fused: expand + backup of playout k, then select of playout k+1, by the same warp
 // of the same game (the path nodes it just updated are still in cache).
 __global__ void __launch_bounds__(128, 6)
@@ -455,7 +697,10 @@ int gzk_expand_select(gz_engine *e, const float *d_priors, const float *d_values
 {
     GZ_CUDA(e, cudaMemsetAsync(e->leaf_count, 0, sizeof(int32_t), e->stream));
     ProfScope ps(e, PC_SELECT);
-    expand_select_kernel<<<gz_warp_blocks(e->G, 4), 128, 0, e->stream>>>(gz_tree_params(e), d_priors, d_values);
+    const unsigned grid = gz_warp_blocks(e->G, 4);
+    if (e->Sp == 32) expand_select_small_kernel<1><<<grid, 128, 0, e->stream>>>(gz_tree_params(e), d_priors, d_values);
+    else if (e->Sp == 64) expand_select_small_kernel<2><<<grid, 128, 0, e->stream>>>(gz_tree_params(e), d_priors, d_values);
+    else expand_select_kernel<<<grid, 128, 0, e->stream>>>(gz_tree_params(e), d_priors, d_values);
     e->launches++;
     GZ_CUDA(e, cudaGetLastError());
     return GZ_OK;

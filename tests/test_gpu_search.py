@@ -167,6 +167,42 @@ def test_search_with_net_vs_oracle_many_games():
     e.close()
 
 
+@pytest.mark.parametrize("w,n,G,P", [(8, 5, 200, 150), (6, 4, 96, 120), (5, 4, 64, 80), (9, 5, 40, 60)])
+def test_fused_wave_kernel_matches_split_kernels(w, n, G, P):
+    """gz_search (fused expand+backup+select kernel across the wave boundary, its low-latency
+    variant on boards of up to 64 cells) against the same search driven wave by wave through
+    gz_search_select / gz_net_forward / gz_search_expand_backup: identical trees, bit for bit."""
+    rng = np.random.RandomState(7)
+    if w == 8:
+        arrs = load_golden_weights("weights_8_8_5")
+    else:
+        from alphazero_gomoku_b200.engine import weight_shapes
+        wr = np.random.RandomState(5)
+        arrs = [(wr.randn(*sh) * (np.sqrt(2.0 / int(np.prod(sh[1:]))) if len(sh) > 1 else 0.1)).astype(np.float32)
+                for sh in weight_shapes(w, w)]
+    _, lists = _random_positions(rng, w, n, G, max_plies=min(w * w - 2, 30))
+    res = []
+    for fused in (True, False):
+        e = _engine(w, w, n, n_games=G, n_playout=P, seed=3)
+        e.set_weights(arrs)
+        for g, mv in enumerate(lists):
+            e.boards_set(g, mv)
+        for rounds in (P, P // 3):  # the second search continues on the grown trees
+            if fused:
+                e.search(rounds)
+            else:
+                for _ in range(rounds):
+                    st, planes, _, _ = e.search_select(want_cells=False)
+                    probs, values = e.net_forward(planes)
+                    e.search_expand_backup(probs, values)
+        vis, q, rn = e.root_visits(want_q=True)
+        res.append((vis.copy(), q.copy(), rn.copy()))
+        e.close()
+    for a, b in zip(res[0], res[1]):
+        assert np.array_equal(a, b)
+    assert (res[0][2] == P + P // 3).all()
+
+
 def test_rollouts_bit_exact_vs_oracle():
     from oracle import orc
     for (w, n) in [(6, 4), (8, 5), (15, 5)]:
