@@ -47,6 +47,7 @@ struct NetWeights {
     float *wvfc = nullptr; // value fc1 transposed [2S][64]
     float *bias = nullptr; // packed: b1 | b2 | b3 | bh[8] | bp[S] | bv[64] | wv2[64] | bv2[1]
     int off_b1 = 0, off_b2 = 0, off_b3 = 0, off_bh = 0, off_bp = 0, off_bv = 0, off_wv2 = 0, off_bv2 = 0;
+    std::vector<float> tc_consts; // host copy of the tcgen05 trunk's epilogue constants (kernel parameter)
     uint8_t *tc_img = nullptr; // tcgen05 path: fp16 hi/lo conv weight image (gz_net_tc.cu layout)
     float tc_inv[5] = {1.f, 1.f, 1.f, 1.f, 1.f}; // 1 / power-of-two weight scale of conv1..3, policy FC, value FC1
     bool loaded = false;

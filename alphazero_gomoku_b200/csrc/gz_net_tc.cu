@@ -38,9 +38,7 @@ constexpr int OFF_W1 = OFF_ACT2 + 16 * CH;  // conv1 weights, resident: [pass][t
 constexpr int W1_BYTES = 2 * 5 * 2 * 32 * 16;
 constexpr int NSTAGE = 4, STAGE_BYTES = 16384;
 constexpr int OFF_RING = OFF_W1 + W1_BYTES;
-constexpr int OFF_WH = OFF_RING + NSTAGE * STAGE_BYTES; // 1x1 head weights fp32 [128][8]
-constexpr int OFF_BIAS = OFF_WH + 4096;   // b1[32] b2[64] b3[128] bh[8]
-constexpr int OFF_BAR = OFF_BIAS + 1024;  // full[4] empty[4] mma_done, tmem base, mma3_done, c3_free
+constexpr int OFF_BAR = OFF_RING + NSTAGE * STAGE_BYTES; // full[4] empty[4] mma_done, tmem base, mma3_done, c3_free
 constexpr int OFF_HST = OFF_BAR + 128;    // head activations of one group, fp16: [board][pass hi|lo][16 J halves]
 constexpr int HST_BYTES = 8192;           // NB * J * 64 bytes <= 5632 for every supported board
 constexpr int SMEM_BYTES = OFF_HST + HST_BYTES;
@@ -53,6 +51,14 @@ constexpr int TM_C1 = 0, TM_C2 = 0, TM_C3 = 256;  // TMEM column bases; conv2 (2
 constexpr int THREADS = 576;              // 8 front epilogue warps, MMA warp, copy warp, 8 back epilogue warps
 constexpr int SYNC_THREADS = 288;         // front warps + MMA warp (phase barrier)
 } // namespace tc
+
+// Per-channel constants of the epilogues, passed BY VALUE as a kernel parameter: they sit in the
+// constant bank and feed the FMAs as immediate-offset operands, so the epilogues spend no
+// shared-memory bandwidth (which the tensor core needs for its operands) on them.
+struct TcConsts {
+    float wh[tc::C3 * 6];  // 1x1 head convs [channel][0-3 policy, 4-5 value]
+    float b1[tc::C1], b2[tc::C2], b3[tc::C3], bh[8];
+};
 
 struct TcGeom {
     int W, S, P, BS, NB; // board side, cells, row pitch W+1, board stride in rows, boards per group
@@ -158,15 +164,15 @@ __device__ __forceinline__ void tc_split8(const float *f, uint4 &hi, uint4 &lo)
 
 // ---- fused trunk ------------------------------------------------------------------------------
 // planes  [B][4][S] fp32 in {0,1};  wimg = conv1 image | 9 conv2 stages | 18 conv3 stages (fp16);
-// wh [128][8] fp32 (cols 0-3 policy conv, 4-5 value conv);  bias = b1 | b2 | b3 | bh[8];
+// cst = biases and 1x1 head conv weights (constant bank);
 // head_act = ReLU(1x1 convs) split into fp16 hi/lo and written directly as the A operand of
 // heads_tc_kernel: [tile of 128 boards][K step][pass hi|lo][8-k chunk 2][board 128][8 halves],
 // k = c*S + cell inside the policy section (steps 0..Jp-1) and the value section (steps Jp..J-1).
 // dbg (optional) = act1 [B][S][32] | act2 [B][S][64] | act3 [B][S][128] | head [B][6][S] fp32 for
 // parity tests.
 __global__ void __launch_bounds__(tc::THREADS, 1)
-trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wimg, const float *__restrict__ wh,
-                const float *__restrict__ bias, float inv_s1, float inv_s2, float inv_s3,
+trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wimg,
+                const __grid_constant__ TcConsts cst, float inv_s1, float inv_s2, float inv_s3,
                 __half *__restrict__ head_act, const int32_t *__restrict__ count, long long maxB, TcGeom g,
                 float *__restrict__ dbg, long long *__restrict__ timeline)
 {
@@ -185,8 +191,6 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
     for (int i = tid; i < OFF_W1 / 16; i += THREADS) reinterpret_cast<uint4 *>(smem)[i] = make_uint4(0, 0, 0, 0);
     for (int i = tid; i < W1_BYTES / 16; i += THREADS)
         reinterpret_cast<uint4 *>(smem + OFF_W1)[i] = reinterpret_cast<const uint4 *>(wimg)[i];
-    for (int i = tid; i < C3 * 8; i += THREADS) reinterpret_cast<float *>(smem + OFF_WH)[i] = wh[i];
-    for (int i = tid; i < C1 + C2 + C3 + 8; i += THREADS) reinterpret_cast<float *>(smem + OFF_BIAS)[i] = bias[i];
     for (int i = tid; i < HST_BYTES / 16; i += THREADS) reinterpret_cast<uint4 *>(smem + OFF_HST)[i] = make_uint4(0, 0, 0, 0);
     if (tid == 0) {
         for (int s = 0; s < NSTAGE; ++s) {
@@ -238,8 +242,6 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         const bool geo_ok = bq < g.NB && ci < g.W && cj < g.W;
         const int cell = ci * g.W + cj;
         const uint32_t t_lane = ((uint32_t)(q * 32)) << 16;
-        const float *s_b3 = reinterpret_cast<const float *>(smem + OFF_BIAS) + C1 + C2, *s_bh = s_b3 + C3;
-        const float *s_wh = reinterpret_cast<const float *>(smem + OFF_WH);
         __half *s_hst = reinterpret_cast<__half *>(smem + OFF_HST);
         uint32_t ph3 = 0;
         for (long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
@@ -251,7 +253,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             {
                 float hacc[6];
 #pragma unroll
-                for (int q = 0; q < 6; ++q) hacc[q] = s_bh[q];
+                for (int q = 0; q < 6; ++q) hacc[q] = cst.bh[q];
 #pragma unroll
                 for (int part = 0; part < 4; ++part) {
                     uint32_t v[32];
@@ -259,15 +261,9 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                     float f[32];
 #pragma unroll
                     for (int c = 0; c < 32; ++c) {
-                        f[c] = fmaxf(fmaf(__uint_as_float(v[c]), inv_s3, s_b3[part * 32 + c]), 0.f);
-                        const float4 w4 = *reinterpret_cast<const float4 *>(s_wh + (part * 32 + c) * 8);
-                        const float2 w2 = *reinterpret_cast<const float2 *>(s_wh + (part * 32 + c) * 8 + 4);
-                        hacc[0] = fmaf(f[c], w4.x, hacc[0]);
-                        hacc[1] = fmaf(f[c], w4.y, hacc[1]);
-                        hacc[2] = fmaf(f[c], w4.z, hacc[2]);
-                        hacc[3] = fmaf(f[c], w4.w, hacc[3]);
-                        hacc[4] = fmaf(f[c], w2.x, hacc[4]);
-                        hacc[5] = fmaf(f[c], w2.y, hacc[5]);
+                        f[c] = fmaxf(fmaf(__uint_as_float(v[c]), inv_s3, cst.b3[part * 32 + c]), 0.f);
+#pragma unroll
+                        for (int q = 0; q < 6; ++q) hacc[q] = fmaf(f[c], cst.wh[(part * 32 + c) * 6 + q], hacc[q]);
                     }
                     if (dbg && valid) {
                         float *d = dbg + (size_t)maxB * g.S * (C1 + C2) + ((size_t)board * g.S + cell) * C3 + part * 32;
@@ -320,8 +316,6 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         const bool geo_ok = warp < 8 && bq < g.NB && ci < g.W && cj < g.W;
         const int cell = ci * g.W + cj;
         const uint32_t t_lane = ((uint32_t)((warp & 3) * 32)) << 16;
-        const float *s_b1 = reinterpret_cast<const float *>(smem + OFF_BIAS);
-        const float *s_b2 = s_b1 + C1;
         const uint32_t row_off = (uint32_t)(LEAD + r) * 16u;
         uint32_t mma_phase = 0, it = 0, c3_phase = 0;
         bool first_group = true;
@@ -387,7 +381,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             tc_tmem_ld32(tmem + t_lane + TM_C1 + tile * C1, v);
             float f[32];
 #pragma unroll
-            for (int c = 0; c < 32; ++c) f[c] = valid ? fmaxf(fmaf(__uint_as_float(v[c]), inv_s1, s_b1[c]), 0.f) : 0.f;
+            for (int c = 0; c < 32; ++c) f[c] = valid ? fmaxf(fmaf(__uint_as_float(v[c]), inv_s1, cst.b1[c]), 0.f) : 0.f;
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 uint4 hi, lo;
@@ -435,7 +429,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             float f[32];
 #pragma unroll
             for (int c = 0; c < 32; ++c)
-                f[c] = valid ? fmaxf(fmaf(__uint_as_float(v[c]) + __uint_as_float(v2[c]), inv_s2, s_b2[half * 32 + c]), 0.f) : 0.f;
+                f[c] = valid ? fmaxf(fmaf(__uint_as_float(v[c]) + __uint_as_float(v2[c]), inv_s2, cst.b2[half * 32 + c]), 0.f) : 0.f;
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 uint4 hi, lo;
@@ -781,6 +775,20 @@ int gz_tc_prepare_weights(gz_engine *e, std::vector<float> h[16])
                 put2(base + o, base + 8192 + o, v);
             }
     GZ_TRY(gz_upload(e, &e->wts.tc_img, img));
+    {   // epilogue constants (TcConsts order): 1x1 head convs [channel][6], b1, b2, b3, head biases
+        std::vector<float> &c = e->wts.tc_consts;
+        c.assign(sizeof(TcConsts) / sizeof(float), 0.f);
+        for (int ch = 0; ch < C3; ++ch) {
+            for (int q = 0; q < 4; ++q) c[ch * 6 + q] = h[6][(size_t)q * C3 + ch];
+            for (int q = 0; q < 2; ++q) c[ch * 6 + 4 + q] = h[10][(size_t)q * C3 + ch];
+        }
+        float *b = c.data() + C3 * 6;
+        for (int i = 0; i < C1; ++i) b[i] = h[1][i];
+        for (int i = 0; i < C2; ++i) b[C1 + i] = h[3][i];
+        for (int i = 0; i < C3; ++i) b[C1 + C2 + i] = h[5][i];
+        for (int q = 0; q < 4; ++q) b[C1 + C2 + C3 + q] = h[7][q];
+        for (int q = 0; q < 2; ++q) b[C1 + C2 + C3 + 4 + q] = h[11][q];
+    }
     {   // FC image: per K = 16 step [pass hi|lo][8-k chunk 2][N rows][8 halves]; policy steps (N = Np)
         // first, then value FC1 steps (N = 64).  Rows / k beyond the real matrix stay zero.
         const int S = e->S, Np = (S + 15) & ~15;
@@ -860,7 +868,9 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
     }
     {
         ProfScope ps(e, PC_TRUNK_TC);
-        trunk_tc_kernel<<<grid, THREADS, SMEM_BYTES, e->stream>>>(d_planes, w.tc_img, w.wh, w.bias + w.off_b1,
+        TcConsts cst;
+        memcpy(&cst, w.tc_consts.data(), sizeof(TcConsts));
+        trunk_tc_kernel<<<grid, THREADS, SMEM_BYTES, e->stream>>>(d_planes, w.tc_img, cst,
                                                                    w.tc_inv[0], w.tc_inv[1], w.tc_inv[2],
                                                                    reinterpret_cast<__half *>(e->tc_head),
                                                                    d_count, maxB, g, want_dbg ? e->tc_dbg : nullptr, d_tl);

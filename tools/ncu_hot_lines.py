@@ -4,6 +4,7 @@ import csv
 import sys
 
 top = int(sys.argv[1]) if len(sys.argv) > 1 else 40
+sort_col = {"samples": 1, "instr": 2, "smem": 8}[sys.argv[2]] if len(sys.argv) > 2 else 1
 rows = list(csv.reader(sys.stdin))
 hdr = None
 cur_file = ""
@@ -15,7 +16,7 @@ for r in rows:
     if len(r) > 10 and r[0] == "Line No":
         hdr = r
         ix = {n: hdr.index(n) for n in ("# Samples", "Instructions Executed", "stall_long_sb", "stall_short_sb", "stall_wait",
-                                        "stall_barrier", "stall_branch_resolving")}
+                                        "stall_barrier", "stall_branch_resolving", "L1 Wavefronts Shared", "L1 Wavefronts Shared Excessive")}
         continue
     if hdr is None or len(r) < len(hdr):
         continue
@@ -27,7 +28,9 @@ for r in rows:
 tot_s = sum(v[1] for v in lines.values()) or 1
 tot_i = sum(v[2] for v in lines.values()) or 1
 print("total samples %d, warp instructions %d" % (tot_s, tot_i))
-print("%7s %6s %10s %6s %7s %7s %6s %6s  source" % ("samples", "%", "instr", "%", "long_sb", "shortsb", "wait", "bar"))
-for (f, ln), v in sorted(lines.items(), key=lambda kv: -kv[1][1])[:top]:
-    print("%7d %5.1f%% %10d %5.1f%% %7d %7d %6d %6d  %s:%d: %s" % (v[1], 100.0 * v[1] / tot_s, v[2], 100.0 * v[2] / tot_i, v[3],
-                                                                 v[4], v[5], v[6], f, ln, v[0][:90]))
+print("smem wavefronts %d (excessive %d)" % (sum(v[8] for v in lines.values()), sum(v[9] for v in lines.values())))
+print("%7s %6s %10s %6s %7s %7s %6s %6s %9s %9s  source" % ("samples", "%", "instr", "%", "long_sb", "shortsb", "wait", "bar",
+                                                           "smem_wf", "smem_exc"))
+for (f, ln), v in sorted(lines.items(), key=lambda kv: -kv[1][sort_col])[:top]:
+    print("%7d %5.1f%% %10d %5.1f%% %7d %7d %6d %6d %9d %9d  %s:%d: %s" % (v[1], 100.0 * v[1] / tot_s, v[2], 100.0 * v[2] / tot_i,
+                                                                         v[3], v[4], v[5], v[6], v[8], v[9], f, ln, v[0][:80]))
