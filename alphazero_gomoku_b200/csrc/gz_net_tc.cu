@@ -38,13 +38,13 @@ constexpr int OFF_W1 = OFF_ACT2 + 16 * CH;  // conv1 weights, resident: [pass][t
 constexpr int W1_BYTES = 2 * 5 * 2 * 32 * 16;
 constexpr int NSTAGE = 4, STAGE_BYTES = 16384;
 constexpr int OFF_RING = OFF_W1 + W1_BYTES;
-constexpr int OFF_BAR = OFF_RING + NSTAGE * STAGE_BYTES; // full[4] empty[4] mma_done, tmem base, mma3_done, c3_free
+constexpr int OFF_BAR = OFF_RING + NSTAGE * STAGE_BYTES; // full[4] empty[4] mma_done, tmem base, mma3_done, c3_free, c2_back
 constexpr int OFF_HST = OFF_BAR + 128;    // head activations of one group, fp16: [board][pass hi|lo][16 J halves]
 constexpr int HST_BYTES = 8192;           // NB * J * 64 bytes <= 5632 for every supported board
 constexpr int SMEM_BYTES = OFF_HST + HST_BYTES;
 constexpr int W2_STAGE = 8192;            // one tap: [chunk 4][128 rows: 64 hi | 64 lo][8]
 constexpr int W3_STAGE = 16384;           // half a tap: [pass][chunk 4][128][8]
-constexpr int N_STAGES_PER_GROUP = 9 + 18;
+constexpr int N_STAGES_PER_GROUP = 5 + 18; // conv2: two taps per ring stage (4 full + 1 half), conv3: 18
 constexpr size_t WIMG_BYTES = (size_t)W1_BYTES + 9 * W2_STAGE + 18 * W3_STAGE;
 constexpr int TM_C1 = 0, TM_C2 = 0, TM_C3 = 256;  // TMEM column bases; conv2 (2 x 128 stacked columns) reuses conv1's
                                                   // columns: conv1's epilogue is over before conv2 of the same group starts
@@ -56,7 +56,7 @@ constexpr int SYNC_THREADS = 288;         // front warps + MMA warp (phase barri
 // constant bank and feed the FMAs as immediate-offset operands, so the epilogues spend no
 // shared-memory bandwidth (which the tensor core needs for its operands) on them.
 struct TcConsts {
-    float wh[tc::C3 * 6];  // 1x1 head convs [channel][0-3 policy, 4-5 value]
+    float wh[tc::C3 * 6];  // 1x1 head convs [channel pair][0-3 policy, 4-5 value][even, odd channel]
     float b1[tc::C1], b2[tc::C2], b3[tc::C3], bh[8];
 };
 
@@ -135,6 +135,19 @@ __device__ __forceinline__ void tc_tmem_ld32(uint32_t taddr, uint32_t (&v)[32])
                  : "memory");
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+// 16 columns, no wait (pair with tc_tmem_wait_ld)
+__device__ __forceinline__ void tc_tmem_ld16_nowait(uint32_t taddr, uint32_t (&v)[16])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]),
+                   "=r"(v[15])
+                 : "r"(taddr)
+                 : "memory");
+}
+__device__ __forceinline__ void tc_tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tc_bar_sync_all() { asm volatile("bar.sync 3, 544;" ::: "memory"); } // front + MMA + back warps
 // K-major, no-swizzle shared-memory matrix descriptor: rows 16 B apart inside an 8-row core
 // matrix, 8-row groups 128 B apart (SBO), the two 8-element K chunks of one MMA lbo bytes apart.
 __device__ __forceinline__ uint64_t tc_desc(uint32_t saddr, uint32_t lbo_bytes)
@@ -162,6 +175,42 @@ __device__ __forceinline__ void tc_split8(const float *f, uint4 &hi, uint4 &lo)
     lo = make_uint4(l[0], l[1], l[2], l[3]);
 }
 
+// conv2 epilogue for 16 output channels (half h, quarter sub) of one row: accumulator columns
+// (hi*hi + lo*hi at 0-63, hi*lo at 64-127) -> scale, bias, ReLU, hi/lo split -> act2 planes.
+// Front warps take sub 0, back-end warps sub 1 of the same rows.
+__device__ __forceinline__ void tc_ep2_part(uint8_t *smem, uint32_t tmem_tile, uint32_t row_off, const TcConsts &cst,
+                                            float inv_s2, int half, int sub, bool valid, float *dbg_row)
+{
+    using namespace tc;
+    uint32_t v[16], v2[16];
+    tc_tmem_ld16_nowait(tmem_tile + half * 32 + sub * 16, v);
+    tc_tmem_ld16_nowait(tmem_tile + 64 + half * 32 + sub * 16, v2);
+    tc_tmem_wait_ld();
+    float f[16];
+#pragma unroll
+    for (int c = 0; c < 16; c += 2) {
+        const int ch = half * 32 + sub * 16 + c;
+        float2 a = __fadd2_rn(make_float2(__uint_as_float(v[c]), __uint_as_float(v[c + 1])),
+                              make_float2(__uint_as_float(v2[c]), __uint_as_float(v2[c + 1])));
+        a = __ffma2_rn(a, make_float2(inv_s2, inv_s2), make_float2(cst.b2[ch], cst.b2[ch + 1]));
+        f[c] = valid ? fmaxf(a.x, 0.f) : 0.f;
+        f[c + 1] = valid ? fmaxf(a.y, 0.f) : 0.f;
+    }
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+        uint4 hi, lo;
+        tc_split8(f + 8 * c, hi, lo);
+        *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (half * 4 + sub * 2 + c) * CH + row_off) = hi;
+        *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (8 + half * 4 + sub * 2 + c) * CH + row_off) = lo;
+    }
+    if (dbg_row && valid) {
+#pragma unroll
+        for (int c = 0; c < 16; ++c) dbg_row[half * 32 + sub * 16 + c] = f[c];
+    }
+    tc_fence_async_smem();
+    tc_fence_before();
+}
+
 // ---- fused trunk ------------------------------------------------------------------------------
 // planes  [B][4][S] fp32 in {0,1};  wimg = conv1 image | 9 conv2 stages | 18 conv3 stages (fp16);
 // cst = biases and 1x1 head conv weights (constant bank);
@@ -184,7 +233,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
     const long long n_groups = (B + g.NB - 1) / g.NB;
     const uint32_t sbase = tc_smem_u32(smem);
     const uint32_t bar_full = sbase + OFF_BAR, bar_empty = sbase + OFF_BAR + 32, bar_mma = sbase + OFF_BAR + 64;
-    const uint32_t bar_mma3 = sbase + OFF_BAR + 104, bar_c3free = sbase + OFF_BAR + 112;
+    const uint32_t bar_mma3 = sbase + OFF_BAR + 104, bar_c3free = sbase + OFF_BAR + 112, bar_c2back = sbase + OFF_BAR + 120;
     volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(smem + OFF_BAR + 96);
 
     // ---- one-time setup ----------------------------------------------------------------------
@@ -200,6 +249,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         tc_mbar_init(bar_mma, 1);
         tc_mbar_init(bar_mma3, 1);
         tc_mbar_init(bar_c3free, 8); // one arrival per back-end warp
+        tc_mbar_init(bar_c2back, 1); // conv2 done, as seen by the back-end warps (own phase counter)
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -212,6 +262,11 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    if (timeline && tid == 0) { // per-CTA wall time (ns) after setup; [512 + 2 * cta] = start, + 1 = end
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        timeline[512 + 2 * blockIdx.x] = (long long)t;
+    }
     const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
     if (warp == 9) {
@@ -222,11 +277,12 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                 for (int s = 0; s < N_STAGES_PER_GROUP; ++s, ++it) {
                     const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
                     tc_mbar_wait(bar_empty + 8 * slot, ph ^ 1u);
-                    const uint32_t bytes = s < 9 ? W2_STAGE : W3_STAGE;
+                    // conv2: taps 2s, 2s+1 share a stage (deep enough to cover the L2 latency of a refill);
                     // conv3 stages are consumed h-major: 9 taps of input channels 0-31, then 32-63
-                    const size_t off = (size_t)W1_BYTES + (s < 9 ? (size_t)s * W2_STAGE
+                    const uint32_t bytes = s < 4 ? 2 * W2_STAGE : (s == 4 ? W2_STAGE : W3_STAGE);
+                    const size_t off = (size_t)W1_BYTES + (s < 5 ? (size_t)s * 2 * W2_STAGE
                                                                  : (size_t)9 * W2_STAGE +
-                                                                       (size_t)(((s - 9) % 9) * 2 + (s - 9) / 9) * W3_STAGE);
+                                                                       (size_t)(((s - 5) % 9) * 2 + (s - 5) / 9) * W3_STAGE);
                     tc_mbar_expect_tx(bar_full + 8 * slot, bytes);
                     tc_bulk_g2s(sbase + OFF_RING + slot * STAGE_BYTES, wimg + off, bytes, bar_full + 8 * slot);
                 }
@@ -244,26 +300,53 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         const uint32_t t_lane = ((uint32_t)(q * 32)) << 16;
         __half *s_hst = reinterpret_cast<__half *>(smem + OFF_HST);
         uint32_t ph3 = 0;
+        int tl_b = 0;
+#define TC_MARK_BACK() /* back-end marks (3 per group): conv3 done, accumulators released, copy-out done */ \
+    do {                                                                           \
+        if (timeline && blockIdx.x == 0 && tid == 320 && tl_b < 256) timeline[1024 + tl_b++] = clock64(); \
+    } while (0)
         for (long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
             const long long board = grp * g.NB + bq;
             const bool valid = geo_ok && board < B;
+            {   // second 16 channels of each conv2 epilogue half (the front warps take the first 16).
+                float *drow = dbg ? dbg + (size_t)maxB * g.S * C1 + ((size_t)board * g.S + cell) * C2 : nullptr;
+                const uint32_t row_off = (uint32_t)(LEAD + r) * 16u;
+                tc_mbar_wait(bar_c2back, ph3);
+                tc_fence_after();
+                tc_ep2_part(smem, tmem + t_lane + TM_C2 + tile * 128, row_off, cst, inv_s2, 0, 1, valid, drow);
+                tc_bar_sync_all(); // A
+                tc_ep2_part(smem, tmem + t_lane + TM_C2 + tile * 128, row_off, cst, inv_s2, 1, 1, valid, drow);
+                tc_bar_sync_all(); // B
+            }
             tc_mbar_wait(bar_mma3, ph3);
             ph3 ^= 1u;
             tc_fence_after();
+            TC_MARK_BACK();
             {
-                float hacc[6];
+                // packed fp32x2 FMAs (FFMA2): channel pairs (c, c+1) share an instruction; each head
+                // accumulator is kept as an (even channels, odd channels) pair and summed at the end
+                float2 hacc2[6];
 #pragma unroll
-                for (int q = 0; q < 6; ++q) hacc[q] = cst.bh[q];
+                for (int q = 0; q < 6; ++q) hacc2[q] = make_float2(cst.bh[q], 0.f);
+                const float2 inv2 = make_float2(inv_s3, inv_s3);
 #pragma unroll
                 for (int part = 0; part < 4; ++part) {
                     uint32_t v[32];
                     tc_tmem_ld32(tmem + t_lane + TM_C3 + tile * C3 + part * 32, v);
                     float f[32];
 #pragma unroll
-                    for (int c = 0; c < 32; ++c) {
-                        f[c] = fmaxf(fmaf(__uint_as_float(v[c]), inv_s3, cst.b3[part * 32 + c]), 0.f);
+                    for (int c = 0; c < 32; c += 2) {
+                        const int ch = part * 32 + c;
+                        float2 f2 = __ffma2_rn(make_float2(__uint_as_float(v[c]), __uint_as_float(v[c + 1])), inv2,
+                                               make_float2(cst.b3[ch], cst.b3[ch + 1]));
+                        f2.x = fmaxf(f2.x, 0.f);
+                        f2.y = fmaxf(f2.y, 0.f);
+                        f[c] = f2.x;
+                        f[c + 1] = f2.y;
 #pragma unroll
-                        for (int q = 0; q < 6; ++q) hacc[q] = fmaf(f[c], cst.wh[(part * 32 + c) * 6 + q], hacc[q]);
+                        for (int q = 0; q < 6; ++q)
+                            hacc2[q] = __ffma2_rn(f2, make_float2(cst.wh[((ch >> 1) * 6 + q) * 2], cst.wh[((ch >> 1) * 6 + q) * 2 + 1]),
+                                                  hacc2[q]);
                     }
                     if (dbg && valid) {
                         float *d = dbg + (size_t)maxB * g.S * (C1 + C2) + ((size_t)board * g.S + cell) * C3 + part * 32;
@@ -271,6 +354,9 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                         for (int c = 0; c < 32; ++c) d[c] = f[c];
                     }
                 }
+                float hacc[6];
+#pragma unroll
+                for (int q = 0; q < 6; ++q) hacc[q] = hacc2[q].x + hacc2[q].y;
                 // stage hi/lo halves of this group's head activations: [board][pass][k], k padded per section
                 if (geo_ok) {
                     __half *hs = s_hst + (size_t)bq * 32 * g.J;
@@ -288,6 +374,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             tc_fence_before();
             __syncwarp();
             if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_c3free) : "memory");
+            TC_MARK_BACK();
             // copy out as 16-byte chunks of heads_tc_kernel's A operand: step j = [pass 2][chunk 2][board 128][8]
             asm volatile("bar.sync 2, 256;" ::: "memory");
             {
@@ -303,7 +390,9 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                 }
             }
             asm volatile("bar.sync 2, 256;" ::: "memory");
+            TC_MARK_BACK();
         }
+#undef TC_MARK_BACK
     } else {
         // ---- front end (warps 0-7: staging, conv1 / conv2 epilogues) and the MMA warp (8) ----------
         // Software pipeline over the groups of this CTA: while conv3 of group g runs on the tensor
@@ -330,7 +419,11 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         int tl_i = 0;
 #define TC_MARK()                                                                  \
     do {                                                                           \
-        if (timeline && blockIdx.x == 0 && tid == 0 && tl_i < 512) timeline[tl_i++] = clock64(); \
+        if (timeline && blockIdx.x == 0 && tid == 0 && tl_i < 256) timeline[tl_i++] = clock64(); \
+    } while (0)
+#define TC_MARK_MMA() /* MMA warp's own marks, second half of the buffer (7 per group) */ \
+    do {                                                                           \
+        if (timeline && blockIdx.x == 0 && tid == 256 && tl_i < 256) timeline[256 + tl_i++] = clock64(); \
     } while (0)
 
         // input planes -> A0 chunk 0 (fp16 hi in channels 0-3, lo in 4-7); front warps
@@ -400,50 +493,38 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         // MMA warp: conv2, one ring stage per tap, completion -> bar_mma
         auto issue_conv2 = [&]() {
             tc_fence_after();
-            for (int t = 0; t < 9; ++t, ++it) {
+            for (int st = 0; st < 5; ++st, ++it) {
                 const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
                 tc_mbar_wait(bar_full + 8 * slot, ph);
                 tc_fence_after();
-                const uint64_t da = dAct1 + (int64_t)shift[t];
-                const uint64_t db = dRing2 + slot * (STAGE_BYTES / 16);
 #pragma unroll
-                for (int j = 0; j < 2; ++j)
+                for (int tt = 0; tt < 2; ++tt) {
+                    const int t = 2 * st + tt;
+                    if (t < 9) {
+                        const uint64_t da = dAct1 + (int64_t)shift[t];
+                        const uint64_t db = dRing2 + slot * (STAGE_BYTES / 16) + tt * (W2_STAGE / 16);
 #pragma unroll
-                    for (int ks = 0; ks < 2; ++ks) {
-                        // x_hi * [w_hi | w_lo] in one N = 128 MMA (A read once), then x_lo * w_hi (N = 64)
-                        tc_umma_f16(leader, tmem + TM_C2 + j * 128, da + (uint32_t)(((2 * ks) * CH) / 16 + j * 128),
-                                    db + (uint32_t)(ks * 256), tc_idesc(128), (t | ks) != 0);
-                        tc_umma_f16(leader, tmem + TM_C2 + j * 128, da + (uint32_t)(((4 + 2 * ks) * CH) / 16 + j * 128),
-                                    db + (uint32_t)(ks * 256), tc_idesc(64), 1u);
+                        for (int j = 0; j < 2; ++j)
+#pragma unroll
+                            for (int ks = 0; ks < 2; ++ks) {
+                                // x_hi * [w_hi | w_lo] in one N = 128 MMA (A read once), then x_lo * w_hi (N = 64)
+                                tc_umma_f16(leader, tmem + TM_C2 + j * 128, da + (uint32_t)(((2 * ks) * CH) / 16 + j * 128),
+                                            db + (uint32_t)(ks * 256), tc_idesc(128), (t | ks) != 0);
+                                tc_umma_f16(leader, tmem + TM_C2 + j * 128, da + (uint32_t)(((4 + 2 * ks) * CH) / 16 + j * 128),
+                                            db + (uint32_t)(ks * 256), tc_idesc(64), 1u);
+                            }
                     }
+                }
                 tc_umma_commit(leader, bar_empty + 8 * slot);
             }
             tc_umma_commit(leader, bar_mma);
+            tc_umma_commit(leader, bar_c2back);
         };
         // front warps: conv2 accumulators (hi*hi + lo*hi in columns 0-63, hi*lo in 64-127) -> act2,
         // one 32-channel half at a time so conv3 can start on channels 0-31
         auto ep2 = [&](long long board, bool valid, int half) {
-            uint32_t v[32], v2[32];
-            tc_tmem_ld32(tmem + t_lane + TM_C2 + tile * 128 + half * 32, v);
-            tc_tmem_ld32(tmem + t_lane + TM_C2 + tile * 128 + 64 + half * 32, v2);
-            float f[32];
-#pragma unroll
-            for (int c = 0; c < 32; ++c)
-                f[c] = valid ? fmaxf(fmaf(__uint_as_float(v[c]) + __uint_as_float(v2[c]), inv_s2, cst.b2[half * 32 + c]), 0.f) : 0.f;
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                uint4 hi, lo;
-                tc_split8(f + 8 * c, hi, lo);
-                *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (half * 4 + c) * CH + row_off) = hi;
-                *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (8 + half * 4 + c) * CH + row_off) = lo;
-            }
-            if (dbg && valid) {
-                float *d = dbg + (size_t)maxB * g.S * C1 + ((size_t)board * g.S + cell) * C2 + half * 32;
-#pragma unroll
-                for (int c = 0; c < 32; ++c) d[c] = f[c];
-            }
-            tc_fence_async_smem();
-            tc_fence_before();
+            tc_ep2_part(smem, tmem + t_lane + TM_C2 + tile * 128, row_off, cst, inv_s2, half, 0, valid,
+                        dbg ? dbg + (size_t)maxB * g.S * C1 + ((size_t)board * g.S + cell) * C2 : nullptr);
         };
         // MMA warp: conv3 ring stages [s0, s1), h-major: 9 taps of input channels 0-31, then of 32-63
         auto issue_conv3 = [&](int s0, int s1) {
@@ -488,31 +569,38 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             const bool nvalid = geo_ok && has_next && nboard < B;
             TC_MARK(); // 0: act1 of this group ready
             if (warp == 8) {
+                TC_MARK_MMA(); // m0
                 issue_conv2();
-                tc_bar_sync(); // A: act2 channels 0-31 written
+                TC_MARK_MMA(); // m1: conv2 issued
+                tc_bar_sync_all(); // A: act2 channels 0-31 written
+                TC_MARK_MMA(); // m2: barrier A passed
                 if (!first_group) { // the back end must have drained the previous conv3 accumulators
                     tc_mbar_wait(bar_c3free, c3_phase);
                     c3_phase ^= 1u;
                 }
                 first_group = false;
                 tc_fence_after();
+                TC_MARK_MMA(); // m3: conv3 accumulators free
                 issue_conv3(0, 4);
-                tc_bar_sync(); // B: act2 channels 32-63 written, next group's planes staged
+                tc_bar_sync_all(); // B: act2 channels 32-63 written, next group's planes staged
+                TC_MARK_MMA(); // m4: barrier B passed
                 tc_fence_after();
                 if (has_next) issue_conv1();
                 issue_conv3(4, 18);
                 tc_umma_commit(leader, bar_mma3);
+                TC_MARK_MMA(); // m5: conv3 issued
                 if (has_next) tc_bar_sync(); // C: next group's act1 written
+                TC_MARK_MMA(); // m6: barrier C passed
             } else {
                 tc_mbar_wait(bar_mma, mma_phase);
                 mma_phase ^= 1u;
                 tc_fence_after();
                 TC_MARK(); // 1: conv2 MMAs done
                 ep2(board, valid, 0);
-                tc_bar_sync(); // A
+                tc_bar_sync_all(); // A
                 ep2(board, valid, 1);
                 if (has_next) stage_in(nboard, nvalid);
-                tc_bar_sync(); // B
+                tc_bar_sync_all(); // B
                 TC_MARK(); // 2: conv2 epilogue done, next group staged
                 if (has_next) {
                     ep1(nboard, nvalid);
@@ -522,8 +610,14 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             }
         }
 #undef TC_MARK
+#undef TC_MARK_MMA
     }
     __syncthreads();
+    if (timeline && tid == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        timeline[512 + 2 * blockIdx.x + 1] = (long long)t;
+    }
     if (warp == 0) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
@@ -779,8 +873,8 @@ int gz_tc_prepare_weights(gz_engine *e, std::vector<float> h[16])
         std::vector<float> &c = e->wts.tc_consts;
         c.assign(sizeof(TcConsts) / sizeof(float), 0.f);
         for (int ch = 0; ch < C3; ++ch) {
-            for (int q = 0; q < 4; ++q) c[ch * 6 + q] = h[6][(size_t)q * C3 + ch];
-            for (int q = 0; q < 2; ++q) c[ch * 6 + 4 + q] = h[10][(size_t)q * C3 + ch];
+            for (int q = 0; q < 4; ++q) c[((ch >> 1) * 6 + q) * 2 + (ch & 1)] = h[6][(size_t)q * C3 + ch];
+            for (int q = 0; q < 2; ++q) c[((ch >> 1) * 6 + 4 + q) * 2 + (ch & 1)] = h[10][(size_t)q * C3 + ch];
         }
         float *b = c.data() + C3 * 6;
         for (int i = 0; i < C1; ++i) b[i] = h[1][i];
@@ -863,8 +957,8 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
     static const char *tl_path = getenv("GZ_TC_TIMELINE");
     long long *d_tl = nullptr;
     if (tl_path) {
-        GZ_CUDA(e, cudaMalloc(&d_tl, 512 * sizeof(long long)));
-        GZ_CUDA(e, cudaMemsetAsync(d_tl, 0, 512 * sizeof(long long), e->stream));
+        GZ_CUDA(e, cudaMalloc(&d_tl, 2048 * sizeof(long long)));
+        GZ_CUDA(e, cudaMemsetAsync(d_tl, 0, 2048 * sizeof(long long), e->stream));
     }
     {
         ProfScope ps(e, PC_TRUNK_TC);
@@ -876,13 +970,24 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
                                                                    d_count, maxB, g, want_dbg ? e->tc_dbg : nullptr, d_tl);
     }
     if (d_tl) {
-        std::vector<long long> h(512);
+        std::vector<long long> h(2048);
         GZ_CUDA(e, cudaStreamSynchronize(e->stream));
-        GZ_CUDA(e, cudaMemcpy(h.data(), d_tl, 512 * sizeof(long long), cudaMemcpyDeviceToHost));
+        GZ_CUDA(e, cudaMemcpy(h.data(), d_tl, 2048 * sizeof(long long), cudaMemcpyDeviceToHost));
         cudaFree(d_tl);
         if (FILE *f = fopen(tl_path, "a")) {
             fprintf(f, "launch B=%lld grid=%u\n", (long long)maxB, grid);
-            for (int i = 0; i < 512 && h[i]; ++i) fprintf(f, "%lld%c", h[i] - h[0], (i % 4 == 3) ? '\n' : ' ');
+            for (int i = 0; i < 256 && h[i]; ++i) fprintf(f, "%lld%c", h[i] - h[0], (i % 4 == 3) ? '\n' : ' ');
+            fprintf(f, "\ncta_ns (start - first start, duration)\n");
+            {
+                long long t0 = h[512];
+                for (unsigned c = 0; c < grid && c < 256; ++c) t0 = h[512 + 2 * c] < t0 ? h[512 + 2 * c] : t0;
+                for (unsigned c = 0; c < grid && c < 256; ++c)
+                    fprintf(f, "%lld:%lld%c", h[512 + 2 * c] - t0, h[513 + 2 * c] - h[512 + 2 * c], (c % 8 == 7) ? '\n' : ' ');
+            }
+            fprintf(f, "\nmma\n");
+            for (int i = 0; i < 256 && h[256 + i]; ++i) fprintf(f, "%lld%c", h[256 + i] - h[0], (i % 7 == 6) ? '\n' : ' ');
+            fprintf(f, "\nback\n");
+            for (int i = 0; i < 256 && h[1024 + i]; ++i) fprintf(f, "%lld%c", h[1024 + i] - h[0], (i % 3 == 2) ? '\n' : ' ');
             fprintf(f, "\n");
             fclose(f);
         }
