@@ -42,6 +42,18 @@ __device__ __forceinline__ void warp_argmax(double &s, int &i)
     }
 }
 
+// Same result (largest score, lowest index on ties) with three warp-wide integer reductions: the
+// double is mapped to an order-preserving 64-bit key and reduced high word first.
+__device__ __forceinline__ int warp_argmax_redux(double s, int i)
+{
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(s + 0.0); // -0.0 -> +0.0
+    const unsigned long long key = (bits >> 63) ? ~bits : (bits | 0x8000000000000000ull);
+    const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+    const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
+    const unsigned ml = __reduce_max_sync(0xffffffffu, hi == mh ? lo : 0u);
+    return (int)__reduce_min_sync(0xffffffffu, (hi == mh && lo == ml) ? (unsigned)i : 0x7fffffffu);
+}
+
 // n-in-a-row test of one colour in one direction (shift 1 / 16 / 17 / 15), see bb_has_line
 __device__ __forceinline__ bool bb_has_line_dir(const BB &b, int n, int s)
 {
@@ -308,13 +320,16 @@ expand_backup_kernel(TreeParams p, const float *__restrict__ priors, const float
 //   then    expand / link / backup from registers, patch the prefetched root block with the one
 //           edge the backup changed, and descend: one trip per level below the root.
 // Same arithmetic, in the same order per node, as gz_expand_backup_game + gz_select_game.
-template <int NSL>
+template <int NSL, int WT>
 __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g, int lane,
                                                       const float *__restrict__ priors,
                                                       const float *__restrict__ values, unsigned &levels_out,
                                                       unsigned &children_out, unsigned &playouts_out)
 {
     constexpr int SP = 32 * NSL;
+    // board side as a compile-time constant where the launcher has one (WT > 0; the net path is
+    // square): cell <-> bit conversions and the plane writer become shifts instead of divisions
+    const int BW = WT > 0 ? WT : p.W, BH = WT > 0 ? WT : p.H, BS = WT > 0 ? WT * WT : p.S;
     levels_out = children_out = playouts_out = 0;
     const size_t nbase = (size_t)g * p.cap;
     // ---- trip 1
@@ -330,7 +345,7 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
     const GameMeta m = p.meta[g];
     BB s0 = load_bb(p.boards[g].stones[0]), s1 = load_bb(p.boards[g].stones[1]);
     const BB occ = bb_or(load_bb(p.leaf_board[g].stones[0]), load_bb(p.leaf_board[g].stones[1]));
-    const uint32_t e_mine = p.path[(size_t)g * p.S + (lane < p.S ? lane : 0)];
+    const uint32_t e_mine = p.path[(size_t)g * BS + (lane < BS ? lane : 0)];
     // ---- trip 2
     const bool do_exp = st == 0, do_bk = st != 2;
     float vnet = 0.f, prr[NSL];
@@ -340,7 +355,7 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
 #pragma unroll
         for (int j = 0; j < NSL; ++j) {
             const int i = lane + 32 * j;
-            prr[j] = i < p.S ? priors[(size_t)slot * p.S + i] : 0.f;
+            prr[j] = i < BS ? priors[(size_t)slot * BS + i] : 0.f;
         }
         if (top > 0) newn = p.free_stack[nbase + top - 1];
     }
@@ -370,7 +385,7 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
 #pragma unroll
             for (int j = 0; j < NSL; ++j) {
                 const int i = lane + 32 * j;
-                const bool leg = (i < p.S) && !bb_test(occ, bb_bit(i, p.W));
+                const bool leg = (i < BS) && !bb_test(occ, bb_bit(i, BW));
                 const float pv = leg ? prr[j] : -1.f;
                 nv.P[i] = pv; nv.N[i] = 0u; nv.Q[i] = 0.0; nv.child[i] = -1;
                 cnt += leg;
@@ -382,7 +397,7 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
             } else if (d <= 32) {
                 if (lane == d - 1) ev.child[cell_e] = newn;
             } else if (lane == 0) {
-                const uint32_t e = p.path[(size_t)g * p.S + d - 1];
+                const uint32_t e = p.path[(size_t)g * BS + d - 1];
                 gz_node_view(p.pool, nbase + e / SP, SP).child[e % SP] = newn;
             }
             cnt = __reduce_add_sync(0xffffffffu, cnt);
@@ -408,7 +423,7 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
             ev.Q[cell_e] = q_new;
         }
         for (int k = lane + 32; k < d; k += 32) { // paths deeper than a warp: the plain way
-            const uint32_t e = p.path[(size_t)g * p.S + k];
+            const uint32_t e = p.path[(size_t)g * BS + k];
             NodeView nv = gz_node_view(p.pool, nbase + e / SP, SP);
             const int cell = (int)(e % SP);
             const double val = ((d - (k + 1)) & 1) ? v : -v;
@@ -463,12 +478,11 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
                 ++nchild;
             }
         }
-        warp_argmax(best, besti);
-        const int mv = besti;
+        const int mv = warp_argmax_redux(best, besti);
         const int owner = mv & (GZ_WARP - 1);
         Np = __shfl_sync(0xffffffffu, bestn, owner);
         const int next = __shfl_sync(0xffffffffu, bestc, owner);
-        if (lane == 0) p.path[(size_t)g * p.S + depth] = (uint32_t)node * SP + mv;
+        if (lane == 0) p.path[(size_t)g * BS + depth] = (uint32_t)node * SP + mv;
         ++depth;
         if (next >= 0) { // next level's block: issue the loads before the board bookkeeping
             NodeView v = gz_node_view(p.pool, nbase + next, SP);
@@ -479,7 +493,7 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
             }
         }
         {
-            const int bit = bb_bit(mv, p.W);
+            const int bit = bb_bit(mv, BW);
             bb_set_if(s0, bit, player == 0);
             bb_set_if(s1, bit, player == 1);
         }
@@ -499,7 +513,7 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
         w1 = (b & 0xF0u) != 0u;
     }
     const int win = w0 ? 1 : (w1 ? 2 : -1);
-    const bool end = (w0 || w1) || ns >= p.W * p.H;
+    const bool end = (w0 || w1) || ns >= BW * BH;
     int nslot = 0;
     if (lane == 0) {
         if (!end) nslot = atomicAdd(p.leaf_count, 1);
@@ -519,15 +533,15 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
     }
     if (!end) {
         nslot = __shfl_sync(0xffffffffu, nslot, 0);
-        gz_write_planes(bb_pick(s0, s1, player == 0), bb_pick(s1, s0, player == 0), last, ns, p.W, p.H,
-                        p.leaf_planes + (size_t)nslot * 4 * p.S, lane);
+        gz_write_planes(bb_pick(s0, s1, player == 0), bb_pick(s1, s0, player == 0), last, ns, BW, BH,
+                        p.leaf_planes + (size_t)nslot * 4 * BS, lane);
     }
     levels_out = (unsigned)depth;
     children_out = __reduce_add_sync(0xffffffffu, nchild);
     playouts_out = 1u;
 }
 
-template <int NSL>
+template <int NSL, int WT>
 __global__ void __launch_bounds__(128, 5)
 expand_select_small_kernel(TreeParams p, const float *__restrict__ priors, const float *__restrict__ values)
 {
@@ -537,7 +551,7 @@ expand_select_small_kernel(TreeParams p, const float *__restrict__ priors, const
     if (threadIdx.x == 0) { ss.levels = 0; ss.children = 0; ss.playouts = 0; ss.done = 0; }
     __syncthreads();
     unsigned lv = 0, ch = 0, pl = 0;
-    if (g < p.G) gz_expand_select_game<NSL>(p, g, lane, priors, values, lv, ch, pl);
+    if (g < p.G) gz_expand_select_game<NSL, WT>(p, g, lane, priors, values, lv, ch, pl);
     gz_stats_finish(&ss, p.ctr, lane, lv, ch, pl);
 }
 
@@ -698,9 +712,13 @@ int gzk_expand_select(gz_engine *e, const float *d_priors, const float *d_values
     GZ_CUDA(e, cudaMemsetAsync(e->leaf_count, 0, sizeof(int32_t), e->stream));
     ProfScope ps(e, PC_SELECT);
     const unsigned grid = gz_warp_blocks(e->G, 4);
-    if (e->Sp == 32) expand_select_small_kernel<1><<<grid, 128, 0, e->stream>>>(gz_tree_params(e), d_priors, d_values);
-    else if (e->Sp == 64) expand_select_small_kernel<2><<<grid, 128, 0, e->stream>>>(gz_tree_params(e), d_priors, d_values);
-    else expand_select_kernel<<<grid, 128, 0, e->stream>>>(gz_tree_params(e), d_priors, d_values);
+    const TreeParams tp = gz_tree_params(e);
+    const bool sq = e->W == e->H;
+    if (e->Sp == 64 && sq && e->W == 8) expand_select_small_kernel<2, 8><<<grid, 128, 0, e->stream>>>(tp, d_priors, d_values);
+    else if (e->Sp == 64 && sq && e->W == 6) expand_select_small_kernel<2, 6><<<grid, 128, 0, e->stream>>>(tp, d_priors, d_values);
+    else if (e->Sp == 64) expand_select_small_kernel<2, 0><<<grid, 128, 0, e->stream>>>(tp, d_priors, d_values);
+    else if (e->Sp == 32) expand_select_small_kernel<1, 0><<<grid, 128, 0, e->stream>>>(tp, d_priors, d_values);
+    else expand_select_kernel<<<grid, 128, 0, e->stream>>>(tp, d_priors, d_values);
     e->launches++;
     GZ_CUDA(e, cudaGetLastError());
     return GZ_OK;
