@@ -542,7 +542,7 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
 }
 
 template <int NSL, int WT>
-__global__ void __launch_bounds__(128, 5)
+__global__ void __launch_bounds__(128, 8)
 expand_select_small_kernel(TreeParams p, const float *__restrict__ priors, const float *__restrict__ values)
 {
     const int lane = threadIdx.x & 31;
