@@ -950,6 +950,7 @@ extern "C" int gz_profile_enable(gz_engine *e, int32_t on)
 {
     if (!e) return GZ_E_INVALID;
     e->prof_on = on != 0;
+    e->prof_stride = on > 1 ? on : 1; // on = N > 1: time every N-th launch of each class and scale
     return GZ_OK;
 }
 
@@ -959,13 +960,20 @@ extern "C" int gz_profile_read(gz_engine *e, double *ms, int64_t *launches, int3
     GZ_CUDA(e, cudaSetDevice(e->cfg.device));
     GZ_CUDA(e, cudaStreamSynchronize(e->stream));
     for (int c = 0; c < GZ_PROF_CLASSES; ++c) {
+        double sum = 0.0;
+        long long n = 0;
         for (size_t i = 0; i + 1 < e->prof_used[c]; i += 2) {
             float t = 0.f;
             if (cudaEventElapsedTime(&t, e->prof_ev[c][i], e->prof_ev[c][i + 1]) == cudaSuccess) {
-                e->prof_ms[c] += t;
-                e->prof_n[c] += 1;
+                sum += t;
+                n += 1;
             }
         }
+        if (n > 0) { // scale the timed sample up to every launch seen
+            e->prof_ms[c] += sum * (double)e->prof_seen[c] / (double)n;
+            e->prof_n[c] += e->prof_seen[c];
+        }
+        e->prof_seen[c] = 0;
         e->prof_used[c] = 0;
         if (ms) ms[c] = e->prof_ms[c];
         if (launches) launches[c] = e->prof_n[c];

@@ -128,6 +128,8 @@ struct gz_engine {
     int64_t roll_cap;
     // per-kernel-class timing
     bool prof_on;
+    int prof_stride;                     // time every prof_stride-th launch of a class (events cost GPU idle time)
+    long long prof_seen[GZ_PROF_CLASSES]; // launches of the class since the last read, timed or not
     std::vector<cudaEvent_t> prof_ev[GZ_PROF_CLASSES]; // start/stop pairs
     size_t prof_used[GZ_PROF_CLASSES];
     double prof_ms[GZ_PROF_CLASSES];
@@ -145,6 +147,7 @@ struct ProfScope {
     ProfScope(gz_engine *eng, int cls) : e(eng), c(cls), live(false)
     {
         if (!e->prof_on) return;
+        if ((e->prof_seen[c]++ % e->prof_stride) != 0) return;
         size_t u = e->prof_used[c];
         if (u + 2 > e->prof_ev[c].size()) {
             if (e->prof_ev[c].size() >= 400000) return;

@@ -315,8 +315,10 @@ class Engine:
         return {k: getattr(c, k) for k, _ in GzCounters._fields_}
 
     # ---- per-kernel-class device timing ------------------------------------------------------
-    def profile_enable(self, on=True):
-        self._ck(self.L.gz_profile_enable(self._h, int(bool(on))))
+    def profile_enable(self, on=True, stride=1):
+        """Per-kernel-class CUDA-event timing; stride N times every N-th launch of a class and
+        scales (the event pairs themselves cost GPU idle time between dependent kernels)."""
+        self._ck(self.L.gz_profile_enable(self._h, max(1, int(stride)) if on else 0))
 
     def profile_read(self, reset=True):
         """{class name: (device ms, timed launches)} since the last reset."""

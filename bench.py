@@ -232,7 +232,7 @@ def run_ours(args):
     eng.selfplay_stats(reset=True)
     eng.counters(reset=True)
     eng.profile_read(reset=True)
-    eng.profile_enable(True)
+    eng.profile_enable(True, stride=args.prof_stride)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -324,13 +324,17 @@ def run_ours(args):
             "config": workload_config(args, wname, args.games),
             "e2e": {"value": tot_playouts_e2e / (e2e_ms_max * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h_total // max(args.steps, 1),
+                    "ms_per_step": e2e_ms_max / max(args.steps, 1),
+                    "net_evals_per_playout": float(ctr2["leaf_evals"]) / max(float(ctr2["playouts"]), 1.0),
                     "what": "per step: gz_set_weights from pinned host arrays, gz_selfplay_step(1), "
-                            "gz_selfplay_last + gz_selfplay_drain into host buffers"},
+                            "gz_selfplay_last + gz_selfplay_drain into host buffers; these steps are the plies "
+                            "AFTER the device-timed ones (later game phase: more playouts end in terminal "
+                            "positions, which need no net evaluation - compare net_evals_per_playout)"},
             "gpu_launches": int(tot_launch),
             "clocks": clocks,
             "roofline": roof,
             "net": {"impl": ("tcgen05 fused trunk (fp16 hi/lo split, 3 MMA passes, fp32 accumulate in TMEM) + tcgen05 FC heads (same split)"
-                             if tc else "fp32 CUDA-core (FFMA) implicit GEMM"), "leaf_evals": int(tot_leaf),
+                             if tc else "fp32 CUDA-core (FFMA) implicit GEMM"), "net_evals_per_playout": float(ctr["leaf_evals"]) / max(float(ctr["playouts"]), 1.0), "leaf_evals": int(tot_leaf),
                     "leaf_evals_per_s": tot_leaf / (ms_max * 1e-3),
                     "algorithmic_tflops": ctr["leaf_evals"] * fl["total"] / max(net_ms * 1e-3, 1e-12) / 1e12,
                     "flops_per_leaf": fl["total"]},
@@ -367,6 +371,8 @@ def main():
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--cpu-plies", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--prof-stride", type=int, default=16,
+                    help="CUDA-event pairs around every N-th launch of each kernel class inside the timed region")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

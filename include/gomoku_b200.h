@@ -199,6 +199,7 @@ int gz_get_counters(gz_engine *e, gz_counters *out, int32_t reset);
 
 /* ---- per-kernel-class device timing (CUDA events on the engine stream) for bench.py ----- */
 #define GZ_PROF_CLASSES 14
+/* on = 0 off, 1 time every launch, N > 1 time every N-th launch of each class (totals are scaled) */
 int gz_profile_enable(gz_engine *e, int32_t on);
 /* ms[c] = summed device time, launches[c] = timed launches of class c since the last reset */
 int gz_profile_read(gz_engine *e, double *ms /*[GZ_PROF_CLASSES]*/, int64_t *launches, int32_t reset);
