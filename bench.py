@@ -249,8 +249,8 @@ def run_ours(args):
     clocks = sampler.stop() if rank == 0 else None
     eng.profile_enable(False)
     prof = eng.profile_read(reset=True)
+    stats = eng.selfplay_stats(reset=False)  # same device counters as counters(): read before the reset
     ctr = eng.counters(reset=True)
-    stats = eng.selfplay_stats(reset=True)
 
     # ---- end to end: host weights in, host results out, every step -------------------------------
     host_w = [torch.from_numpy(a.copy()).pin_memory() for a in arrs]
@@ -270,8 +270,33 @@ def run_ours(args):
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     barrier()
+    stats2 = eng.selfplay_stats(reset=False)
     ctr2 = eng.counters(reset=True)
-    stats2 = eng.selfplay_stats(reset=True)
+
+    # ---- one generation: keep playing until every slot has finished a game (bounded) -------------
+    # The other half of BASELINE.json's metric (self-play games/hour) needs whole games; this
+    # region is timed on its own and does not enter `value` / `e2e`.
+    gen = None
+    if args.generation_plies > 0:
+        barrier()
+        torch.cuda.synchronize()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record(stream)
+        n_gen = 0
+        for _ in range(args.generation_plies):
+            eng.selfplay_step(1)
+            n_gen += 1
+            if n_gen % 8 == 0:
+                eng.selfplay_drain()      # keep the device sample ring from filling up
+                if eng.selfplay_stats(reset=False)["n_games"] >= args.games:
+                    break
+        g1.record(stream)
+        torch.cuda.synchronize()
+        eng.selfplay_drain()
+        st3 = eng.selfplay_stats(reset=False)
+        ctr3 = eng.counters(reset=True)
+        gen = [g0.elapsed_time(g1), float(n_gen), float(st3["n_games"]), float(st3["n_samples"]), float(ctr3["playouts"]),
+               float(ctr3["leaf_evals"]), float(st3["n_plies"])]
 
     playouts = float(ctr["playouts"])
     t = torch.tensor([ms, e2e_s * 1000.0], dtype=torch.float64, device=dev)
@@ -283,6 +308,25 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(s, op=dist.ReduceOp.SUM)
     ms_max, e2e_ms_max = t.tolist()
+    gen_line = None
+    if gen is not None:
+        gt = torch.tensor(gen[:1], dtype=torch.float64, device=dev)
+        gs = torch.tensor(gen[1:], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(gt, op=dist.ReduceOp.MAX)
+            dist.all_reduce(gs, op=dist.ReduceOp.SUM)
+        g_ms = gt.item()
+        g_steps, g_games, g_samples, g_playouts, g_leaf, g_plies = gs.tolist()
+        g_len = (g_samples / g_games) if g_games > 0 else None
+        gen_line = {"plies_played_per_slot": int(round(g_steps / world)), "seconds": g_ms * 1e-3,
+                    "games_finished": int(g_games), "mean_game_len": g_len,
+                    "games_per_hour_counted": g_games / (g_ms * 1e-3) * 3600.0,
+                    "games_per_hour_steady": ((g_plies / (g_ms * 1e-3)) / g_len * 3600.0) if g_len else None,
+                    "playouts_per_sec": g_playouts / (g_ms * 1e-3),
+                    "net_evals_per_playout": g_leaf / max(g_playouts, 1.0),
+                    "what": "untimed for value/e2e: the same engine keeps playing (slots recycle) until every slot "
+                            "has finished a game or --generation-plies; counted = games finished in this window / "
+                            "time, steady = plies per second / mean game length"}
     tot_playouts, tot_playouts_e2e, tot_leaf, tot_plies, tot_games, tot_samples, tot_launch, tot_over = s.tolist()
 
     if rank == 0:
@@ -346,6 +390,8 @@ def run_ours(args):
                          "mean_game_len": mean_len,
                          "games_per_hour": (plies_per_s / mean_len * 3600.0) if mean_len else None},
         }
+        if gen_line is not None:
+            line["generation"] = gen_line
         if world == 1 and not args.no_cpu_baseline:
             from oracle import orc
             orc.build()
@@ -371,6 +417,9 @@ def main():
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--cpu-plies", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--generation-plies", type=int, default=48,
+                    help="after the timed regions, play up to this many more plies (until every slot finished a game) "
+                         "and report games/hour; 0 disables")
     ap.add_argument("--prof-stride", type=int, default=16,
                     help="CUDA-event pairs around every N-th launch of each kernel class inside the timed region")
     args = ap.parse_args()
