@@ -50,7 +50,7 @@ class GzConfig(C.Structure):
 class GzSelfplayStats(C.Structure):
     _fields_ = [("n_games", C.c_int64), ("n_samples", C.c_int64), ("n_playouts", C.c_int64),
                 ("n_leaf_evals", C.c_int64), ("n_plies", C.c_int64), ("pool_overflows", C.c_int64),
-                ("n_wins", C.c_int64 * 3)]
+                ("n_wins", C.c_int64 * 3), ("max_tree_nodes", C.c_int64)]
 
 
 class GzCounters(C.Structure):

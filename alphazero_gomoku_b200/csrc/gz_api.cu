@@ -167,7 +167,7 @@ extern "C" int gz_create(const gz_config *cfg, gz_engine **out)
     if (e->cfg.dirichlet_eps < 0.f) e->cfg.dirichlet_eps = 0.25f;
     if (e->cfg.n_playout <= 0) e->cfg.n_playout = 400;
     e->W = W; e->H = H; e->S = W * H; e->Sp = (e->S + 31) / 32 * 32; e->n_in_row = n; e->G = cfg->n_games;
-    e->cap = cfg->nodes_per_game > 0 ? cfg->nodes_per_game : 4 * e->cfg.n_playout + 8;
+    e->cap = cfg->nodes_per_game > 0 ? cfg->nodes_per_game : 8 * e->cfg.n_playout + 8;
     e->c1 = cfg->trunk[0] > 0 ? cfg->trunk[0] : 32;
     e->c2 = cfg->trunk[1] > 0 ? cfg->trunk[1] : 64;
     e->c3 = cfg->trunk[2] > 0 ? cfg->trunk[2] : 128;
@@ -856,6 +856,7 @@ extern "C" int gz_selfplay_get_stats(gz_engine *e, gz_selfplay_stats *out, int32
     out->n_plies = (int64_t)c.plies;
     out->pool_overflows = (int64_t)c.pool_overflows;
     for (int i = 0; i < 3; ++i) out->n_wins[i] = (int64_t)c.wins[i];
+    out->max_tree_nodes = (int64_t)c.max_nodes;
     if (reset) GZ_CUDA(e, cudaMemset(e->counters, 0, sizeof(DevCounters)));
     return GZ_OK;
 }

@@ -31,7 +31,7 @@ __host__ __device__ __forceinline__ NodeView gz_node_view(uint8_t *pool, size_t 
 // device-side counters (one struct in device memory, updated with warp-aggregated atomics)
 struct DevCounters {
     unsigned long long select_levels, select_children, playouts, leaf_evals, expanded_children,
-        rollout_plies, pool_overflows, plies, games_finished, samples_out, dropped, wins[3];
+        rollout_plies, pool_overflows, plies, games_finished, samples_out, dropped, wins[3], max_nodes;
 };
 
 struct NetWeights {

@@ -217,6 +217,8 @@ __global__ void __launch_bounds__(128) selfplay_advance_kernel(TreeParams p, Sel
     const int mv = sp.sel_moves[g];
     if (mv < 0) return;
     const int S = p.S;
+    // high-water mark of tree nodes in use (the tree is largest right after a search)
+    if (lane == 0) atomicMax(&p.ctr->max_nodes, (unsigned long long)(p.cap - p.free_top[g]));
     GameMeta m = sp.meta[g];
     const int ply = m.n_stones;
     // record (state before the move is implied by the move list), pi, then play the move

@@ -45,6 +45,7 @@ class Engine:
         cfg = GzConfig()
         cfg.width, cfg.height, cfg.n_in_row = int(width), int(height), int(n_in_row)
         cfg.n_games, cfg.n_playout, cfg.nodes_per_game = int(n_games), int(n_playout), int(nodes_per_game)
+        self.nodes_per_game = int(nodes_per_game) if nodes_per_game > 0 else 8 * int(n_playout) + 8
         cfg.c_puct, cfg.dirichlet_alpha, cfg.dirichlet_eps = float(c_puct), float(dirichlet_alpha), float(dirichlet_eps)
         cfg.trunk[0], cfg.trunk[1], cfg.trunk[2] = [int(t) for t in trunk]
         cfg.seed, cfg.game_id_base = int(seed), int(game_id_base)
@@ -292,7 +293,7 @@ class Engine:
         self._ck(self.L.gz_selfplay_get_stats(self._h, C.byref(s), int(reset)))
         return {"n_games": s.n_games, "n_samples": s.n_samples, "n_playouts": s.n_playouts,
                 "n_leaf_evals": s.n_leaf_evals, "n_plies": s.n_plies, "pool_overflows": s.pool_overflows,
-                "n_wins": [s.n_wins[0], s.n_wins[1], s.n_wins[2]]}
+                "n_wins": [s.n_wins[0], s.n_wins[1], s.n_wins[2]], "max_tree_nodes": s.max_tree_nodes}
 
     # ---- pure MCTS -------------------------------------------------------------------------
     def pure_search(self, n_playout, search_id=0):

@@ -218,7 +218,7 @@ def run_ours(args):
     dev_arrs = list(torch.split(flat, sizes))
     eng = Engine(width=args.board, height=args.board, n_in_row=args.n_in_row, n_games=args.games,
                  n_playout=args.playouts, seed=args.seed + rank, game_id_base=rank << 40, device=local,
-                 stream=stream.cuda_stream)
+                 stream=stream.cuda_stream, nodes_per_game=args.nodes_per_game)
     eng.set_weights(dev_arrs)
     eng.selfplay_begin(temp=1.0, recycle=True)
 
@@ -296,7 +296,7 @@ def run_ours(args):
         st3 = eng.selfplay_stats(reset=False)
         ctr3 = eng.counters(reset=True)
         gen = [g0.elapsed_time(g1), float(n_gen), float(st3["n_games"]), float(st3["n_samples"]), float(ctr3["playouts"]),
-               float(ctr3["leaf_evals"]), float(st3["n_plies"])]
+               float(ctr3["leaf_evals"]), float(st3["n_plies"]), float(st3["pool_overflows"])]
 
     playouts = float(ctr["playouts"])
     t = torch.tensor([ms, e2e_s * 1000.0], dtype=torch.float64, device=dev)
@@ -316,7 +316,7 @@ def run_ours(args):
             dist.all_reduce(gt, op=dist.ReduceOp.MAX)
             dist.all_reduce(gs, op=dist.ReduceOp.SUM)
         g_ms = gt.item()
-        g_steps, g_games, g_samples, g_playouts, g_leaf, g_plies = gs.tolist()
+        g_steps, g_games, g_samples, g_playouts, g_leaf, g_plies, g_over = gs.tolist()
         g_len = (g_samples / g_games) if g_games > 0 else None
         gen_line = {"plies_played_per_slot": int(round(g_steps / world)), "seconds": g_ms * 1e-3,
                     "games_finished": int(g_games), "mean_game_len": g_len,
@@ -324,6 +324,8 @@ def run_ours(args):
                     "games_per_hour_steady": ((g_plies / (g_ms * 1e-3)) / g_len * 3600.0) if g_len else None,
                     "playouts_per_sec": g_playouts / (g_ms * 1e-3),
                     "net_evals_per_playout": g_leaf / max(g_playouts, 1.0),
+                    "pool_overflows": int(g_over), "max_tree_nodes": int(st3["max_tree_nodes"]),
+                    "nodes_per_game": eng.nodes_per_game,
                     "what": "untimed for value/e2e: the same engine keeps playing (slots recycle) until every slot "
                             "has finished a game or --generation-plies; counted = games finished in this window / "
                             "time, steady = plies per second / mean game length"}
@@ -417,6 +419,7 @@ def main():
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--cpu-plies", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--nodes-per-game", type=int, default=0, help="tree pool blocks per game (0 = engine default)")
     ap.add_argument("--generation-plies", type=int, default=48,
                     help="after the timed regions, play up to this many more plies (until every slot finished a game) "
                          "and report games/hour; 0 disables")

@@ -370,3 +370,75 @@ def test_selfplay_pi_matches_oracle_search_with_tree_reuse():
     print("selfplay pi vs oracle: exact", exact, "of", total, "worst TV", worst)
     assert worst <= 0.02
     e.close()
+
+
+def test_full_size_search_equals_small_engine():
+    """BASELINE configs[2] per-GPU size (16384 games, 8x8, 400 playouts): 64 distinct positions,
+    256 copies of each spread over the slots.  Size-independent properties: every copy of a
+    position ends with the identical tree statistics (games never interact), those statistics equal
+    the same search in a 64-game engine (whose kernels the oracle tests pin), and the per-game
+    visit invariants hold."""
+    w, n, G, P, K = 8, 5, 16384, 400, 64
+    arrs = load_golden_weights("weights_8_8_5")
+    rng = np.random.RandomState(21)
+    _, lists = _random_positions(rng, w, n, K, max_plies=24)
+    small = _engine(w, w, n, n_games=K, n_playout=P)
+    small.set_weights(arrs)
+    for g, mv in enumerate(lists):
+        small.boards_set(g, mv)
+    small.search(P)
+    svis, sq, srn = small.root_visits(want_q=True)
+    small.close()
+    big = _engine(w, w, n, n_games=G, n_playout=P)
+    big.set_weights(arrs)
+    # copy c of position k sits in slot c * K + k: neighbouring slots hold different positions
+    for g in range(G):
+        big.boards_set(g, lists[g % K])
+    big.search(P)
+    vis, q, rn = big.root_visits(want_q=True)
+    ctr = big.counters()
+    overflows = big.selfplay_stats()["pool_overflows"]
+    big.close()
+    assert (rn == P).all()
+    assert (np.maximum(vis, 0).sum(axis=1) == P - 1).all()
+    v3, q3 = vis.reshape(G // K, K, -1), q.reshape(G // K, K, -1)
+    assert (v3 == v3[0]).all() and (q3 == q3[0]).all()         # replica invariance, bit for bit
+    assert np.array_equal(v3[0], svis) and np.array_equal(q3[0], sq)  # == the small engine
+    for k, mv in enumerate(lists):                             # children are exactly the empty cells
+        legal = np.ones(w * w, bool); legal[mv] = False
+        assert ((vis[k] >= 0) == legal).all()
+    assert ctr["playouts"] == G * P and overflows == 0
+
+
+def test_full_size_selfplay_records_are_legal_games():
+    """16384 concurrent self-play games (8x8, 40 playouts to keep it short): every finished game
+    replays legally through the oracle rules to the recorded winner, z follows game.py:396-399,
+    sample count = sum of game lengths, game ids are unique."""
+    from oracle import orc
+    w, n, G, P = 8, 5, 16384, 40
+    e = _engine(w, w, n, n_games=G, n_playout=P, seed=9)
+    e.set_weights(load_golden_weights("weights_8_8_5"))
+    e.selfplay_begin(temp=1.0, recycle=True)
+    e.selfplay_step(14)
+    games = e.selfplay_drain_games()
+    data = e.selfplay_drain()
+    stats = e.selfplay_stats()
+    e.close()
+    assert stats["pool_overflows"] == 0 and stats["n_plies"] == 14 * G
+    assert len(games) == stats["n_games"] > 0
+    assert len(data["zs"]) == stats["n_samples"] == sum(len(m) for _, _, m in games)
+    gids = [gid for gid, _, _ in games]
+    assert len(set(gids)) == len(gids)
+    zs = {}
+    for gid, ply, z in zip(data["game_ids"], data["plies"], data["zs"]):
+        zs[(int(gid), int(ply))] = float(z)
+    assert abs(data["pis"].sum(axis=1) - 1).max() < 1e-4
+    for gid, win, mv in games[:600]:
+        b = orc.Board(w, w, n)
+        b.init_board(0)
+        for t, m in enumerate(mv):
+            assert not b.game_end()[0]
+            want = 0.0 if win == -1 else (1.0 if b.current_player == win else -1.0)
+            assert zs[(gid, t)] == want
+            b.do_move(m)
+        assert b.game_end() == (True, win)
