@@ -686,6 +686,22 @@ extern "C" int gz_update_with_move(gz_engine *e, const int32_t *moves)
     return a.finish();
 }
 
+extern "C" int gz_set_active(gz_engine *e, const int8_t *mask)
+{
+    if (!e) return GZ_E_INVALID;
+    GZ_CUDA(e, cudaSetDevice(e->cfg.device));
+    if (!mask) {
+        GZ_CUDA(e, cudaMemsetAsync(e->active, 1, e->G, e->stream));
+        return GZ_OK;
+    }
+    ArgStage a(e);
+    GZ_TRY(a.reserve((size_t)e->G + 256));
+    const int8_t *dm = a.in(mask, e->G);
+    if (a.rc) return a.rc;
+    GZ_CUDA(e, cudaMemcpyAsync(e->active, dm, e->G, cudaMemcpyDeviceToDevice, e->stream));
+    return a.finish();
+}
+
 extern "C" int gz_root_select_move(gz_engine *e, float temp, int32_t selfplay, int32_t *moves, float *probs)
 {
     if (!e || !moves || !(temp > 0.f)) return GZ_E_INVALID;

@@ -235,6 +235,14 @@ class Engine:
         mv = np.ascontiguousarray(moves, dtype=np.int32)
         self._ck(self.L.gz_update_with_move(self._h, _ptr(mv)))
 
+    def set_active(self, mask=None):
+        """Slots that take part in the next searches (None = all)."""
+        if mask is None:
+            self._ck(self.L.gz_set_active(self._h, None))
+        else:
+            m = np.ascontiguousarray(np.asarray(mask) != 0, dtype=np.int8)
+            self._ck(self.L.gz_set_active(self._h, _ptr(m)))
+
     def root_select_move(self, temp=1e-3, selfplay=False):
         moves = np.zeros(self.G, np.int32)
         probs = np.zeros((self.G, self.S), np.float32)

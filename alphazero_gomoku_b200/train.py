@@ -129,6 +129,9 @@ class TrainPipeline():
         self.mcts_player = MCTSPlayer(self.policy_value_net.policy_value_fn, c_puct=self.c_puct,
                                       n_playout=self.n_playout, is_selfplay=1)
         self._engine = None
+        self._arena = None
+        self._arena_rounds = 0
+        self.best_model = best_model
         self._engine_version = -1
         self._games_played = 0
         self.last_games = []
@@ -210,6 +213,96 @@ class TrainPipeline():
                      "explained_var_new=%4.3f" % (kl, self.lr_multiplier, loss, entropy, explained_var_old,
                                                   explained_var_new))
         return loss, entropy
+
+    def policy_evaluate(self, n_games=10, player=0):
+        """train.py:216-276: the current policy (player 1) against pure MCTS with
+        pure_mcts_playout_num rollouts (player 2), first move alternating; all n_games are played
+        concurrently on the device.  Returns (wins + 0.5 ties) / n_games."""
+        if player != 0:
+            raise NotImplementedError("the Yixin engine bridge is outside the hot path (SURVEY 2)")
+        n_games = int(n_games)
+        if self._arena is None or self._arena.G != n_games:
+            if self._arena is not None:
+                self._arena.close()
+            self._arena = Engine(width=self.board_width, height=self.board_height, n_in_row=self.n_in_row,
+                                 n_games=n_games, n_playout=max(self.n_playout, self.pure_mcts_playout_num),
+                                 c_puct=float(self.c_puct), seed=self.seed + 7919 + _rank())
+        self._arena.set_weights(self.policy_value_net.get_policy_param())
+        self._arena_rounds += 1
+        winners = arena_play(self._arena, self.n_playout, self.pure_mcts_playout_num,
+                             start_players=np.arange(n_games) % 2, search_salt=1000 * self._arena_rounds)
+        win_cnt = {w: int((winners == w).sum()) for w in (1, 2, -1)}
+        for i, w in enumerate(winners):
+            _logger.info("%d-%d : winner is player%d (start from player%d)" % (n_games, i + 1, w, i % 2 + 1))
+        win_ratio = 1.0 * (win_cnt[1] + 0.5 * win_cnt[-1]) / n_games
+        _logger.info("Win: %d, Lose: %d, Tie: %d" % (win_cnt[1], win_cnt[2], win_cnt[-1]))
+        return win_ratio
+
+    def run(self, eval_games=10):
+        """train.py:278-350 (the self-play branch): collect -> update -> every check_freq batches
+        save, evaluate against pure MCTS, keep the best model and raise the opponent's playouts."""
+        for i in range(self.game_batch_num):
+            self.collect_selfplay_data(n_games=self.play_batch_size, train_data=[])
+            _logger.info("batch %d-%d, episode_len=%02d: " % (self.game_batch_num, i + 1, self.episode_len))
+            if len(self.data_buffer) > self.batch_size:
+                self.policy_update()
+            if (i + 1) % self.check_freq == 0:
+                _logger.info("current self-play batch: %d" % (i + 1))
+                self.policy_value_net.save_model('./current_policy.model')
+                win_ratio = self.policy_evaluate(n_games=eval_games)
+                if win_ratio > self.best_win_ratio:
+                    self.policy_value_net.save_model(self.best_model)
+                    _logger.info("New best policy(%3.2f>%3.2f), save to %s" % (win_ratio, self.best_win_ratio, self.best_model))
+                    self.best_win_ratio = win_ratio
+                    if self.best_win_ratio == 1.0 and self.pure_mcts_playout_num < 5000:
+                        self.pure_mcts_playout_num += 1000
+                        self.best_win_ratio = 0.0
+                        _logger.info("pure_mcts_playout increase to %d" % self.pure_mcts_playout_num)
+        self.policy_value_net.save_model('./current_policy.model')
+
+
+def arena_play(engine, n_playout, pure_playouts, start_players, temp=1e-3, search_salt=0):
+    """Batched Game.start_play (game.py:211-290) of MCTSPlayer (player 1, net-guided, is_selfplay=0)
+    against mcts_pure.MCTSPlayer (player 2, rollouts) in every slot of `engine` at once.
+
+    Both reference players search from a FRESH tree every move (update_with_move(-1),
+    mcts_alphaZero.py:255, mcts_pure.py:268), so one engine serves both: on every ply the slots
+    where player 1 is to move run the net search and the others the rollout search.  The AZ move
+    is sampled from softmax(log(visits)/temp) (np.random.choice(acts, p=probs), :247; the 15x15
+    first-move override :251-253 is applied), the pure move is the most visited child (:230).
+    Returns winners int8[G] (1, 2 or -1 = tie)."""
+    G, S = engine.G, engine.S
+    engine.set_active(None)
+    engine.boards_reset(np.asarray(start_players, np.int8))
+    winners = np.zeros(G, np.int8)
+    done = np.zeros(G, bool)
+    for ply in range(S + 1):
+        st = engine.boards_status()
+        ended = st["ended"].astype(bool)
+        winners[ended & ~done] = st["winner"][ended & ~done]
+        done |= ended
+        if done.all():
+            break
+        moves = np.full(G, -2, np.int32)
+        for who, mask in ((1, ~done & (st["cur_player"] == 1)), (2, ~done & (st["cur_player"] == 2))):
+            if not mask.any():
+                continue
+            engine.set_active(mask)
+            engine.update_with_move(np.where(mask, -1, -2).astype(np.int32))  # fresh trees for the movers
+            if who == 1:
+                engine.search(n_playout)
+                mv, _ = engine.root_select_move(temp=temp, selfplay=False)
+                if engine.width == 15 and engine.height == 15:  # mcts_alphaZero.py:251-253
+                    first = mask & (st["n_stones"] == 0)
+                    mv = np.where(first, np.random.choice([96, 97, 98, 111, 112, 113, 126, 127, 128], size=G), mv)
+            else:
+                engine.pure_search(pure_playouts, search_id=search_salt + ply)
+                mv = engine.pure_best_move()
+            moves[mask] = mv[mask]
+        engine.set_active(None)
+        engine.boards_do_move(moves)
+    engine.update_with_move(np.full(G, -1, np.int32))
+    return winners
 
 
 def _rank():

@@ -132,6 +132,10 @@ int gz_root_visits(gz_engine *e, int32_t *visits /*[G,S], -1 = not a child*/,
  * child re-roots (subtree kept), anything else (e.g. -1) resets to a fresh root.
  * Does NOT touch the boards.                                                             */
 int gz_update_with_move(gz_engine *e, const int32_t *moves);
+/* Which slots take part in the next searches / move choices: mask[G] (0 = sit out), NULL = all.
+ * Used by the batched arena (train.py:216-276 policy_evaluate): the two players of a match search
+ * on alternate plies, each on the games where it is to move.                                */
+int gz_set_active(gz_engine *e, const int8_t *mask);
 /* MCTSPlayer.get_action after the search (mcts_alphaZero.py:212-262): visit counts ->
  * softmax(log(v + 1e-10) / temp) -> (self-play) 0.75 p + 0.25 Dir(alpha) -> sampled move.
  * Writes moves[G] and probs[G,S] (noise-free pi); does not apply the move.               */

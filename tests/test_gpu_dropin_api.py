@@ -196,3 +196,42 @@ def test_collect_selfplay_data_batched():
     assert any(not np.array_equal(a, b) for a, b in zip(before, after))
     tp.collect_selfplay_data(n_games=4)  # the engine picks up the updated weights
     assert len(tp.last_games) == 4
+
+
+def test_batched_arena_policy_evaluate():
+    """TrainPipeline.policy_evaluate (train.py:216-276): every evaluation game runs concurrently on
+    the device, net player vs pure-MCTS rollouts, alternating first move.  The shipped 6x6 policy
+    must beat a weak rollout player clearly; a stronger rollout player must do no worse against
+    the same net than a weaker one does."""
+    from alphazero_gomoku_b200 import Engine, TrainPipeline
+    from alphazero_gomoku_b200.train import arena_play
+    from oracle import orc
+    w, n, G = 6, 4, 64
+    e = Engine(width=w, height=w, n_in_row=n, n_games=G, n_playout=400, seed=5)
+    e.set_weights(load_golden_weights("weights_6_6_4"))
+    start = np.arange(G) % 2
+    winners = arena_play(e, n_playout=200, pure_playouts=100, start_players=start)
+    assert set(np.unique(winners)) <= {1, 2, -1}
+    ratio_weak = ((winners == 1).sum() + 0.5 * (winners == -1).sum()) / G
+    # the boards hold finished, legal games whose winner is what the arena reported
+    st = e.boards_status()
+    assert st["ended"].all() and np.array_equal(st["winner"], winners)
+    cells = e.boards_cells()
+    for g in range(0, G, 7):
+        n1, n2 = int((cells[g] == 1).sum()), int((cells[g] == 2).sum())
+        first, second = (n1, n2) if start[g] == 0 else (n2, n1)
+        assert first - second in (0, 1)           # players alternated, the chosen one moved first
+    winners2 = arena_play(e, n_playout=200, pure_playouts=400, start_players=start, search_salt=77)
+    ratio_strong = ((winners2 == 1).sum() + 0.5 * (winners2 == -1).sum()) / G
+    e.close()
+    print("arena: net(200) vs pure(100): %.3f, vs pure(400): %.3f" % (ratio_weak, ratio_strong))
+    assert ratio_weak >= 0.75
+    assert ratio_strong <= ratio_weak + 0.1
+    # through the reference-shaped entry point
+    tp = TrainPipeline({"board_width": 6, "board_height": 6, "n_in_row": 4, "n_playout": 100,
+                        "pure_mcts_playout_num": 60}, seed=2)
+    tp.policy_value_net.set_policy_param(load_golden_weights("weights_6_6_4"))
+    r = tp.policy_evaluate(n_games=16)
+    assert 0.5 <= r <= 1.0
+    with pytest.raises(NotImplementedError):
+        tp.policy_evaluate(n_games=2, player=1)
