@@ -1,39 +1,24 @@
-"""Profiling aid: per-phase clock64 timeline of CTA 0 of the tcgen05 trunk (GZ_TC_TIMELINE)."""
-import os
+"""Summarise a GZ_TC_TIMELINE dump (front-warp marks, per-CTA wall times, MMA-warp marks)."""
+import re
+import statistics as st
 import sys
 
-import numpy as np
-
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
-out = sys.argv[1] if len(sys.argv) > 1 else "gpurun_out/tc_timeline.txt"
-w = int(sys.argv[2]) if len(sys.argv) > 2 else 8
-B = int(sys.argv[3]) if len(sys.argv) > 3 else 16384
-if os.path.exists(out):
-    os.remove(out)
-os.environ["GZ_TC_TIMELINE"] = out
-from alphazero_gomoku_b200 import Engine
-from alphazero_gomoku_b200.engine import weight_shapes
-
-rng = np.random.RandomState(0)
-arrs = [(rng.randn(*s) * 0.05).astype(np.float32) for s in weight_shapes(w, w)]
-e = Engine(width=w, height=w, n_in_row=3, net_impl=2)
-e.set_weights(arrs)
-planes = (rng.rand(B, 4, w, w) < 0.3).astype(np.float32)
-import torch
-xp = torch.from_numpy(planes).cuda()
-for _ in range(3):
-    e.net_forward(xp)
-e.sync()
-names = ["conv2_mma", "ep2+stage_next", "conv1_next+ep1", "wait_conv3_issue"]
-rows = []
-for blk in open(out).read().split("launch")[1:]:
-    lines = [l for l in blk.strip().splitlines()[1:] if l.strip()]
-    t = np.array([[int(x) for x in l.split()] for l in lines if len(l.split()) == 4])
-    rows.append(t)
-t = rows[-1]
-d = np.diff(t.reshape(-1))
-d = np.append(d, 0).reshape(-1, 4)[:-1]  # drop the last (partial) group
-print("groups", len(t), "cycles/group", (t[-1, 0] - t[0, 0]) / (len(t) - 1))
-for i, n in enumerate(names):
-    print("%-10s mean %8.0f  min %8.0f  max %8.0f" % (n, d[1:, i].mean(), d[1:, i].min(), d[1:, i].max()))
+txt = open(sys.argv[1]).read().strip().split('launch ')
+blk = [b for b in txt if b.startswith('B=')][-1]
+front, rest = blk.split('cta_ns')
+cta, mma = rest.split('mma')
+F = [list(map(int, l.split())) for l in front.splitlines()[1:] if len(l.split()) == 4]
+M = [list(map(int, l.split())) for l in mma.splitlines() if len(l.split()) == 7]
+med = lambda x: int(st.median(x))
+print(blk.splitlines()[0])
+print('group period (cycles)', med([F[i + 1][0] - F[i][0] for i in range(5, len(F) - 2)]))
+print('front: wait conv2 %d | ep2 + stage next %d | ep1 next %d | idle %d' % (
+    med([f[1] - f[0] for f in F[5:-2]]), med([f[2] - f[1] for f in F[5:-2]]), med([f[3] - f[2] for f in F[5:-2]]),
+    med([F[i + 1][0] - F[i][3] for i in range(5, len(F) - 2)])))
+names = ['issue conv2', 'barrier A (ep2 half 0)', 'wait conv3 accum free', 'conv3 st 0-3 + barrier B', 'conv1 next + conv3 st 4-17',
+         'barrier C (ep1 next)']
+for k in range(6):
+    print('mma  %-28s %6d' % (names[k], med([m[k + 1] - m[k] for m in M[5:-2]])))
+vals = [(int(a), int(b)) for a, b in re.findall(r'(-?\d+):(-?\d+)', cta.split('duration)')[1])]
+d = [v[1] for v in vals]
+print('per-CTA wall time ns: min %d median %d max %d (n=%d)' % (min(d), st.median(d), max(d), len(d)))
