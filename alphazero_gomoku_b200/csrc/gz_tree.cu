@@ -311,7 +311,7 @@ expand_backup_kernel(TreeParams p, const float *__restrict__ priors, const float
     gz_expand_backup_game(p, g, lane, priors, values, compacted);
 }
 
-// Fused wave boundary for boards of up to 64 cells (NSL = Sp / 32 child slots per lane), written
+// Fused wave boundary (NSL = Sp / 32 child slots per lane, instantiated for 1-4 and 8), written
 // around the number of dependent memory round trips, which is what bounds these kernels:
 //   trip 1  everything addressed by the game index alone (flags, path length, leaf slot, root,
 //           free-list top, both positions, this lane's path entry)
@@ -542,7 +542,7 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
 }
 
 template <int NSL, int WT>
-__global__ void __launch_bounds__(128, 8)
+__global__ void __launch_bounds__(128, NSL <= 2 ? 8 : (NSL <= 4 ? 5 : 3))
 expand_select_small_kernel(TreeParams p, const float *__restrict__ priors, const float *__restrict__ values)
 {
     const int lane = threadIdx.x & 31;
@@ -714,10 +714,19 @@ int gzk_expand_select(gz_engine *e, const float *d_priors, const float *d_values
     const unsigned grid = gz_warp_blocks(e->G, 4);
     const TreeParams tp = gz_tree_params(e);
     const bool sq = e->W == e->H;
-    if (e->Sp == 64 && sq && e->W == 8) expand_select_small_kernel<2, 8><<<grid, 128, 0, e->stream>>>(tp, d_priors, d_values);
-    else if (e->Sp == 64 && sq && e->W == 6) expand_select_small_kernel<2, 6><<<grid, 128, 0, e->stream>>>(tp, d_priors, d_values);
-    else if (e->Sp == 64) expand_select_small_kernel<2, 0><<<grid, 128, 0, e->stream>>>(tp, d_priors, d_values);
-    else if (e->Sp == 32) expand_select_small_kernel<1, 0><<<grid, 128, 0, e->stream>>>(tp, d_priors, d_values);
+    // round-trip-minimal kernel: NSL = Sp / 32 child slots per lane, board side compile-time for the
+    // reference's usual sizes; other sizes take the generic fused kernel
+#define GZ_ES(NSL, WT) expand_select_small_kernel<NSL, WT><<<grid, 128, 0, e->stream>>>(tp, d_priors, d_values)
+    if (e->Sp == 64 && sq && e->W == 8) GZ_ES(2, 8);
+    else if (e->Sp == 64 && sq && e->W == 6) GZ_ES(2, 6);
+    else if (e->Sp == 64) GZ_ES(2, 0);
+    else if (e->Sp == 32) GZ_ES(1, 0);
+    else if (e->Sp == 96 && sq && e->W == 9) GZ_ES(3, 9);
+    else if (e->Sp == 96) GZ_ES(3, 0);
+    else if (e->Sp == 128) GZ_ES(4, 0);
+    else if (e->Sp == 256 && sq && e->W == 15) GZ_ES(8, 15);
+    else if (e->Sp == 256) GZ_ES(8, 0);
+#undef GZ_ES
     else expand_select_kernel<<<grid, 128, 0, e->stream>>>(tp, d_priors, d_values);
     e->launches++;
     GZ_CUDA(e, cudaGetLastError());

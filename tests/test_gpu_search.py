@@ -167,7 +167,8 @@ def test_search_with_net_vs_oracle_many_games():
     e.close()
 
 
-@pytest.mark.parametrize("w,n,G,P", [(8, 5, 200, 150), (6, 4, 96, 120), (5, 4, 64, 80), (9, 5, 40, 60)])
+@pytest.mark.parametrize("w,n,G,P", [(8, 5, 200, 150), (6, 4, 96, 120), (5, 4, 64, 80), (9, 5, 40, 60), (11, 5, 24, 40),
+                                     (15, 5, 12, 40), (13, 5, 8, 30), (7, 4, 32, 60)])
 def test_fused_wave_kernel_matches_split_kernels(w, n, G, P):
     """gz_search (fused expand+backup+select kernel across the wave boundary, its low-latency
     variant on boards of up to 64 cells) against the same search driven wave by wave through
