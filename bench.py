@@ -342,6 +342,12 @@ def run_ours(args):
         roof = {"bound": "tensor", "kernel": dom, "unit": "TFLOP/s", "peak": pk["bf16_tflops_sustained"],
                 "peak_source": pk_src + ", sustained bf16 (kernel timed inside a long step)",
                 "traffic": None}
+        # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
+        # (profiles/r1_ncu_v5_summary.txt: dram__bytes_read.sum + dram__bytes_write.sum, one launch,
+        # 16384 leaves at 8x8); only quoted for the configuration it was captured on
+        if dom == "trunk_tc" and args.board == 8 and args.games == 16384:
+            roof["traffic"] = 17244160 + 8448
+            roof["traffic_source"] = "profiles/r1_ncu_v5_summary.txt (ncu --set full, 1 launch; algorithmic input planes 16.8 MB)"
         if dom in fl and dom_ms > 0:
             ach = ctr["leaf_evals"] * fl[dom] / (dom_ms * 1e-3) / 1e12
             roof.update({"achieved": ach, "frac": ach / pk["bf16_tflops_sustained"],
