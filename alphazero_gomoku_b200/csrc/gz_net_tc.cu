@@ -6,8 +6,10 @@
 //                     tcgen05.mma (M = 128 board cells, N = Cout, K = 16 channels of one filter tap),
 //                     accumulators in TMEM, weights streamed by the bulk-copy engine (cp.async.bulk,
 //                     the TMA unit) through a 4-slot mbarrier ring.
-//   heads_fc_kernel   policy FC + softmax, value FC1 + ReLU + FC2 + tanh in fp32 on CUDA cores over
-//                     tiles of boards (the FC weights of a tile are read once per tile, not per board).
+//                     Warp roles: 8 front epilogue warps, 1 MMA warp, 1 bulk-copy warp, 8 back-end
+//                     warps; software pipeline across groups.
+//   heads_tc_kernel   policy FC + softmax, value FC1 + ReLU + FC2 + tanh as two tcgen05 GEMMs per
+//                     tile of 128 boards; its A operand is written by the trunk's back end.
 //
 // Implicit GEMM without im2col.  A board lives in shared memory as rows of a padded line space:
 // cell (i, j) -> row i * P + j with P = W + 1 (one always-zero column separates board rows) and

@@ -7,6 +7,9 @@
 //      walks the recorded path updating N and the running-mean Q with alternating sign
 //      (update_recursive, mcts_alphaZero.py:57-73).  One playout in flight per game, so the
 //      tree sees exactly the reference's sequential statistics.
+//   K2+K1 fused across the wave boundary (expand_select*_kernel): the expand + backup of playout k
+//      and the descent of playout k+1 by the same warp, organised around dependent memory round
+//      trips; bit-identical to running K2 then K1.
 //   re-root with subtree reuse (update_with_move, :183-192) frees the discarded nodes onto a
 //      per-game free stack that doubles as the BFS queue.
 #include "gz_engine.h"
