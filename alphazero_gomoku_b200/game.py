@@ -108,79 +108,70 @@ class Board(object):
 
 
 class Game(object):
-    """game server (game.py:175-416)"""
+    """Match / self-play driver with the reference's entry points (game.py:175-416).  Everything
+    that touches the rules goes through the Board above, i.e. through the device library."""
 
     def __init__(self, board, **kwargs):
         self.board = board
 
     def graphic(self, board, player1, player2):
-        width, height = board.width, board.height
-        print("Player", player1, "with X".rjust(3))
-        print("Player", player2, "with O".rjust(3))
-        print()
-        print('\r\n')
-        for i in range(height - 1, -1, -1):
-            print("%4d" % i, end='')
-            for j in range(width):
-                p = board.states.get(i * width + j, -1)
-                print("%2s" % ('X' if p == player1 else 'O' if p == player2 else '-'), end=' ')
-            print('')
-        print("%4s" % ' ', end='')
-        for x in range(width):
-            print("%2d" % x, end=' ')
-        print('\r\n')
+        """Text rendering in the reference's format (game.py:183-209): X / O / - grid, top row first."""
+        marks = {player1: 'X', player2: 'O'}
+        out = ["Player %s %s" % (player1, "with X".rjust(3)), "Player %s %s" % (player2, "with O".rjust(3)), "", "\r\n"]
+        for row in reversed(range(board.height)):
+            cells = (marks.get(board.states.get(row * board.width + col, -1), '-') for col in range(board.width))
+            out.append("%4d" % row + "".join("%2s " % c for c in cells))
+        out.append("%4s" % ' ' + "".join("%2d " % col for col in range(board.width)) + "\r\n")
+        print("\n".join(out))
+
+    def _finished(self, show, *who):
+        if show:
+            self.graphic(self.board, *who)
+        return self.board.game_end()
 
     def start_play(self, player1, player2, start_player=0, is_shown=1):
-        """game.py:211-290: a match between two players; returns the winner (1, 2 or -1)."""
+        """game.py:211-290: a match between two player objects; returns the winner (1, 2 or -1) and
+        logs the move list in the reference's `{'steps': ...}` format."""
         if start_player not in (0, 1):
             raise Exception('start_player should be either 0 (player1 first) '
                             'or 1 (player2 first)')
-        play_steps = []
         self.board.init_board(start_player)
-        p1, p2 = self.board.players
-        player1.set_player_ind(p1)
-        player2.set_player_ind(p2)
-        players = {p1: player1, p2: player2}
+        seat = dict(zip(self.board.players, (player1, player2)))
+        for ind, pl in seat.items():
+            pl.set_player_ind(ind)
+        shown = (player1.player, player2.player)
         if is_shown:
-            self.graphic(self.board, player1.player, player2.player)
-        while True:
-            current_player = self.board.get_current_player()
-            move = players[current_player].get_action(self.board)
-            play_steps.append(move)
-            self.board.do_move(move)
-            if is_shown:
-                self.graphic(self.board, player1.player, player2.player)
-            end, winner = self.board.game_end()
-            if end:
-                winner_r = winner
-                if start_player == 1:
-                    winner_r = 2 if winner == 1 else 1
-                _logger.warning("{'steps':[%s],'winner':%d,'start_player':%d}"
-                                % (",".join(map(str, play_steps)), winner_r, start_player + 1))
-                return winner
+            self.graphic(self.board, *shown)
+        record = []
+        ended, winner = False, -1
+        while not ended:
+            mover = seat[self.board.get_current_player()]
+            record.append(mover.get_action(self.board))
+            self.board.do_move(record[-1])
+            ended, winner = self._finished(is_shown, *shown)
+        # the log names the winner by seat order of the opening move (game.py:275-288)
+        logged = winner if start_player == 0 else (2 if winner == 1 else 1)
+        _logger.warning("{'steps':[%s],'winner':%d,'start_player':%d}"
+                        % (",".join(map(str, record)), logged, start_player + 1))
+        return winner
 
     def start_self_play(self, player, is_shown=0, temp=1e-3):
-        """game.py:360-416: one self-play game; returns (winner, zip(states, mcts_probs, winners_z))."""
+        """game.py:360-416: one self-play game of `player` against itself; returns
+        (winner, zip(states, mcts_probs, winners_z)), z from each mover's point of view."""
         self.board.init_board()
-        p1, p2 = self.board.players
-        states, mcts_probs, current_players, moves = [], [], [], []
-        while True:
-            move, move_probs = player.get_action(self.board, temp=temp, return_prob=1)
-            states.append(self.board.current_state())
-            mcts_probs.append(move_probs)
-            current_players.append(self.board.current_player)
-            moves.append(move)
+        trace = []  # (state, pi, mover, move) per ply
+        ended, winner = False, -1
+        while not ended:
+            move, pi = player.get_action(self.board, temp=temp, return_prob=1)
+            trace.append((self.board.current_state(), pi, self.board.current_player, move))
             self.board.do_move(move)
-            if is_shown:
-                self.graphic(self.board, p1, p2)
-            end, winner = self.board.game_end()
-            if end:
-                winners_z = np.zeros(len(current_players))
-                if winner != -1:
-                    winners_z[np.array(current_players) == winner] = 1.0
-                    winners_z[np.array(current_players) != winner] = -1.0
-                player.reset_player()
-                if is_shown:
-                    print("Game end. Winner is player:", winner) if winner != -1 else print("Game end. Tie")
-                _logger.warning("{'steps':[%s],'winner':%d}" % (",".join(map(str, moves)), winner))
-                return winner, zip(states, mcts_probs, winners_z)
+            ended, winner = self._finished(is_shown, *self.board.players)
+        movers = np.array([t[2] for t in trace])
+        winners_z = np.zeros(len(trace))
+        if winner != -1:
+            winners_z = np.where(movers == winner, 1.0, -1.0)
+        player.reset_player()
+        if is_shown:
+            print("Game end. Winner is player:", winner) if winner != -1 else print("Game end. Tie")
+        _logger.warning("{'steps':[%s],'winner':%d}" % (",".join(str(t[3]) for t in trace), winner))
+        return winner, zip([t[0] for t in trace], [t[1] for t in trace], winners_z)
