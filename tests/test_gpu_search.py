@@ -443,3 +443,43 @@ def test_full_size_selfplay_records_are_legal_games():
             assert zs[(gid, t)] == want
             b.do_move(m)
         assert b.game_end() == (True, win)
+
+
+def test_degenerate_batches_do_not_disturb_other_games():
+    """Edge cases of the wave machinery: an empty net batch, slots whose root is already terminal
+    (won / full board: every playout ends at the root and no leaf reaches the net) next to a live
+    game, and a wave in which no game needs the net at all."""
+    w, n, P = 6, 4, 50
+    arrs = load_golden_weights("weights_6_6_4")
+    e = _engine(w, w, n, n_games=4, n_playout=P)
+    e.set_weights(arrs)
+    probs, vals = e.net_forward(np.zeros((0, 4, w, w), np.float32))
+    assert probs.shape == (0, w * w) and vals.shape == (0,)
+    won = [0, 6, 1, 7, 2, 8, 3]                      # player 1 completes 0-1-2-3
+    live = [14, 15, 20]
+    e.boards_set(0, won)
+    e.boards_set(1, live)
+    e.boards_set(2, won)
+    e.boards_set(3, live)
+    st = e.boards_status()
+    assert list(st["ended"]) == [1, 0, 1, 0] and st["winner"][0] == 1
+    e.search(P)
+    vis, rn = e.root_visits()
+    assert (vis[0] == -1).all() and (vis[2] == -1).all()          # terminal roots never expand
+    assert rn[0] == P and rn[2] == P
+    assert np.array_equal(vis[1], vis[3]) and np.maximum(vis[1], 0).sum() == P - 1
+    alone = _engine(w, w, n, n_games=1, n_playout=P)
+    alone.set_weights(arrs)
+    alone.boards_set(0, live)
+    alone.search(P)
+    v1, _ = alone.root_visits()
+    assert np.array_equal(v1[0], vis[1])
+    alone.close()
+    # now only terminal roots are left active: waves with an empty leaf batch
+    e.boards_set(1, won)
+    e.boards_set(3, won)
+    e.update_with_move(np.full(4, -1, np.int32))
+    e.search(7)
+    vis, rn = e.root_visits()
+    assert (vis == -1).all() and (rn == 7).all()
+    e.close()
