@@ -736,40 +736,74 @@ heads_tc_kernel(const uint8_t *__restrict__ head_act, FcTc w, float *__restrict_
         tc_mbar_wait(bar_done, 0);
         tc_fence_after();
         const int nchunk = (S + 31) >> 5;
-        float mx = -3.0e38f;
-        for (int ch = 0; ch < nchunk; ++ch) {
-            uint32_t v[32];
-            tc_tmem_ld32(tmem + t_lane + TM_P + ch * 32, v);
-#pragma unroll
-            for (int c = 0; c < 32; ++c)
-                if (ch * 32 + c < S) mx = fmaxf(mx, fmaf(__uint_as_float(v[c]), w.inv_p, s_bp[ch * 32 + c]));
-        }
-        float sum = 0.f;
-        for (int ch = 0; ch < nchunk; ++ch) {
-            uint32_t v[32];
-            tc_tmem_ld32(tmem + t_lane + TM_P + ch * 32, v);
-#pragma unroll
-            for (int c = 0; c < 32; ++c)
-                if (ch * 32 + c < S) sum += expf(fmaf(__uint_as_float(v[c]), w.inv_p, s_bp[ch * 32 + c]) - mx);
-        }
-        const float inv = 1.f / sum;
         float *prow = probs + board * S;
         const bool vec = (S & 3) == 0 && (reinterpret_cast<uintptr_t>(probs) & 15) == 0;
-        for (int ch = 0; ch < nchunk; ++ch) {
-            uint32_t v[32];
-            tc_tmem_ld32(tmem + t_lane + TM_P + ch * 32, v);
-            float p[32];
+        if (S <= 64) {
+            // the whole row of logits fits in registers: one pass over TMEM
+            float x[64];
 #pragma unroll
-            for (int c = 0; c < 32; ++c) p[c] = expf(fmaf(__uint_as_float(v[c]), w.inv_p, s_bp[ch * 32 + c]) - mx) * inv;
+            for (int ch = 0; ch < 2; ++ch) {
+                uint32_t v[32];
+                tc_tmem_ld32(tmem + t_lane + TM_P + ch * 32, v);
+#pragma unroll
+                for (int c = 0; c < 32; ++c)
+                    x[ch * 32 + c] = (ch * 32 + c < S) ? fmaf(__uint_as_float(v[c]), w.inv_p, s_bp[ch * 32 + c]) : -3.0e38f;
+            }
+            float mx = x[0];
+#pragma unroll
+            for (int c = 1; c < 64; ++c) mx = fmaxf(mx, x[c]);
+            float sum = 0.f;
+#pragma unroll
+            for (int c = 0; c < 64; ++c) {
+                x[c] = __expf(x[c] - mx); // padding columns: exp(-huge) = 0
+                sum += x[c];
+            }
+            const float inv = 1.f / sum;
             if (valid) {
                 if (vec) {
 #pragma unroll
-                    for (int c = 0; c < 32; c += 4)
-                        if (ch * 32 + c < S) *reinterpret_cast<float4 *>(prow + ch * 32 + c) = make_float4(p[c], p[c + 1], p[c + 2], p[c + 3]);
+                    for (int c = 0; c < 64; c += 4)
+                        if (c < S) *reinterpret_cast<float4 *>(prow + c) = make_float4(x[c] * inv, x[c + 1] * inv, x[c + 2] * inv, x[c + 3] * inv);
                 } else {
 #pragma unroll
-                    for (int c = 0; c < 32; ++c)
-                        if (ch * 32 + c < S) prow[ch * 32 + c] = p[c];
+                    for (int c = 0; c < 64; ++c)
+                        if (c < S) prow[c] = x[c] * inv;
+                }
+            }
+        } else {
+            float mx = -3.0e38f;
+            for (int ch = 0; ch < nchunk; ++ch) {
+                uint32_t v[32];
+                tc_tmem_ld32(tmem + t_lane + TM_P + ch * 32, v);
+#pragma unroll
+                for (int c = 0; c < 32; ++c)
+                    if (ch * 32 + c < S) mx = fmaxf(mx, fmaf(__uint_as_float(v[c]), w.inv_p, s_bp[ch * 32 + c]));
+            }
+            float sum = 0.f;
+            for (int ch = 0; ch < nchunk; ++ch) {
+                uint32_t v[32];
+                tc_tmem_ld32(tmem + t_lane + TM_P + ch * 32, v);
+#pragma unroll
+                for (int c = 0; c < 32; ++c)
+                    if (ch * 32 + c < S) sum += __expf(fmaf(__uint_as_float(v[c]), w.inv_p, s_bp[ch * 32 + c]) - mx);
+            }
+            const float inv = 1.f / sum;
+            for (int ch = 0; ch < nchunk; ++ch) {
+                uint32_t v[32];
+                tc_tmem_ld32(tmem + t_lane + TM_P + ch * 32, v);
+                float p[32];
+#pragma unroll
+                for (int c = 0; c < 32; ++c) p[c] = __expf(fmaf(__uint_as_float(v[c]), w.inv_p, s_bp[ch * 32 + c]) - mx) * inv;
+                if (valid) {
+                    if (vec) {
+#pragma unroll
+                        for (int c = 0; c < 32; c += 4)
+                            if (ch * 32 + c < S) *reinterpret_cast<float4 *>(prow + ch * 32 + c) = make_float4(p[c], p[c + 1], p[c + 2], p[c + 3]);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < 32; ++c)
+                            if (ch * 32 + c < S) prow[ch * 32 + c] = p[c];
+                    }
                 }
             }
         }
