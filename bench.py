@@ -188,6 +188,8 @@ def workload_config(args, wname, games):
             "board": args.board, "n_in_row": args.n_in_row, "n_playout": args.playouts, "games_per_gpu": games,
             "c_puct": 5, "temp": 1.0, "dirichlet": [0.1, 0.25], "weights": wname,
             "step": "one self-play ply in every game (n_playout waves + move choice + record + re-root)",
+            "phase": "steady state: %d untimed prefill plies before the warm-up, so the recycled slots sit at mixed "
+                     "game phases (SURVEY 8d C3)" % args.prefill_plies,
             "l2": "inputs larger than L2 (tree pool >> 126 MB)"}
 
 
@@ -226,9 +228,22 @@ def run_ours(args):
         if world > 1:
             dist.barrier()
 
+    # Setup (untimed): bring the slots to the steady state BASELINE's C3 measurement asks for (SURVEY 8d:
+    # "every slot finishes >= 1 game ... steady state").  Games that all start together are in
+    # lock-step for the first plies; after a prefill of about one and a half mean game lengths the
+    # recycled slots are spread over all game phases, which is what a long self-play run looks like.
+    done_prefill = 0
+    while done_prefill < args.prefill_plies:
+        k = min(8, args.prefill_plies - done_prefill)
+        eng.selfplay_step(k)
+        eng.selfplay_drain()
+        eng.selfplay_drain_games()
+        done_prefill += k
     for _ in range(args.warmup):
         eng.selfplay_step(1)
     eng.sync()
+    eng.selfplay_drain()
+    eng.selfplay_drain_games()
     eng.selfplay_stats(reset=True)
     eng.counters(reset=True)
     eng.profile_read(reset=True)
@@ -379,9 +394,9 @@ def run_ours(args):
                     "ms_per_step": e2e_ms_max / max(args.steps, 1),
                     "net_evals_per_playout": float(ctr2["leaf_evals"]) / max(float(ctr2["playouts"]), 1.0),
                     "what": "per step: gz_set_weights from pinned host arrays, gz_selfplay_step(1), "
-                            "gz_selfplay_last + gz_selfplay_drain into host buffers; these steps are the plies "
-                            "AFTER the device-timed ones (later game phase: more playouts end in terminal "
-                            "positions, which need no net evaluation - compare net_evals_per_playout)"},
+                            "gz_selfplay_last + gz_selfplay_drain into host buffers; these steps follow the "
+                            "device-timed ones in the same games (net_evals_per_playout says how many playouts "
+                            "needed the net: terminal leaves do not)"},
             "gpu_launches": int(tot_launch),
             "clocks": clocks,
             "roofline": roof,
@@ -425,6 +440,9 @@ def main():
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--cpu-plies", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--prefill-plies", type=int, default=24,
+                    help="untimed setup plies before the warm-up that bring the slots to mixed game phases (0 = time the "
+                         "opening plies of synchronised games)")
     ap.add_argument("--nodes-per-game", type=int, default=0, help="tree pool blocks per game (0 = engine default)")
     ap.add_argument("--generation-plies", type=int, default=48,
                     help="after the timed regions, play up to this many more plies (until every slot finished a game) "
