@@ -85,6 +85,7 @@ _PROTOS = {
     "gz_root_visits": (C.c_int, [_P, _P, _P, _P]),
     "gz_update_with_move": (C.c_int, [_P, _P]),
     "gz_set_active": (C.c_int, [_P, _P]),
+    "gz_equi_data": (C.c_int, [_P, _P, _P, _P, C.c_int64, _P, _P, _P]),
     "gz_root_select_move": (C.c_int, [_P, C.c_float, C.c_int32, _P, _P]),
     "gz_selfplay_begin": (C.c_int, [_P, C.c_float, C.c_int32]),
     "gz_selfplay_step": (C.c_int, [_P, C.c_int32]),

@@ -998,3 +998,5 @@ extern "C" int gz_profile_read(gz_engine *e, double *ms, int64_t *launches, int3
     }
     return GZ_OK;
 }
+
+#include "gz_augment.cu"

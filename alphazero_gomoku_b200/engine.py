@@ -235,6 +235,27 @@ class Engine:
         mv = np.ascontiguousarray(moves, dtype=np.int32)
         self._ck(self.L.gz_update_with_move(self._h, _ptr(mv)))
 
+    def equi_data(self, states, pis, zs):
+        """The 8 dihedral images of every sample, reference order (train.py:116-135); numpy float32 in
+        and out, or torch cuda tensors in and out (no host round trip)."""
+        if hasattr(states, "data_ptr"):
+            import torch
+            n = states.shape[0]
+            st, pi, z = states.float().contiguous(), pis.float().contiguous(), zs.float().contiguous()
+            os_ = torch.empty((8 * n, 4, self.width, self.height), dtype=torch.float32, device=st.device)
+            op = torch.empty((8 * n, self.S), dtype=torch.float32, device=st.device)
+            oz = torch.empty((8 * n,), dtype=torch.float32, device=st.device)
+        else:
+            st = np.ascontiguousarray(states, dtype=np.float32)
+            pi = np.ascontiguousarray(pis, dtype=np.float32)
+            z = np.ascontiguousarray(zs, dtype=np.float32)
+            n = st.shape[0]
+            os_ = np.zeros((8 * n, 4, self.width, self.height), np.float32)
+            op = np.zeros((8 * n, self.S), np.float32)
+            oz = np.zeros((8 * n,), np.float32)
+        self._ck(self.L.gz_equi_data(self._h, _ptr(st), _ptr(pi), _ptr(z), int(n), _ptr(os_), _ptr(op), _ptr(oz)))
+        return os_, op, oz
+
     def set_active(self, mask=None):
         """Slots that take part in the next searches (None = all)."""
         if mask is None:

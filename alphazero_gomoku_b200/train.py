@@ -153,40 +153,45 @@ class TrainPipeline():
             self._engine_version = self.policy_value_net.version
         return self._engine
 
-    def selfplay_games(self, n_games):
-        """Play n_games concurrently on the device; returns per-game [(state, pi, z), ...] lists
-        (float64 arrays, the reference's dtypes) in slot order plus the move lists."""
+    def _play(self, n_games):
+        """n_games concurrent device games; returns the drained records ordered by (game, ply)."""
         e = self._selfplay_engine(int(n_games))
         e.selfplay_begin(temp=float(self.temp), recycle=False)
-        S = self.board_width * self.board_height
-        for _ in range(S):
+        for _ in range(self.board_width * self.board_height):
             e.selfplay_step(1)
             if e.selfplay_pending()[2] == 0:
                 break
         d = e.selfplay_drain()
         self.last_games = e.selfplay_drain_games()
         order = np.lexsort((d["plies"], d["game_ids"]))
-        games, cur, last = [], None, None
-        for i in order:
-            if d["game_ids"][i] != last:
-                cur = []
-                games.append(cur)
-                last = d["game_ids"][i]
-            cur.append((d["states"][i].astype(np.float64), d["pis"][i].astype(np.float64), float(d["zs"][i])))
         for gid, winner, moves in sorted(self.last_games):
             _logger.warning("{'steps':[%s],'winner':%d}" % (",".join(map(str, moves)), winner))  # game.py:411
-        self._games_played += len(games)
+        self._games_played += len(self.last_games)
+        return e, {k: v[order] for k, v in d.items()}
+
+    def selfplay_games(self, n_games):
+        """Play n_games concurrently on the device; returns per-game [(state, pi, z), ...] lists
+        (float64 arrays, the reference's dtypes) in slot order."""
+        _, d = self._play(n_games)
+        games, last = [], None
+        for i in range(len(d["zs"])):
+            if d["game_ids"][i] != last:
+                games.append([])
+                last = d["game_ids"][i]
+            games[-1].append((d["states"][i].astype(np.float64), d["pis"][i].astype(np.float64), float(d["zs"][i])))
         return games
 
     def collect_selfplay_data(self, n_games=1, train_data=[]):
-        """train.py:137-159 (self-play branch): n_games games -> x8 augmentation -> data_buffer."""
+        """train.py:137-159 (self-play branch): n_games games -> x8 augmentation -> data_buffer.  The
+        games run concurrently and the dihedral images are produced on the device (gz_equi_data);
+        the buffer receives the reference's items in the reference's order (game, ply, image)."""
         if len(train_data) != 0:
             raise NotImplementedError("start_from_train_data (recorded games) is outside the hot path (SURVEY 8f-4)")
-        epi_len = 0
-        for play_data in self.selfplay_games(n_games):
-            epi_len += len(play_data)
-            self.data_buffer.extend(self.get_equi_data(play_data))
-        self.episode_len = epi_len
+        e, d = self._play(n_games)
+        st, pi, z = e.equi_data(d["states"], d["pis"], d["zs"])
+        st, pi = st.astype(np.float64), pi.astype(np.float64)
+        self.data_buffer.extend((st[i], pi[i], float(z[i])) for i in range(len(z)))
+        self.episode_len = len(d["zs"])
         return
 
     def policy_update(self):

@@ -179,6 +179,13 @@ int gz_selfplay_get_stats(gz_engine *e, gz_selfplay_stats *out, int32_t reset);
  * (mcts_alphaZero.py:257-260).                                                             */
 int gz_selfplay_last(gz_engine *e, int32_t *moves, float *probs);
 
+/* TrainPipeline.get_equi_data (train.py:116-135) on the device: the 8 dihedral images of n samples
+ * in the reference's order (quarter turns 1..4, each followed by its left-right mirror).
+ * states float[n,4,W,H], pis float[n,S], zs float[n] -> out_states float[8n,4,W,H],
+ * out_pis float[8n,S], out_zs float[8n].  Square boards; host or device pointers.           */
+int gz_equi_data(gz_engine *e, const float *states, const float *pis, const float *zs, int64_t n,
+                 float *out_states, float *out_pis, float *out_zs);
+
 /* ---- pure MCTS with random rollouts (mcts_pure.py:156-231) ---------------------------- */
 /* n_playout waves of: select -> uniform priors over Board.move_target -> Philox rollout
  * to the end of the game -> backup; search_id salts the Philox counter.                   */

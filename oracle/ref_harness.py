@@ -124,3 +124,33 @@ def random_position(Board, width, height, n_in_row, rng, max_plies=None, start_p
         if b.game_end()[0]:
             break
     return b, moves
+
+
+def train_module():
+    """The reference's train.py imported with the two shims of SURVEY 8c (PyYAML 6 safe_load, the
+    absent keras back end aliased to the pytorch one), from a scratch cwd holding conf/ and logs/."""
+    import shutil
+    import tempfile
+    if "train" in sys.modules and getattr(sys.modules["train"], "__file__", "").startswith(REF_DIR):
+        return sys.modules["train"]
+    import yaml
+    scratch = tempfile.mkdtemp(prefix="gz_ref_train_")
+    shutil.copytree(os.path.join(REF_DIR, "conf"), os.path.join(scratch, "conf"))
+    os.makedirs(os.path.join(scratch, "logs"), exist_ok=True)
+    mytoolkit = _import("mytoolkit")
+    mytoolkit.load_config = lambda *a, **k: yaml.safe_load(open(os.path.join(scratch, "conf", "train_config.yaml")))
+    sys.modules["policy_value_net_keras"] = _import("policy_value_net_pytorch")
+    cwd = os.getcwd()
+    os.chdir(scratch)
+    try:
+        return _import("train")
+    finally:
+        os.chdir(cwd)
+
+
+def equi_data(play_data, width, height):
+    """TrainPipeline.get_equi_data (train.py:116-135) of the live reference."""
+    class _Self(object):
+        board_width, board_height = width, height
+    return train_module().TrainPipeline.get_equi_data(_Self(), play_data)
+

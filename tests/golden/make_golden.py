@@ -275,6 +275,23 @@ def make_rollout():
     save("rollout.npz", **kw)
 
 
+def make_equi():
+    """get_equi_data (train.py:116-135) of the live reference on random samples."""
+    kw = {}
+    rng = np.random.RandomState(17)
+    for w in (6, 8, 9, 15):
+        n = 5
+        states = (rng.rand(n, 4, w, w) < 0.4).astype(np.float64)
+        pis = rng.dirichlet(np.ones(w * w), size=n)
+        zs = rng.choice([-1.0, 0.0, 1.0], size=n)
+        out = rh.equi_data([(states[i], pis[i], zs[i]) for i in range(n)], w, w)
+        kw["w%d_states" % w], kw["w%d_pis" % w], kw["w%d_zs" % w] = states, pis, zs
+        kw["w%d_out_states" % w] = np.array([o[0] for o in out])
+        kw["w%d_out_pis" % w] = np.array([o[1] for o in out])
+        kw["w%d_out_zs" % w] = np.array([o[2] for o in out])
+    save("equi.npz", **kw)
+
+
 if __name__ == "__main__":
     which = sys.argv[1:] or ["weights", "rules", "corpus", "net", "mcts", "rollout"]
     weights = make_weights() if "weights" in which or "net" in which or "mcts" in which else None
@@ -283,3 +300,4 @@ if __name__ == "__main__":
     if "net" in which: make_net(weights)
     if "mcts" in which: make_mcts(weights)
     if "rollout" in which: make_rollout()
+    if "equi" in which: make_equi()

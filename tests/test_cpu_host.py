@@ -182,3 +182,16 @@ def test_bench_reference_arm_contract():
     assert line["impl"] == "reference" and line["metric"] == "mcts_playouts_per_sec" and line["value"] > 0
     assert line["cpu_baseline"]["kind"] in ("port", "reference") and line["cpu_baseline"]["cores"] >= 1
     assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["e2e"]["d2h_bytes_per_step"] == 0
+
+
+def test_equi_data_host_vs_reference_golden():
+    """train.equi_data (host mirror of train.py:116-135) against fixtures generated by the live
+    reference's TrainPipeline.get_equi_data (tests/golden/make_golden.py equi)."""
+    from alphazero_gomoku_b200.train import equi_data
+    z = np.load(os.path.join(ROOT, "tests", "golden", "equi.npz"))
+    for w in (6, 8, 9, 15):
+        st, pi, zs = z["w%d_states" % w], z["w%d_pis" % w], z["w%d_zs" % w]
+        out = equi_data([(st[i], pi[i], zs[i]) for i in range(len(zs))], w, w)
+        assert np.array_equal(np.array([o[0] for o in out]), z["w%d_out_states" % w])
+        assert np.array_equal(np.array([o[1] for o in out]), z["w%d_out_pis" % w])
+        assert np.array_equal(np.array([o[2] for o in out]), z["w%d_out_zs" % w])

@@ -235,3 +235,37 @@ def test_batched_arena_policy_evaluate():
     assert 0.5 <= r <= 1.0
     with pytest.raises(NotImplementedError):
         tp.policy_evaluate(n_games=2, player=1)
+
+
+def test_device_equi_data_vs_reference_golden():
+    """gz_equi_data (the 8 dihedral images on the device) against the live reference's
+    get_equi_data fixtures: a pure permutation, so bit-exact; host and device (torch) pointers."""
+    import torch
+    from alphazero_gomoku_b200 import Engine
+    z = np.load(os.path.join(GOLDEN, "equi.npz"))
+    for w in (6, 8, 9, 15):
+        e = Engine(width=w, height=w, n_in_row=3, n_games=1, n_playout=1, nodes_per_game=4)
+        st, pi, zs = z["w%d_states" % w], z["w%d_pis" % w], z["w%d_zs" % w]
+        os_, op, oz = e.equi_data(st, pi, zs)
+        assert np.array_equal(os_, z["w%d_out_states" % w].astype(np.float32))
+        assert np.array_equal(op, z["w%d_out_pis" % w].astype(np.float32))
+        assert np.array_equal(oz, z["w%d_out_zs" % w].astype(np.float32))
+        ts, tp_, tz = (torch.from_numpy(a.astype(np.float32)).cuda() for a in (st, pi, zs))
+        ds, dp, dz = e.equi_data(ts, tp_, tz)
+        assert np.array_equal(ds.cpu().numpy(), os_) and np.array_equal(dp.cpu().numpy(), op)
+        assert np.array_equal(dz.cpu().numpy(), oz)
+        # a large ragged batch through the grid-stride path
+        rng = np.random.RandomState(w)
+        n = 3001
+        bs = (rng.rand(n, 4, w, w) < 0.3).astype(np.float32)
+        bp = rng.rand(n, w * w).astype(np.float32)
+        bz = rng.choice([-1.0, 0.0, 1.0], size=n).astype(np.float32)
+        gs, gp, gz_ = e.equi_data(bs, bp, bz)
+        from alphazero_gomoku_b200.train import equi_data
+        for i in (0, 1499, 3000):
+            ref = equi_data([(bs[i], bp[i], bz[i])], w, w)
+            assert np.array_equal(gs[8 * i:8 * i + 8], np.array([r[0] for r in ref]))
+            assert np.array_equal(gp[8 * i:8 * i + 8], np.array([r[1] for r in ref]))
+            assert (gz_[8 * i:8 * i + 8] == bz[i]).all()
+        assert e.equi_data(bs[:0], bp[:0], bz[:0])[0].shape[0] == 0
+        e.close()
