@@ -86,6 +86,12 @@ _PROTOS = {
     "gz_update_with_move": (C.c_int, [_P, _P]),
     "gz_set_active": (C.c_int, [_P, _P]),
     "gz_equi_data": (C.c_int, [_P, _P, _P, _P, C.c_int64, _P, _P, _P]),
+    "gz_train_step": (C.c_int, [_P, _P, _P, _P, C.c_int64, C.c_float, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "gz_train_backward": (C.c_int, [_P, _P, _P, _P, C.c_int64, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "gz_train_grads": (C.c_int, [_P, _P, C.c_int64, C.POINTER(C.c_int64)]),
+    "gz_train_apply": (C.c_int, [_P, _P, C.c_float]),
+    "gz_train_forward": (C.c_int, [_P, _P, C.c_int64, _P, _P]),
+    "gz_train_reset": (C.c_int, [_P]),
     "gz_root_select_move": (C.c_int, [_P, C.c_float, C.c_int32, _P, _P]),
     "gz_selfplay_begin": (C.c_int, [_P, C.c_float, C.c_int32]),
     "gz_selfplay_step": (C.c_int, [_P, C.c_int32]),

@@ -12,6 +12,10 @@
 #include "gz_move.cu"
 #include "gz_net_ffma.cu"
 
+static int gz_train_flush(gz_engine *e); // gz_train.cu
+static void gz_train_free(gz_engine *e);
+static void gz_train_invalidate(gz_engine *e);
+
 static std::string g_create_error;
 
 // ---- host/device argument marshalling -----------------------------------------------------
@@ -214,6 +218,7 @@ extern "C" void gz_destroy(gz_engine *e)
                     e->roll_results, e->wts.w1, e->wts.w2, e->wts.w3, e->wts.wh, e->wts.wpfc, e->wts.wvfc,
                     e->wts.bias, e->wts.tc_img, e->wts.tc_fcimg, e->tc_head, e->tc_dbg};
     for (void *p : ptrs) if (p) cudaFree(p);
+    gz_train_free(e);
     for (int i = 0; i < 16; ++i) if (e->wts.raw[i]) cudaFree(e->wts.raw[i]);
     for (int c = 0; c < GZ_PROF_CLASSES; ++c) for (cudaEvent_t ev : e->prof_ev[c]) cudaEventDestroy(ev);
     if (e->own_stream) cudaStreamDestroy(e->stream);
@@ -244,6 +249,7 @@ template <typename T> static int gz_upload(gz_engine *e, T **dst, const std::vec
 }
 
 #include "gz_net_tc.cu"
+
 
 static void gz_conv_to_tap_major(const std::vector<float> &w, int cout, int cin, std::vector<float> &o)
 {
@@ -342,6 +348,7 @@ extern "C" int gz_set_weights(gz_engine *e, const float *const ptrs[16], int32_t
     }
     GZ_TRY(gz_net_prepare_weights(e, h));
     e->wts.loaded = true;
+    gz_train_invalidate(e); // new weights from outside: the optimiser state no longer describes them
     return GZ_OK;
 }
 
@@ -349,6 +356,8 @@ extern "C" int gz_get_weights(gz_engine *e, float *const ptrs[16])
 {
     if (!e || !ptrs) return GZ_E_INVALID;
     if (!e->wts.loaded) { e->err = "weights not set"; return GZ_E_NOWEIGHTS; }
+    GZ_CUDA(e, cudaSetDevice(e->cfg.device));
+    GZ_TRY(gz_train_flush(e));
     GZ_CUDA(e, cudaStreamSynchronize(e->stream));
     for (int i = 0; i < 16; ++i)
         GZ_CUDA(e, cudaMemcpy(ptrs[i], e->wts.raw[i], e->wts.raw_elems[i] * sizeof(float), cudaMemcpyDefault));
@@ -359,6 +368,7 @@ int gzk_net_forward(gz_engine *e, const float *d_planes, const int32_t *d_count,
                     float *d_probs, float *d_values)
 {
     if (!e->wts.loaded) { e->err = "gz_set_weights has not been called"; return GZ_E_NOWEIGHTS; }
+    GZ_TRY(gz_train_flush(e)); // weights trained on the device since the last forward
     // net_impl: 0 = tcgen05 path when the trunk is the reference 32/64/128, 1 = fp32 CUDA-core path,
     // 2 = tcgen05 path or an error
     const int impl = e->cfg.net_impl;
@@ -1000,3 +1010,4 @@ extern "C" int gz_profile_read(gz_engine *e, double *ms, int64_t *launches, int3
 }
 
 #include "gz_augment.cu"
+#include "gz_train.cu"

@@ -53,6 +53,8 @@ struct NetWeights {
     bool loaded = false;
 };
 
+struct TrainState; // gz_train.cu
+
 struct gz_engine {
     gz_config cfg;
     int W, H, S, Sp, n_in_row, G, cap;
@@ -123,6 +125,7 @@ struct gz_engine {
     unsigned long long *gout_count; // [1]
     int64_t gout_drained;
     DevCounters *counters;
+    TrainState *tr;      // device train step state (master weights, Adam moments), created on first use
     // rollouts
     int8_t *roll_results;
     int64_t roll_cap;

@@ -61,7 +61,9 @@ conv1_kernel(const float *__restrict__ planes, const float *__restrict__ w /*[9]
 #define IG_BK 8
 #define IG_AS (IG_BM + 4) // padded row stride of the transposed A tile
 
-template <int BN>
+// EPI 0: out = ReLU(acc + bias) (forward).  EPI 1: out = acc where mask > 0, else 0 (data gradient of
+// a ReLU layer, gz_train.cu: `bias` then points at the layer's forward activations [M][Cout]).
+template <int BN, int EPI = 0>
 __global__ void __launch_bounds__(2 * BN)
 conv3x3_igemm_kernel(const float *__restrict__ in /*[M][Cin]*/, const float *__restrict__ w /*[9][Cin][Cout]*/,
                      const float *__restrict__ bias, float *__restrict__ out /*[M][Cout]*/,
@@ -152,6 +154,24 @@ conv3x3_igemm_kernel(const float *__restrict__ in /*[M][Cin]*/, const float *__r
         }
         if (ch + 1 < n_chunks) sstore(buf ^ 1);
         __syncthreads();
+    }
+    if (EPI == 1) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const long long m = m0 + ty * 8 + i;
+            if (m >= M) continue;
+            float *o = out + m * Cout + n0;
+            const float4 k0 = *reinterpret_cast<const float4 *>(bias + m * Cout + n0 + tx * 4);
+            const float4 k1 = *reinterpret_cast<const float4 *>(bias + m * Cout + n0 + BN / 2 + tx * 4);
+            float4 v0, v1;
+            v0.x = k0.x > 0.f ? acc[i][0] : 0.f; v0.y = k0.y > 0.f ? acc[i][1] : 0.f;
+            v0.z = k0.z > 0.f ? acc[i][2] : 0.f; v0.w = k0.w > 0.f ? acc[i][3] : 0.f;
+            v1.x = k1.x > 0.f ? acc[i][4] : 0.f; v1.y = k1.y > 0.f ? acc[i][5] : 0.f;
+            v1.z = k1.z > 0.f ? acc[i][6] : 0.f; v1.w = k1.w > 0.f ? acc[i][7] : 0.f;
+            *reinterpret_cast<float4 *>(o + tx * 4) = v0;
+            *reinterpret_cast<float4 *>(o + BN / 2 + tx * 4) = v1;
+        }
+        return;
     }
     const float4 bi0 = *reinterpret_cast<const float4 *>(bias + n0 + tx * 4);
     const float4 bi1 = *reinterpret_cast<const float4 *>(bias + n0 + BN / 2 + tx * 4);

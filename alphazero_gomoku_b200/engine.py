@@ -256,6 +256,62 @@ class Engine:
         self._ck(self.L.gz_equi_data(self._h, _ptr(st), _ptr(pi), _ptr(z), int(n), _ptr(os_), _ptr(op), _ptr(oz)))
         return os_, op, oz
 
+    # ---- train step on the device -------------------------------------------------
+    def _train_args(self, states, pis, zs):
+        if hasattr(states, "data_ptr"):
+            st, pi, z = states.float().contiguous(), pis.float().contiguous(), zs.float().contiguous()
+        else:
+            st = np.ascontiguousarray(states, dtype=np.float32)
+            pi = np.ascontiguousarray(pis, dtype=np.float32)
+            z = np.ascontiguousarray(zs, dtype=np.float32)
+        return st, pi, z, int(st.shape[0])
+
+    def train_step(self, states, pis, zs, lr):
+        """PolicyValueNet.train_step (policy_value_net_pytorch.py:117-148) -> (loss, entropy)."""
+        st, pi, z, n = self._train_args(states, pis, zs)
+        loss, ent = C.c_float(0), C.c_float(0)
+        self._ck(self.L.gz_train_step(self._h, _ptr(st), _ptr(pi), _ptr(z), n, float(lr), C.byref(loss), C.byref(ent)))
+        return loss.value, ent.value
+
+    def train_backward(self, states, pis, zs):
+        """Forward + backward only; the flat gradient stays in the engine (see train_grads)."""
+        st, pi, z, n = self._train_args(states, pis, zs)
+        loss, ent = C.c_float(0), C.c_float(0)
+        self._ck(self.L.gz_train_backward(self._h, _ptr(st), _ptr(pi), _ptr(z), n, C.byref(loss), C.byref(ent)))
+        return loss.value, ent.value
+
+    def train_param_count(self):
+        n = C.c_int64(0)
+        self._ck(self.L.gz_train_grads(self._h, None, 0, C.byref(n)))
+        return int(n.value)
+
+    def train_grads(self, out=None):
+        """Flat gradient of the last train_backward in state_dict order / torch layout; `out` may be a
+        torch cuda tensor (filled in place, e.g. for an NCCL all-reduce)."""
+        n = self.train_param_count()
+        if out is None:
+            out = np.zeros(n, np.float32)
+        self._ck(self.L.gz_train_grads(self._h, _ptr(out), n, None))
+        return out
+
+    def train_apply(self, lr, grads=None):
+        """Adam step with `grads` (flat, host or device) or the engine's own gradient."""
+        if grads is not None and not hasattr(grads, "data_ptr"):
+            grads = np.ascontiguousarray(grads, dtype=np.float32)
+        self._ck(self.L.gz_train_apply(self._h, _ptr(grads) if grads is not None else None, float(lr)))
+
+    def train_forward(self, states):
+        """policy_value with the weights as trained so far (fp32 path) -> (probs [n,S], values [n])."""
+        st = np.ascontiguousarray(states, dtype=np.float32)
+        n = int(st.shape[0])
+        probs = np.zeros((n, self.S), np.float32)
+        values = np.zeros(n, np.float32)
+        self._ck(self.L.gz_train_forward(self._h, _ptr(st), n, _ptr(probs), _ptr(values)))
+        return probs, values
+
+    def train_reset(self):
+        self._ck(self.L.gz_train_reset(self._h))
+
     def set_active(self, mask=None):
         """Slots that take part in the next searches (None = all)."""
         if mask is None:

@@ -1,9 +1,9 @@
 """PolicyValueNet: drop-in for the reference's policy_value_net_pytorch.py (:60-157).
 
 Inference (`policy_value_fn`, `policy_value`) runs through the C ABI (gz_net_forward: the
-tcgen05 fused trunk + FC heads).  `train_step` (reference :117-148, SURVEY 8f-1, off the self-play
-hot path) is a plain PyTorch autograd step on the GPU over a torch copy of the same 16 tensors;
-after every step the new weights are pushed to every engine that uses this net.
+tcgen05 fused trunk + FC heads).  `train_step` (reference :117-148) is gz_train_step:
+hand-written forward/backward/Adam kernels over a flat master weight vector on the device; engines
+that search with this net pick the new weights up through `version` / `get_policy_param()`.
 """
 import pickle
 
@@ -68,8 +68,7 @@ class PolicyValueNet():
         else:
             arrs, layout = _default_init(board_width, board_height, seed), _lib.LAYOUT_TORCH
         self._engine.set_weights(arrs, layout=layout)
-        self._params = self._engine.get_weights()  # torch layout, host copies
-        self._torch = None  # lazily built training state (module tensors + Adam)
+        self._params = self._engine.get_weights()  # torch layout, host copies (None = stale after training)
 
     # ---- inference -----------------------------------------------------------------------------
     def policy_value(self, state_batch):
@@ -89,19 +88,23 @@ class PolicyValueNet():
         return act_probs, float(values[0])
 
     # ---- weights -------------------------------------------------------------------------------
+    def _host_params(self):
+        if self._params is None:
+            self._params = self._engine.get_weights()
+        return self._params
+
     def get_policy_param(self):
         """16 float32 arrays in state_dict order and layout (the reference returns the state_dict)."""
-        return [p.copy() for p in self._params]
+        return [p.copy() for p in self._host_params()]
 
     def state_dict(self):
         import torch
-        return {k: torch.from_numpy(p.copy()) for k, p in zip(STATE_DICT_KEYS, self._params)}
+        return {k: torch.from_numpy(p.copy()) for k, p in zip(STATE_DICT_KEYS, self._host_params())}
 
     def set_policy_param(self, arrays, layout=0):
         self._engine.set_weights(arrays, layout=layout)
         self._params = self._engine.get_weights()
         self.version += 1
-        self._torch = None
 
     def save_model(self, model_file):
         """:154-157: torch.save(state_dict) -- loadable by the reference's PolicyValueNet."""
@@ -109,47 +112,23 @@ class PolicyValueNet():
         torch.save(self.state_dict(), model_file)
 
     # ---- training ----------------------------------------------------------------
-    def _train_state(self):
-        if self._torch is None:
-            import torch
-            dev = torch.device("cuda", self._engine.device)
-            params = [torch.nn.Parameter(torch.from_numpy(p.copy()).to(dev)) for p in self._params]
-            opt = torch.optim.Adam(params, weight_decay=self.l2_const)
-            self._torch = (params, opt)
-        return self._torch
-
-    def _forward_torch(self, p, x):
-        import torch
-        import torch.nn.functional as F
-        x = F.relu(F.conv2d(x, p[0], p[1], padding=1))
-        x = F.relu(F.conv2d(x, p[2], p[3], padding=1))
-        x = F.relu(F.conv2d(x, p[4], p[5], padding=1))
-        a = F.relu(F.conv2d(x, p[6], p[7])).flatten(1)
-        a = F.log_softmax(F.linear(a, p[8], p[9]), dim=1)
-        v = F.relu(F.conv2d(x, p[10], p[11])).flatten(1)
-        v = F.relu(F.linear(v, p[12], p[13]))
-        return a, torch.tanh(F.linear(v, p[14], p[15]))
-
     def train_step(self, state_batch, mcts_probs, winner_batch, lr):
-        """:117-148: loss = MSE(v, z) - mean(sum(pi * log p)), Adam with weight decay 1e-4."""
-        import torch
-        import torch.nn.functional as F
-        params, opt = self._train_state()
-        dev = params[0].device
-        x = torch.as_tensor(np.asarray(state_batch, dtype=np.float32), device=dev)
-        pi = torch.as_tensor(np.asarray(mcts_probs, dtype=np.float32), device=dev)
-        z = torch.as_tensor(np.asarray(winner_batch, dtype=np.float32), device=dev)
-        opt.zero_grad()
-        set_learning_rate(opt, lr)
-        log_act_probs, value = self._forward_torch(params, x)
-        value_loss = F.mse_loss(value.view(-1), z)
-        policy_loss = -torch.mean(torch.sum(pi * log_act_probs, 1))
-        loss = value_loss + policy_loss
-        loss.backward()
-        opt.step()
-        entropy = -torch.mean(torch.sum(torch.exp(log_act_probs) * log_act_probs, 1))
-        with torch.no_grad():
-            self._engine.set_weights([p.detach() for p in params])
-        self._params = self._engine.get_weights()
+        """:117-148: loss = MSE(v, z) - mean(sum(pi * log p)), Adam with weight decay 1e-4; forward,
+        backward and the optimiser step are CUDA kernels behind gz_train_step (the Adam moments live
+        in the engine for the life of this object, like the reference's self.optimizer)."""
+        st = np.ascontiguousarray(np.asarray(state_batch, dtype=np.float32).reshape(
+            -1, 4, self.board_width, self.board_height))
+        loss, entropy = self._engine.train_step(st, np.asarray(mcts_probs, dtype=np.float32),
+                                                np.asarray(winner_batch, dtype=np.float32), lr)
+        self._params = None  # pulled from the device on demand
+        self._trained = True
         self.version += 1
-        return loss.item(), entropy.item()
+        return loss, entropy
+
+    def policy_value_train(self, state_batch):
+        """policy_value (:80-94) with the weights as trained so far, without refreshing the tcgen05
+        inference images: what policy_update's KL check calls between epochs (train.py:178-193)."""
+        st = np.ascontiguousarray(np.asarray(state_batch, dtype=np.float32).reshape(
+            -1, 4, self.board_width, self.board_height))
+        probs, values = self._engine.train_forward(st)
+        return probs, values.reshape(-1, 1)

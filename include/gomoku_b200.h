@@ -186,6 +186,30 @@ int gz_selfplay_last(gz_engine *e, int32_t *moves, float *probs);
 int gz_equi_data(gz_engine *e, const float *states, const float *pis, const float *zs, int64_t n,
                  float *out_states, float *out_pis, float *out_zs);
 
+/* ---- train step on the device (policy_value_net_pytorch.py:117-148, train.py:161-214) --- */
+/* PolicyValueNet.train_step: forward, loss = mean((v - z)^2) - mean(sum(pi * log p, 1)), backward and
+ * one torch.optim.Adam(weight_decay=1e-4) step at learning rate lr, all fp32.  states [n,4,W,H]
+ * (current_state layout), pis [n,S], zs [n]; host or device pointers.  *loss / *entropy receive
+ * loss.item() and -mean(sum(p * log p, 1)) (:139-148), both taken BEFORE the update as in the
+ * reference.  The optimiser state (Adam moments, step count) lives in the engine from the first call
+ * until gz_set_weights or gz_train_reset; inference entry points see the new weights on their next
+ * call.  Needs the reference trunk 32/64/128 (GZ_E_INVALID otherwise).                             */
+int gz_train_step(gz_engine *e, const float *states, const float *pis, const float *zs, int64_t n, float lr,
+                  float *loss, float *entropy);
+/* The two halves of gz_train_step for data-parallel training: backward leaves the flat gradient
+ * (state_dict order, torch layout, n_params floats) in the engine; gz_train_grads copies it out (host or
+ * device `out`; out = NULL only reports n_params); gz_train_apply does the Adam step with `grads`
+ * (e.g. the all-reduced mean) or, if NULL, with the engine's own gradient.                          */
+int gz_train_backward(gz_engine *e, const float *states, const float *pis, const float *zs, int64_t n,
+                      float *loss, float *entropy);
+int gz_train_grads(gz_engine *e, float *out, int64_t capacity, int64_t *n_params);
+int gz_train_apply(gz_engine *e, const float *grads, float lr);
+/* PolicyValueNet.policy_value (:80-94) with the weights as trained so far, on the fp32 path: the call
+ * policy_update makes between epochs for its KL early stop (train.py:178-193).                      */
+int gz_train_forward(gz_engine *e, const float *states, int64_t n, float *probs /*[n,S]*/, float *values /*[n]*/);
+/* Drops the optimiser state; the next train call restarts Adam from the current weights. */
+int gz_train_reset(gz_engine *e);
+
 /* ---- pure MCTS with random rollouts (mcts_pure.py:156-231) ---------------------------- */
 /* n_playout waves of: select -> uniform priors over Board.move_target -> Philox rollout
  * to the end of the game -> backup; search_id salts the Philox counter.                   */

@@ -154,3 +154,35 @@ def equi_data(play_data, width, height):
         board_width, board_height = width, height
     return train_module().TrainPipeline.get_equi_data(_Self(), play_data)
 
+
+
+@contextlib.contextmanager
+def item_shim():
+    """the reference's train_step ends with `loss.data[0]`, an IndexError on a 0-dim
+    tensor under torch >= 0.5.  While active, indexing a 0-dim tensor with 0 returns `.item()`; the
+    reference source runs unmodified."""
+    import torch
+    orig = torch.Tensor.__getitem__
+
+    def getitem(self, idx):
+        if self.dim() == 0 and isinstance(idx, int) and idx == 0:
+            return self.item()
+        return orig(self, idx)
+    torch.Tensor.__getitem__ = getitem
+    try:
+        yield
+    finally:
+        torch.Tensor.__getitem__ = orig
+
+
+def train_steps(width, height, arrays, batches, lrs):
+    """The live reference's PolicyValueNet.train_step (policy_value_net_pytorch.py:117-148, CPU fp32)
+    run on `batches` = [(states, pis, zs), ...] starting from state_dict-layout `arrays`.  Returns
+    ([(loss, entropy), ...], final arrays)."""
+    net = make_ref_net(width, height, arrays)
+    out = []
+    with item_shim(), contextlib.redirect_stderr(io.StringIO()):
+        for (st, pi, z), lr in zip(batches, lrs):
+            loss, ent = net.train_step(st, pi, z, lr)
+            out.append((float(loss), float(ent)))
+    return out, net_arrays(net)

@@ -12,6 +12,9 @@ Fixtures (all small):
   mcts.npz    reference MCTS.get_move_probs visit counts (400 playouts, c_puct 5, shipped
         weights, value wrapped as float — SURVEY 8c-3) on seeded positions, with tree reuse
         over two consecutive searches.
+  equi.npz    get_equi_data (train.py:116-135) outputs on random samples.
+  train_step.npz  three reference train_step calls (loss, entropy, final parameters) from the shipped
+        weights on seeded batches.
   rollout.npz reference _evaluate_rollout outcome counts from fixed positions (distribution
         check for the Philox rollout kernel) and pure-MCTS get_move visit statistics.
 """
@@ -292,12 +295,48 @@ def make_equi():
     save("equi.npz", **kw)
 
 
+def make_train(weights):
+    """PolicyValueNet.train_step (policy_value_net_pytorch.py:117-148) of the live reference, CPU fp32:
+    three Adam steps from the shipped weights on seeded batches of reference positions.  Stores the
+    batches, (loss, entropy) per step and every 5th element of the final flat parameter vector."""
+    kw = {}
+    for tag, w, n_row in (("6_6_4", 6, 4), ("8_8_5", 8, 5)):
+        rng = np.random.RandomState(23 + w)
+        S = w * w
+        lrs = [2e-3, 3e-3, 1.3e-3]
+        batches = []
+        for _ in lrs:
+            st, pi, z = [], [], []
+            while len(st) < 48:
+                b, moves = rh.random_position(G.Board, w, w, n_row, rng)
+                if b.game_end()[0]:
+                    continue
+                st.append(np.ascontiguousarray(b.current_state()))
+                p = np.zeros(S)
+                p[b.availables] = rng.dirichlet(0.3 * np.ones(len(b.availables)))
+                pi.append(p)
+                z.append(float(rng.choice([-1.0, 0.0, 1.0])))
+            batches.append((np.array(st), np.array(pi), np.array(z)))
+        out, final = rh.train_steps(w, w, weights[tag], batches, lrs)
+        flat = np.concatenate([a.ravel() for a in final]).astype(np.float32)
+        kw["t%s_states" % tag] = np.array([b[0] for b in batches]).astype(np.uint8)
+        kw["t%s_pis" % tag] = np.array([b[1] for b in batches]).astype(np.float32)
+        kw["t%s_zs" % tag] = np.array([b[2] for b in batches]).astype(np.float32)
+        kw["t%s_lrs" % tag] = np.array(lrs, np.float64)
+        kw["t%s_loss_entropy" % tag] = np.array(out, np.float64)
+        kw["t%s_final_every5" % tag] = flat[::5].copy()
+        kw["t%s_final_sums" % tag] = np.array([[a.astype(np.float64).sum(), np.abs(a.astype(np.float64)).sum()] for a in final])
+        print(tag, out)
+    save("train_step.npz", **kw)
+
+
 if __name__ == "__main__":
     which = sys.argv[1:] or ["weights", "rules", "corpus", "net", "mcts", "rollout"]
-    weights = make_weights() if "weights" in which or "net" in which or "mcts" in which else None
+    weights = make_weights() if {"weights", "net", "mcts", "train"} & set(which) else None
     if "rules" in which: make_rules()
     if "corpus" in which: make_corpus()
     if "net" in which: make_net(weights)
     if "mcts" in which: make_mcts(weights)
     if "rollout" in which: make_rollout()
     if "equi" in which: make_equi()
+    if "train" in which: make_train(weights)
