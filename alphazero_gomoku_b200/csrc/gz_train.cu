@@ -240,33 +240,48 @@ __global__ void __launch_bounds__(128) train_loss_kernel(const float *__restrict
     }
 }
 
-// ---- FC weight gradients: one thread per parameter, fixed-order sum over the batch ---------------
-__global__ void __launch_bounds__(256)
-train_fc_wgrad_kernel(const float *__restrict__ h6, const float *__restrict__ hv, const float *__restrict__ dlog,
-                      const float *__restrict__ dhv, const float *__restrict__ dvpre, float *__restrict__ g,
-                      TrainPack k, int B)
-{
-    const int S = k.S;
-    const int n_wp = 4 * S * S, n_wv = 128 * S;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+// ---- FC weight gradients: one thread per (parameter, batch chunk), fixed-order sums ----------------
+// parameter index i enumerates act_fc1.weight [S][4S], act_fc1.bias, val_fc1.weight [64][2S],
+// val_fc1.bias, val_fc2.weight [64], val_fc2.bias; fc_map gives the two factor streams and the
+// position in the flat gradient vector.
+struct FcMap {
     const float *x, *d;
     int xs, ds, dst;
-    if (i < n_wp) { const int o = i / (4 * S), kk = i % (4 * S); x = h6 + kk; xs = 6 * S; d = dlog + o; ds = S; dst = k.p[8] + i; }
-    else if (i < n_wp + S) { const int o = i - n_wp; x = nullptr; xs = 0; d = dlog + o; ds = S; dst = k.p[9] + o; }
-    else if (i < n_wp + S + n_wv) { const int j = i - n_wp - S, o = j / (2 * S), kk = j % (2 * S); x = h6 + 4 * S + kk; xs = 6 * S; d = dhv + o; ds = 64; dst = k.p[12] + j; }
-    else if (i < n_wp + S + n_wv + 64) { const int o = i - n_wp - S - n_wv; x = nullptr; xs = 0; d = dhv + o; ds = 64; dst = k.p[13] + o; }
-    else if (i < n_wp + S + n_wv + 128) { const int o = i - n_wp - S - n_wv - 64; x = hv + o; xs = 64; d = dvpre; ds = 1; dst = k.p[14] + o; }
-    else if (i == n_wp + S + n_wv + 128) { x = nullptr; xs = 0; d = dvpre; ds = 1; dst = k.p[15]; }
-    else return;
+};
+__device__ __forceinline__ FcMap train_fc_map(int i, const TrainPack &k, const float *h6, const float *hv,
+                                              const float *dlog, const float *dhv, const float *dvpre)
+{
+    const int S = k.S, n_wp = 4 * S * S, n_wv = 128 * S;
+    FcMap f;
+    f.x = nullptr; f.xs = 0; f.dst = -1; f.d = nullptr; f.ds = 0;
+    if (i < n_wp) { const int o = i / (4 * S), kk = i % (4 * S); f.x = h6 + kk; f.xs = 6 * S; f.d = dlog + o; f.ds = S; f.dst = k.p[8] + i; }
+    else if (i < n_wp + S) { const int o = i - n_wp; f.d = dlog + o; f.ds = S; f.dst = k.p[9] + o; }
+    else if (i < n_wp + S + n_wv) { const int j = i - n_wp - S, o = j / (2 * S), kk = j % (2 * S); f.x = h6 + 4 * S + kk; f.xs = 6 * S; f.d = dhv + o; f.ds = 64; f.dst = k.p[12] + j; }
+    else if (i < n_wp + S + n_wv + 64) { const int o = i - n_wp - S - n_wv; f.d = dhv + o; f.ds = 64; f.dst = k.p[13] + o; }
+    else if (i < n_wp + S + n_wv + 128) { const int o = i - n_wp - S - n_wv - 64; f.x = hv + o; f.xs = 64; f.d = dvpre; f.ds = 1; f.dst = k.p[14] + o; }
+    else if (i == n_wp + S + n_wv + 128) { f.d = dvpre; f.ds = 1; f.dst = k.p[15]; }
+    return f;
+}
+
+// part [nchunk][n_fc]
+__global__ void __launch_bounds__(256)
+train_fc_wgrad_kernel(const float *__restrict__ h6, const float *__restrict__ hv, const float *__restrict__ dlog,
+                      const float *__restrict__ dhv, const float *__restrict__ dvpre, float *__restrict__ part,
+                      TrainPack k, int B, int chunk, int n_fc)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_fc) return;
+    const FcMap f = train_fc_map(i, k, h6, hv, dlog, dhv, dvpre);
+    const int b0 = blockIdx.y * chunk, b1 = min(B, b0 + chunk);
     float acc = 0.f;
-    if (x) {
+    if (f.x) {
 #pragma unroll 8
-        for (int b = 0; b < B; ++b) acc = fmaf(x[(size_t)b * xs], d[(size_t)b * ds], acc);
+        for (int b = b0; b < b1; ++b) acc = fmaf(f.x[(size_t)b * f.xs], f.d[(size_t)b * f.ds], acc);
     } else {
 #pragma unroll 8
-        for (int b = 0; b < B; ++b) acc += d[(size_t)b * ds];
+        for (int b = b0; b < b1; ++b) acc += f.d[(size_t)b * f.ds];
     }
-    g[dst] = acc;
+    part[(size_t)blockIdx.y * n_fc + i] = acc;
 }
 
 // ---- 1x1 head convs backward: g3 = mask(a3) * (dh6 . wh^T), partial sums of dWh and dbh ----------
@@ -376,39 +391,54 @@ train_conv_wgrad_kernel(const float *__restrict__ in, const float *__restrict__ 
     }
 }
 
-// conv1: the input is the NCHW plane stack (4 channels); one thread per (ci, co) of the CTA's tap
+// conv1: the input is the NCHW plane stack (4 channels).  Each CTA owns a range of boards, stages one
+// board's planes zero-padded in shared memory, and every thread (ci = warp, co = lane) accumulates its
+// 9 taps; part [nsplit][36*c1 + c1], blockDim = 4*c1.
 __global__ void __launch_bounds__(128)
 train_conv1_wgrad_kernel(const float *__restrict__ planes, const float *__restrict__ gout, float *__restrict__ part,
-                         long long M, int rows_per_split, int S, int W, int H, int c1)
+                         int B, int boards_per_split, int S, int W, int H, int c1)
 {
-    const int tap = blockIdx.x, dy = tap / 3 - 1, dx = tap % 3 - 1;
-    const long long m_begin = (long long)blockIdx.y * rows_per_split;
-    const long long m_end = (m_begin + rows_per_split < M) ? m_begin + rows_per_split : M;
-    float *o = part + (size_t)blockIdx.y * (36 * c1 + c1);
-    for (int t = threadIdx.x; t < 4 * c1; t += blockDim.x) {
-        const int ci = t / c1, co = t % c1;
-        float acc = 0.f, bacc = 0.f;
-        for (long long m = m_begin; m < m_end; ++m) {
-            const long long b = m / S;
-            const int cell = (int)(m % S), yy = cell / W + dy, xx = cell % W + dx;
-            const float gv = gout[m * c1 + co];
-            bacc += gv;
-            if (yy >= 0 && yy < H && xx >= 0 && xx < W)
-                acc = fmaf(planes[b * 4 * S + ci * S + yy * W + xx], gv, acc);
+    extern __shared__ float sp[]; // [4][(H+2)*(W+2)]
+    const int PW = W + 2, PS = (H + 2) * PW;
+    const int b0 = blockIdx.x * boards_per_split, b1 = min(B, b0 + boards_per_split);
+    const int co = threadIdx.x % c1, ci = threadIdx.x / c1;
+    float acc[9], bacc = 0.f;
+#pragma unroll
+    for (int t = 0; t < 9; ++t) acc[t] = 0.f;
+    for (int i = threadIdx.x; i < 4 * PS; i += blockDim.x) sp[i] = 0.f;
+    for (int b = b0; b < b1; ++b) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < 4 * S; i += blockDim.x) {
+            const int c = i / S, cell = i % S;
+            sp[c * PS + (cell / W + 1) * PW + cell % W + 1] = planes[(size_t)b * 4 * S + i];
         }
-        o[(tap * 4 + ci) * c1 + co] = acc;
-        if (tap == 4 && ci == 0) o[36 * c1 + co] = bacc;
+        __syncthreads();
+        const float *g = gout + (size_t)b * S * c1 + co;
+        const float *win = sp + ci * PS;
+        for (int y = 0; y < H; ++y)
+            for (int x = 0; x < W; ++x) {
+                const float gv = g[(y * W + x) * c1];
+                bacc += gv;
+                const float *q = win + y * PW + x;
+#pragma unroll
+                for (int t = 0; t < 9; ++t) acc[t] = fmaf(q[(t / 3) * PW + t % 3], gv, acc[t]);
+            }
     }
+    float *o = part + (size_t)blockIdx.x * (36 * c1 + c1);
+#pragma unroll
+    for (int t = 0; t < 9; ++t) o[(t * 4 + ci) * c1 + co] = acc[t];
+    if (ci == 0) o[36 * c1 + co] = bacc;
 }
 
 // ---- fixed-order reduction of the split partials into the flat gradient vector --------------------
 // mode 0: conv partial [9][Cin][Cout] + [Cout]  -> OIHW weight at offW, bias at offB
 // mode 1: head partial [7][c3] (see train_head_dgrad_kernel) -> act_conv1 / val_conv1 weights + biases
+// mode 2: FC partial [n_fc] -> train_fc_map destinations
 struct TrainReduce {
     int mode, n, nsplit, Cin, Cout, offW, offB, offW2, offB2;
 };
 __global__ void __launch_bounds__(256)
-train_reduce_kernel(const float *__restrict__ part, float *__restrict__ g, TrainReduce r)
+train_reduce_kernel(const float *__restrict__ part, float *__restrict__ g, TrainReduce r, TrainPack k)
 {
     __shared__ float s[8][33];
     const int li = threadIdx.x & 31, ls = threadIdx.x >> 5;
@@ -428,6 +458,8 @@ train_reduce_kernel(const float *__restrict__ part, float *__restrict__ g, Train
             dst = r.offW + (co * r.Cin + ci) * 9 + tap;
         } else
             dst = r.offB + (i - nw);
+    } else if (r.mode == 2) {
+        dst = train_fc_map(i, k, nullptr, nullptr, nullptr, nullptr, nullptr).dst;
     } else {
         const int c3 = r.Cin, j = i / c3, c = i % c3;
         if (j < 4) dst = r.offW + j * c3 + c;
@@ -487,6 +519,11 @@ static int gz_train_ensure(gz_engine *e, int64_t B)
     if (!e->wts.loaded) { e->err = "gz_set_weights has not been called"; return GZ_E_NOWEIGHTS; }
     if (!gz_train_supported(e)) { e->err = "the device train step needs the reference trunk 32/64/128"; return GZ_E_INVALID; }
     if (!e->tr) e->tr = new TrainState();
+    if (e->n_sm <= 0) {
+        int dev = 0;
+        GZ_CUDA(e, cudaGetDevice(&dev));
+        GZ_CUDA(e, cudaDeviceGetAttribute(&e->n_sm, cudaDevAttrMultiProcessorCount, dev));
+    }
     TrainState *t = e->tr;
     const int S = e->S, c1 = e->c1, c2 = e->c2, c3 = e->c3;
     if (!t->p) {
@@ -566,7 +603,11 @@ static int gz_train_ensure(gz_engine *e, int64_t B)
         // reduction (ceil(rows / 32) x 7*c3)
         const size_t n_head = ((rows + 31) / 32) * 7 * c3;
         const size_t n_conv = (size_t)64 * (9 * c2 * c3 + c3);
+        const size_t n_fcp = (size_t)16 * (4 * S * S + S + 128 * S + 129);
+        const size_t n_c1 = (size_t)(2 * e->n_sm + 1) * (37 * c1);
         t->part_n = n_head > n_conv ? n_head : n_conv;
+        if (n_fcp > t->part_n) t->part_n = n_fcp;
+        if (n_c1 > t->part_n) t->part_n = n_c1;
         GZ_CUDA(e, cudaMalloc(&t->part, t->part_n * sizeof(float)));
         t->cap = B;
     }
@@ -621,14 +662,22 @@ static int gz_train_backward_pass(gz_engine *e, const float *d_states, const flo
     train_heads_kernel<<<(unsigned)B, 128, hsm, e->stream>>>(ha);
     train_loss_kernel<<<1, 128, 0, e->stream>>>(t->terms, (int)B, t->out2);
     const int n_fc = 4 * S * S + S + 128 * S + 64 + 64 + 1;
-    train_fc_wgrad_kernel<<<(n_fc + 255) / 256, 256, 0, e->stream>>>(t->h6, t->hv, t->dlog, t->dhv, t->dvpre, t->g, k, (int)B);
+    TrainReduce r;
+    {
+        int chunk = (int)((B + 15) / 16);
+        if (chunk < 32) chunk = 32;
+        const int nchunk = (int)((B + chunk - 1) / chunk);
+        train_fc_wgrad_kernel<<<dim3((n_fc + 255) / 256, nchunk), 256, 0, e->stream>>>(
+            t->h6, t->hv, t->dlog, t->dhv, t->dvpre, t->part, k, (int)B, chunk, n_fc);
+        r.mode = 2; r.n = n_fc; r.nsplit = nchunk; r.Cin = r.Cout = r.offW = r.offB = r.offW2 = r.offB2 = 0;
+        train_reduce_kernel<<<(r.n + 31) / 32, 256, 0, e->stream>>>(t->part, t->g, r, k);
+    }
     // 1x1 head convs
     const int R = 32, nblk = (int)((M + R - 1) / R);
     train_head_dgrad_kernel<<<nblk, 128, 0, e->stream>>>(t->a3, t->dh6, t->packed + k.o_wh, t->g3, t->part, M, S, c3, R);
-    TrainReduce r;
     r.mode = 1; r.n = 7 * c3; r.nsplit = nblk; r.Cin = c3; r.Cout = 0;
     r.offW = k.p[6]; r.offB = k.p[7]; r.offW2 = k.p[10]; r.offB2 = k.p[11];
-    train_reduce_kernel<<<(r.n + 31) / 32, 256, 0, e->stream>>>(t->part, t->g, r);
+    train_reduce_kernel<<<(r.n + 31) / 32, 256, 0, e->stream>>>(t->part, t->g, r, k);
     // conv3: weight gradient, then the data gradient masked by ReLU(conv2)
     int nsplit = (int)((M + 511) / 512);
     if (nsplit > 64) nsplit = 64;
@@ -638,25 +687,24 @@ static int gz_train_backward_pass(gz_engine *e, const float *d_states, const flo
     nsplit = (int)((M + rows - 1) / rows);
     train_conv_wgrad_kernel<64, 128, 4><<<dim3(9, nsplit), 256, 0, e->stream>>>(t->a2, t->g3, t->part, M, rows, S, W, H);
     r.mode = 0; r.Cin = c2; r.Cout = c3; r.n = 9 * c2 * c3 + c3; r.nsplit = nsplit; r.offW = k.p[4]; r.offB = k.p[5];
-    train_reduce_kernel<<<(r.n + 31) / 32, 256, 0, e->stream>>>(t->part, t->g, r);
+    train_reduce_kernel<<<(r.n + 31) / 32, 256, 0, e->stream>>>(t->part, t->g, r, k);
     const unsigned gx = (unsigned)((M + IG_BM - 1) / IG_BM);
     conv3x3_igemm_kernel<64, 1><<<dim3(gx, 1), 128, 0, e->stream>>>(
         t->g3, t->packed + k.o_w3d, t->a2, t->g2, nullptr, B, S, W, H, c3, c2);
     // conv2
     train_conv_wgrad_kernel<32, 64, 2><<<dim3(9, nsplit), 128, 0, e->stream>>>(t->a1, t->g2, t->part, M, rows, S, W, H);
     r.Cin = c1; r.Cout = c2; r.n = 9 * c1 * c2 + c2; r.offW = k.p[2]; r.offB = k.p[3];
-    train_reduce_kernel<<<(r.n + 31) / 32, 256, 0, e->stream>>>(t->part, t->g, r);
+    train_reduce_kernel<<<(r.n + 31) / 32, 256, 0, e->stream>>>(t->part, t->g, r, k);
     conv3x3_igemm_kernel<32, 1><<<dim3(gx, 1), 64, 0, e->stream>>>(
         t->g2, t->packed + k.o_w2d, t->a1, t->g1, nullptr, B, S, W, H, c2, c1);
     // conv1 (no data gradient: the input is the position)
-    int ns1 = (int)((M + 255) / 256);
-    if (ns1 > 64) ns1 = 64;
-    const int rows1 = (int)((M + ns1 - 1) / ns1);
-    ns1 = (int)((M + rows1 - 1) / rows1);
-    train_conv1_wgrad_kernel<<<dim3(9, ns1), 128, 0, e->stream>>>(d_states, t->g1, t->part, M, rows1, S, W, H, c1);
+    const int bps = (int)((B + 2 * e->n_sm - 1) / (2 * e->n_sm));
+    const int ns1 = (int)((B + bps - 1) / bps);
+    train_conv1_wgrad_kernel<<<ns1, 4 * c1, (size_t)4 * (H + 2) * (W + 2) * sizeof(float), e->stream>>>(
+        d_states, t->g1, t->part, (int)B, bps, S, W, H, c1);
     r.Cin = 4; r.Cout = c1; r.n = 36 * c1 + c1; r.nsplit = ns1; r.offW = k.p[0]; r.offB = k.p[1];
-    train_reduce_kernel<<<(r.n + 31) / 32, 256, 0, e->stream>>>(t->part, t->g, r);
-    e->launches += 13;
+    train_reduce_kernel<<<(r.n + 31) / 32, 256, 0, e->stream>>>(t->part, t->g, r, k);
+    e->launches += 14;
     GZ_CUDA(e, cudaGetLastError());
     t->have_grads = true;
     return GZ_OK;

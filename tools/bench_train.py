@@ -43,7 +43,7 @@ def main():
     a = ap.parse_args()
     w, B, S = a.width, a.batch, a.width * a.width
     rng = np.random.RandomState(0)
-    arrs = [rng.uniform(-1, 1, size=s).astype(np.float32) / np.sqrt(max(int(np.prod(s[1:])), 16))
+    arrs = [(rng.uniform(-1, 1, size=s) / np.sqrt(max(int(np.prod(s[1:])), 16))).astype(np.float32)
             for s in weight_shapes(w, w)]
     st = (rng.rand(B, 4, w, w) < 0.3).astype(np.float32)
     pi = rng.dirichlet(0.3 * np.ones(S), size=B).astype(np.float32)
