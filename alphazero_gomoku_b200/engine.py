@@ -242,6 +242,7 @@ class Engine:
             import torch
             n = states.shape[0]
             st, pi, z = states.float().contiguous(), pis.float().contiguous(), zs.float().contiguous()
+            torch.cuda.current_stream(st.device).synchronize()
             os_ = torch.empty((8 * n, 4, self.width, self.height), dtype=torch.float32, device=st.device)
             op = torch.empty((8 * n, self.S), dtype=torch.float32, device=st.device)
             oz = torch.empty((8 * n,), dtype=torch.float32, device=st.device)
@@ -259,7 +260,9 @@ class Engine:
     # ---- train step on the device -------------------------------------------------
     def _train_args(self, states, pis, zs):
         if hasattr(states, "data_ptr"):
+            import torch
             st, pi, z = states.float().contiguous(), pis.float().contiguous(), zs.float().contiguous()
+            torch.cuda.current_stream(st.device).synchronize()  # the engine runs on its own stream
         else:
             st = np.ascontiguousarray(states, dtype=np.float32)
             pi = np.ascontiguousarray(pis, dtype=np.float32)
@@ -296,13 +299,21 @@ class Engine:
 
     def train_apply(self, lr, grads=None):
         """Adam step with `grads` (flat, host or device) or the engine's own gradient."""
-        if grads is not None and not hasattr(grads, "data_ptr"):
+        if grads is not None and hasattr(grads, "data_ptr"):
+            import torch
+            torch.cuda.current_stream(grads.device).synchronize()  # e.g. an NCCL all-reduce still in flight
+        elif grads is not None:
             grads = np.ascontiguousarray(grads, dtype=np.float32)
         self._ck(self.L.gz_train_apply(self._h, _ptr(grads) if grads is not None else None, float(lr)))
 
     def train_forward(self, states):
         """policy_value with the weights as trained so far (fp32 path) -> (probs [n,S], values [n])."""
-        st = np.ascontiguousarray(states, dtype=np.float32)
+        if hasattr(states, "data_ptr"):
+            import torch
+            st = states.float().contiguous()
+            torch.cuda.current_stream(st.device).synchronize()
+        else:
+            st = np.ascontiguousarray(states, dtype=np.float32)
         n = int(st.shape[0])
         probs = np.zeros((n, self.S), np.float32)
         values = np.zeros(n, np.float32)

@@ -51,7 +51,7 @@ def load_model_file(path, width, height):
 class PolicyValueNet():
     """policy-value network"""
 
-    def __init__(self, board_width, board_height, model_file=None, use_gpu=True, seed=None):
+    def __init__(self, board_width, board_height, model_file=None, use_gpu=True, seed=None, device=0):
         if not use_gpu:
             raise RuntimeError("alphazero_gomoku_b200 has no CPU path: use_gpu must be True")
         self.use_gpu = True
@@ -61,7 +61,7 @@ class PolicyValueNet():
         self.version = 0  # bumped whenever the weights change; MCTS engines re-upload lazily
         n = min(board_width, board_height, 5)
         self._engine = Engine(width=board_width, height=board_height, n_in_row=n, n_games=1, n_playout=1,
-                              nodes_per_game=4)
+                              nodes_per_game=4, device=device)
         from . import _lib
         if model_file:
             arrs, layout = load_model_file(model_file, board_width, board_height)
@@ -112,23 +112,44 @@ class PolicyValueNet():
         torch.save(self.state_dict(), model_file)
 
     # ---- training ----------------------------------------------------------------
+    def _batch(self, state_batch, mcts_probs=None, winner_batch=None):
+        """Lists / numpy arrays (the reference's inputs) -> float32 arrays; torch cuda tensors (a batch
+        drawn from the device replay buffer) pass through untouched."""
+        if hasattr(state_batch, "data_ptr"):
+            return state_batch, mcts_probs, winner_batch
+        st = np.ascontiguousarray(np.asarray(state_batch, dtype=np.float32).reshape(
+            -1, 4, self.board_width, self.board_height))
+        pi = None if mcts_probs is None else np.asarray(mcts_probs, dtype=np.float32)
+        z = None if winner_batch is None else np.asarray(winner_batch, dtype=np.float32)
+        return st, pi, z
+
     def train_step(self, state_batch, mcts_probs, winner_batch, lr):
         """:117-148: loss = MSE(v, z) - mean(sum(pi * log p)), Adam with weight decay 1e-4; forward,
         backward and the optimiser step are CUDA kernels behind gz_train_step (the Adam moments live
         in the engine for the life of this object, like the reference's self.optimizer)."""
-        st = np.ascontiguousarray(np.asarray(state_batch, dtype=np.float32).reshape(
-            -1, 4, self.board_width, self.board_height))
-        loss, entropy = self._engine.train_step(st, np.asarray(mcts_probs, dtype=np.float32),
-                                                np.asarray(winner_batch, dtype=np.float32), lr)
+        st, pi, z = self._batch(state_batch, mcts_probs, winner_batch)
+        loss, entropy = self._engine.train_step(st, pi, z, lr)
         self._params = None  # pulled from the device on demand
         self._trained = True
         self.version += 1
         return loss, entropy
 
+    def train_backward(self, state_batch, mcts_probs, winner_batch):
+        """Forward + backward of train_step without the optimiser step -> (loss, entropy); the flat
+        gradient stays on the device (`train_grads`) so that ranks can average it first."""
+        return self._engine.train_backward(*self._batch(state_batch, mcts_probs, winner_batch))
+
+    def train_grads(self, out=None):
+        return self._engine.train_grads(out)
+
+    def train_apply(self, lr, grads=None):
+        """The Adam step of train_step, with `grads` (flat, host or device) or the local gradient."""
+        self._engine.train_apply(lr, grads)
+        self._params = None
+        self.version += 1
+
     def policy_value_train(self, state_batch):
         """policy_value (:80-94) with the weights as trained so far, without refreshing the tcgen05
         inference images: what policy_update's KL check calls between epochs (train.py:178-193)."""
-        st = np.ascontiguousarray(np.asarray(state_batch, dtype=np.float32).reshape(
-            -1, 4, self.board_width, self.board_height))
-        probs, values = self._engine.train_forward(st)
+        probs, values = self._engine.train_forward(self._batch(state_batch)[0])
         return probs, values.reshape(-1, 1)

@@ -109,8 +109,73 @@ def broadcast_weights(arrays, src=0, group=None):
     return out
 
 
+class DeviceReplayBuffer(object):
+    """The reference's `deque(maxlen=buffer_size)` + `random.sample` (train.py:82,167) with the samples
+    resident on the device: a ring of float32 tensors; `extend` keeps the newest maxlen
+    samples, `sample(k)` draws k distinct positions with the host `random` module exactly as
+    random.sample does on a sequence of the same length, and gathers them on the device."""
+
+    def __init__(self, maxlen, width, height, device):
+        import torch
+        self.maxlen, self.count, self.head = int(maxlen), 0, 0
+        dev = device if isinstance(device, (str, torch.device)) else torch.device("cuda", device)
+        self.states = torch.zeros((self.maxlen, 4, width, height), dtype=torch.float32, device=dev)
+        self.pis = torch.zeros((self.maxlen, width * height), dtype=torch.float32, device=dev)
+        self.zs = torch.zeros((self.maxlen,), dtype=torch.float32, device=dev)
+
+    def __len__(self):
+        return self.count
+
+    def extend(self, states, pis, zs):
+        n = int(zs.shape[0])
+        if n >= self.maxlen:
+            states, pis, zs, n = states[-self.maxlen:], pis[-self.maxlen:], zs[-self.maxlen:], self.maxlen
+            self.head = 0
+        first = min(n, self.maxlen - self.head)
+        for dst, src in ((self.states, states), (self.pis, pis), (self.zs, zs)):
+            dst[self.head:self.head + first] = src[:first]
+            if n > first:
+                dst[:n - first] = src[first:]
+        self.head = (self.head + n) % self.maxlen
+        self.count = min(self.maxlen, self.count + n)
+
+    def physical(self, logical):
+        """deque position (0 = oldest) -> ring slot"""
+        return (self.head - self.count + np.asarray(logical, np.int64)) % self.maxlen
+
+    def sample(self, k):
+        import torch
+        idx = torch.from_numpy(self.physical(random.sample(range(self.count), k))).to(self.zs.device)
+        return self.states.index_select(0, idx), self.pis.index_select(0, idx), self.zs.index_select(0, idx)
+
+
+def allreduce_mean(x, group=None):
+    """In-place mean over ranks of a flat float32 vector (torch tensor on the backend's device, or a
+    numpy array that is staged through one); the gradient exchange of the data-parallel update."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return x
+    world = dist.get_world_size(group)
+    if isinstance(x, np.ndarray):
+        dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+        t = torch.from_numpy(x).to(dev)
+        dist.all_reduce(t, group=group)
+        x[...] = (t / world).cpu().numpy()
+        return x
+    dist.all_reduce(x, group=group)
+    x /= world
+    return x
+
+
 class TrainPipeline():
-    def __init__(self, conf=None, init_model=None, best_model="best_policy.model", seed=0):
+    def __init__(self, conf=None, init_model=None, best_model="best_policy.model", seed=0, device_buffer=False,
+                 device=None):
+        """device_buffer=True keeps the replay buffer on the device (DeviceReplayBuffer): samples go
+        self-play ring -> augmentation -> buffer -> train step without touching the host.
+        device: CUDA ordinal of this process (default: LOCAL_RANK, one process per GPU)."""
+        import os
+        self.device = int(os.environ.get("LOCAL_RANK", "0")) if device is None else int(device)
         c = dict(DEFAULT_CONF)
         c.update(conf or {})
         self.board_width, self.board_height, self.n_in_row = c['board_width'], c['board_height'], c['n_in_row']
@@ -120,12 +185,14 @@ class TrainPipeline():
         self.n_playout, self.c_puct = c['n_playout'], c['c_puct']
         self.buffer_size, self.batch_size = c['buffer_size'], c['batch_size']
         self.data_buffer = deque(maxlen=self.buffer_size)
+        self.device_buffer = bool(device_buffer)
         self.play_batch_size, self.epochs, self.kl_targ = c['play_batch_size'], c['epochs'], c['kl_targ']
         self.check_freq, self.game_batch_num = c['check_freq'], c['game_batch_num']
         self.best_win_ratio = 0.2
         self.pure_mcts_playout_num = c['pure_mcts_playout_num']
         self.seed = seed
-        self.policy_value_net = PolicyValueNet(self.board_width, self.board_height, model_file=init_model)
+        self.policy_value_net = PolicyValueNet(self.board_width, self.board_height, model_file=init_model,
+                                               device=self.device)
         self.mcts_player = MCTSPlayer(self.policy_value_net.policy_value_fn, c_puct=self.c_puct,
                                       n_playout=self.n_playout, is_selfplay=1)
         self._engine = None
@@ -146,7 +213,7 @@ class TrainPipeline():
             rank = _rank()
             self._engine = Engine(width=self.board_width, height=self.board_height, n_in_row=self.n_in_row,
                                   n_games=n_slots, n_playout=self.n_playout, c_puct=float(self.c_puct),
-                                  seed=self.seed + rank, game_id_base=(rank << 40))
+                                  seed=self.seed + rank, game_id_base=(rank << 40), device=self.device)
             self._engine_version = -1
         if self._engine_version != self.policy_value_net.version:
             self._engine.set_weights(self.policy_value_net.get_policy_param())
@@ -187,6 +254,8 @@ class TrainPipeline():
         the buffer receives the reference's items in the reference's order (game, ply, image)."""
         if len(train_data) != 0:
             raise NotImplementedError("start_from_train_data (recorded games) is outside the hot path (SURVEY 8f-4)")
+        if self.device_buffer:
+            return self._collect_on_device(n_games)
         e, d = self._play(n_games)
         st, pi, z = e.equi_data(d["states"], d["pis"], d["zs"])
         st, pi = st.astype(np.float64), pi.astype(np.float64)
@@ -194,12 +263,79 @@ class TrainPipeline():
         self.episode_len = len(d["zs"])
         return
 
+    def _collect_on_device(self, n_games):
+        """collect_selfplay_data with every array on the device: the finished games' samples are drained
+        into torch tensors, augmented by gz_equi_data and appended to the DeviceReplayBuffer in the
+        engine's output order (games in finishing order, plies ascending inside a game)."""
+        import torch
+        e = self._selfplay_engine(int(n_games))
+        e.selfplay_begin(temp=float(self.temp), recycle=False)
+        for _ in range(self.board_width * self.board_height):
+            e.selfplay_step(1)
+            if e.selfplay_pending()[2] == 0:
+                break
+        n = int(e.selfplay_pending()[0])
+        dev = torch.device("cuda", e.device)
+        bufs = {"states": torch.empty((max(n, 1), 4, self.board_width, self.board_height), dtype=torch.float32, device=dev),
+                "pis": torch.empty((max(n, 1), self.board_width * self.board_height), dtype=torch.float32, device=dev),
+                "zs": torch.empty((max(n, 1),), dtype=torch.float32, device=dev),
+                "game_ids": torch.empty((max(n, 1),), dtype=torch.int64, device=dev),
+                "plies": torch.empty((max(n, 1),), dtype=torch.int32, device=dev)}
+        d = e.selfplay_drain(n, bufs)
+        self.last_games = e.selfplay_drain_games()
+        self._games_played += len(self.last_games)
+        if isinstance(self.data_buffer, deque):
+            self.data_buffer = DeviceReplayBuffer(self.buffer_size, self.board_width, self.board_height, e.device)
+        st, pi, z = e.equi_data(d["states"], d["pis"], d["zs"])
+        self.data_buffer.extend(st, pi, z)
+        self.episode_len = int(d["zs"].shape[0])
+
+    def _minibatch(self, k):
+        """(states, pis, zs, zs as numpy): random.sample of the buffer (train.py:167)."""
+        if isinstance(self.data_buffer, DeviceReplayBuffer):
+            st, pi, z = self.data_buffer.sample(k)
+            return st, pi, z, z.cpu().numpy().astype(np.float64)
+        mini_batch = random.sample(self.data_buffer, k)
+        z = [data[2] for data in mini_batch]
+        return [data[0] for data in mini_batch], [data[1] for data in mini_batch], z, np.array(z)
+
+    def policy_update_dp(self, group=None):
+        """train.py:161-214 as a data-parallel update: every rank draws batch_size / world
+        samples from ITS OWN buffer, runs forward + backward on the device, the flat gradients are
+        averaged with one all-reduce (NCCL over NVLink) and every rank applies the same Adam step, so
+        the weights stay identical without a broadcast and samples never leave their GPU.  The KL used
+        for the early stop and the lr schedule is the mean over ranks."""
+        import torch
+        import torch.distributed as dist
+        world = dist.get_world_size(group) if dist.is_initialized() else 1
+        local_bs = max(1, self.batch_size // world)
+        state_batch, mcts_probs_batch, winner_batch, _ = self._minibatch(local_bs)
+        net = self.policy_value_net
+        old_probs, old_v = net.policy_value_train(state_batch)
+        nccl = dist.is_initialized() and dist.get_backend(group) == "nccl"
+        grads = torch.empty(net._engine.train_param_count(), dtype=torch.float32,
+                            device=torch.device("cuda", net._engine.device)) if nccl else None
+        for i in range(self.epochs):
+            loss, entropy = net.train_backward(state_batch, mcts_probs_batch, winner_batch)
+            grads = allreduce_mean(net.train_grads(grads), group)
+            net.train_apply(self.learn_rate * self.lr_multiplier, grads)
+            new_probs, new_v = net.policy_value_train(state_batch)
+            kl = np.mean(np.sum(old_probs * (np.log(old_probs + 1e-10) - np.log(new_probs + 1e-10)), axis=1))
+            stats = allreduce_mean(np.array([kl, loss, entropy], np.float32), group)
+            kl, loss, entropy = float(stats[0]), float(stats[1]), float(stats[2])
+            if kl > self.kl_targ * 4:
+                break
+        if kl > self.kl_targ * 2 and self.lr_multiplier > 0.05:
+            self.lr_multiplier /= 1.5
+        elif kl < self.kl_targ / 2 and self.lr_multiplier < 10:
+            self.lr_multiplier *= 1.5
+        _logger.info("kl=%4.3f, lr_multiplier=%4.3f, loss=%4.3f, entropy=%4.3f (data parallel, %d ranks)"
+                     % (kl, self.lr_multiplier, loss, entropy, world))
+        return loss, entropy
+
     def policy_update(self):
         """train.py:161-214."""
-        mini_batch = random.sample(self.data_buffer, self.batch_size)
-        state_batch = [data[0] for data in mini_batch]
-        mcts_probs_batch = [data[1] for data in mini_batch]
-        winner_batch = [data[2] for data in mini_batch]
+        state_batch, mcts_probs_batch, winner_batch, z_host = self._minibatch(self.batch_size)
         # both sides of the KL come from the fp32 training path (gz_train_forward): the tcgen05
         # inference images are refreshed once, when self-play next needs the weights
         old_probs, old_v = self.policy_value_net.policy_value_train(state_batch)
@@ -214,8 +350,8 @@ class TrainPipeline():
             self.lr_multiplier /= 1.5
         elif kl < self.kl_targ / 2 and self.lr_multiplier < 10:
             self.lr_multiplier *= 1.5
-        explained_var_old = 1 - np.var(np.array(winner_batch) - old_v.flatten()) / np.var(np.array(winner_batch))
-        explained_var_new = 1 - np.var(np.array(winner_batch) - new_v.flatten()) / np.var(np.array(winner_batch))
+        explained_var_old = 1 - np.var(z_host - old_v.flatten()) / np.var(z_host)
+        explained_var_new = 1 - np.var(z_host - new_v.flatten()) / np.var(z_host)
         _logger.info("kl=%4.3f, lr_multiplier=%4.3f, loss=%4.3f, entropy=%4.3f, explained_var_old=%4.3f, "
                      "explained_var_new=%4.3f" % (kl, self.lr_multiplier, loss, entropy, explained_var_old,
                                                   explained_var_new))
@@ -233,7 +369,7 @@ class TrainPipeline():
                 self._arena.close()
             self._arena = Engine(width=self.board_width, height=self.board_height, n_in_row=self.n_in_row,
                                  n_games=n_games, n_playout=max(self.n_playout, self.pure_mcts_playout_num),
-                                 c_puct=float(self.c_puct), seed=self.seed + 7919 + _rank())
+                                 c_puct=float(self.c_puct), seed=self.seed + 7919 + _rank(), device=self.device)
         self._arena.set_weights(self.policy_value_net.get_policy_param())
         self._arena_rounds += 1
         winners = arena_play(self._arena, self.n_playout, self.pure_mcts_playout_num,

@@ -132,7 +132,7 @@ import numpy as np
 import torch
 import torch.distributed as dist
 sys.path.insert(0, %(root)r)
-from alphazero_gomoku_b200.train import all_gather_samples, broadcast_weights, pack_samples, shard_games
+from alphazero_gomoku_b200.train import all_gather_samples, allreduce_mean, broadcast_weights, pack_samples, shard_games
 rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 dist.init_process_group("gloo", rank=rank, world_size=world)
 # every rank "plays" its shard of 11 games; game g yields (g %% 4) + 1 samples tagged with g
@@ -153,6 +153,11 @@ assert got == want, (got, want)            # union ordered (rank, game, ply) == 
 ws = [np.full((3, 2), 7.0 + i, np.float32) if rank == 0 else np.zeros((3, 2), np.float32) for i in range(16)]
 out = broadcast_weights(ws, src=0)
 assert all(float(o[0, 0]) == 7.0 + i for i, o in enumerate(out))
+# gradient exchange of the data-parallel update: in-place mean over ranks, numpy and torch inputs
+g = np.arange(5, dtype=np.float32) * (rank + 1)
+assert np.allclose(allreduce_mean(g), np.arange(5) * 1.5) and np.allclose(g, np.arange(5) * 1.5)
+t = torch.full((4,), float(rank))
+assert torch.allclose(allreduce_mean(t), torch.full((4,), 0.5))
 dist.barrier()
 dist.destroy_process_group()
 print("rank", rank, "ok")
@@ -160,7 +165,7 @@ print("rank", rank, "ok")
 
 
 def test_collectives_gloo_world2(tmp_path):
-    """sample all-gather (ragged) and weight broadcast on 2 ranks over gloo."""
+    """sample all-gather (ragged), weight broadcast and gradient mean on 2 ranks over gloo."""
     script = tmp_path / "worker.py"
     script.write_text(_WORKER % {"root": ROOT})
     env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29731", WORLD_SIZE="2")
@@ -195,3 +200,32 @@ def test_equi_data_host_vs_reference_golden():
         assert np.array_equal(np.array([o[0] for o in out]), z["w%d_out_states" % w])
         assert np.array_equal(np.array([o[1] for o in out]), z["w%d_out_pis" % w])
         assert np.array_equal(np.array([o[2] for o in out]), z["w%d_out_zs" % w])
+
+
+def test_device_replay_buffer_is_deque_plus_random_sample():
+    """DeviceReplayBuffer (ring of tensors, here on the CPU device) == deque(maxlen) + random.sample
+    (train.py:82,167) under the same host RNG state, through several wrap-arounds."""
+    import random
+    from collections import deque
+    import torch
+    from alphazero_gomoku_b200.train import DeviceReplayBuffer
+    rng = np.random.RandomState(1)
+    buf, ref = DeviceReplayBuffer(50, 3, 3, "cpu"), deque(maxlen=50)
+    tag = 0
+    for n in (7, 20, 30, 3, 50, 64, 1, 49, 120, 5):
+        st = np.zeros((n, 4, 3, 3), np.float32)
+        st[:, 0, 0, 0] = np.arange(tag, tag + n)
+        pi = rng.rand(n, 9).astype(np.float32)
+        z = np.arange(tag, tag + n).astype(np.float32)
+        tag += n
+        buf.extend(torch.from_numpy(st), torch.from_numpy(pi), torch.from_numpy(z))
+        ref.extend((st[i], pi[i], z[i]) for i in range(n))
+        assert len(buf) == len(ref)
+        k = min(len(ref), 6)
+        random.seed(tag)
+        want = random.sample(ref, k)
+        random.seed(tag)
+        gs, gp, gz = buf.sample(k)
+        assert np.array_equal(gz.numpy(), np.array([w[2] for w in want]))
+        assert np.array_equal(gs.numpy(), np.array([w[0] for w in want]))
+        assert np.array_equal(gp.numpy(), np.array([w[1] for w in want]))
