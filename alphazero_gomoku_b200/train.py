@@ -299,6 +299,11 @@ class TrainPipeline():
         z = [data[2] for data in mini_batch]
         return [data[0] for data in mini_batch], [data[1] for data in mini_batch], z, np.array(z)
 
+    def broadcast_initial_weights(self, src=0, group=None):
+        """Every rank starts from rank `src`'s weights (one flat broadcast); after that the data-parallel
+        updates keep them bit-identical without further weight traffic."""
+        self.policy_value_net.set_policy_param(broadcast_weights(self.policy_value_net.get_policy_param(), src, group))
+
     def policy_update_dp(self, group=None):
         """train.py:161-214 as a data-parallel update: every rank draws batch_size / world
         samples from ITS OWN buffer, runs forward + backward on the device, the flat gradients are

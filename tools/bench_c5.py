@@ -36,6 +36,7 @@ def main():
     conf = {"board_width": a.board, "board_height": a.board, "n_in_row": 5, "n_playout": a.playouts,
             "buffer_size": 10000, "batch_size": 512, "epochs": 5}
     tp = TrainPipeline(conf, seed=0, device_buffer=True, device=local)
+    tp.broadcast_initial_weights()
     t_play, t_upd, games, plies, steps = [], [], 0, 0, 0
     for it in range(a.iters + 1):  # iteration 0 is the warm-up (allocations, first-touch)
         if world > 1:
@@ -45,6 +46,10 @@ def main():
         tp.collect_selfplay_data(a.games)
         torch.cuda.synchronize()
         t1 = time.perf_counter()
+        if world > 1:
+            dist.barrier()  # rank skew of the self-play phase is not update time
+        torch.cuda.synchronize()
+        t1b = time.perf_counter()
         loss, ent = tp.policy_update_dp() if world > 1 else tp.policy_update()
         w = tp.policy_value_net.get_policy_param()  # refresh point: self-play engines pick these up
         torch.cuda.synchronize()
@@ -52,7 +57,7 @@ def main():
         if it == 0:
             continue
         t_play.append(t1 - t0)
-        t_upd.append(t2 - t1)
+        t_upd.append(t2 - t1b)
         games += len(tp.last_games)
         plies += tp.episode_len
     stat = torch.tensor([sum(t_play), sum(t_upd), float(games), float(plies)], dtype=torch.float64, device="cuda")
