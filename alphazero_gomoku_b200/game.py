@@ -175,3 +175,34 @@ class Game(object):
             print("Game end. Winner is player:", winner) if winner != -1 else print("Game end. Tie")
         _logger.warning("{'steps':[%s],'winner':%d}" % (",".join(str(t[3]) for t in trace), winner))
         return winner, zip([t[0] for t in trace], [t[1] for t in trace], winners_z)
+
+    def start_from_train_data(self, player, train_data, is_shown=0):
+        """game.py:292-358: samples from a recorded game `[winner, moves]` (player 1 moves first): the
+        state before every move, pi = 0.99999 on the move played and 1e-6 elsewhere, z from each
+        mover's point of view.  Returns (winner, zip(states, mcts_probs, winners_z)); an illegal move
+        gives the reference's (1, None, None)."""
+        winner, record = train_data[0], list(train_data[1])
+        self.board.init_board()
+        cells = self.board.width * self.board.height
+        trace = []  # (state, pi, mover)
+        for move in record:
+            pi = np.full(cells, 0.000001)
+            pi[move] = 0.99999
+            trace.append((self.board.current_state(), pi, self.board.current_player))
+            try:
+                self.board.do_move(move)
+            except Exception as e:
+                print(str(e))
+                return 1, None, None
+            if is_shown:
+                self.graphic(self.board, *self.board.players)
+        if not trace:
+            return None
+        movers = np.array([t[2] for t in trace])
+        winners_z = np.zeros(len(trace))
+        if winner != -1:
+            winners_z = np.where(movers == winner, 1.0, -1.0)
+        player.reset_player()
+        if is_shown:
+            print("Game end. Winner is player:", winner) if winner != -1 else print("Game end. Tie")
+        return winner, zip([t[0] for t in trace], [t[1] for t in trace], winners_z)

@@ -109,6 +109,56 @@ def broadcast_weights(arrays, src=0, group=None):
     return out
 
 
+def samples_from_train_data(engine, games):
+    """Game.start_from_train_data (game.py:292-358) for a list of recorded games `[winner, moves]` at
+    once: every prefix position of every game goes through ONE gz_rules_eval call (planes and move
+    legality on the device).  Returns per-game lists of (state float64 [4,W,H], pi float64 [S], z)."""
+    prefixes, owner = [], []
+    for gi, (winner, moves) in enumerate(games):
+        moves = [int(m) for m in moves]
+        for k in range(len(moves)):
+            prefixes.append(moves[:k])
+            owner.append(gi)
+        prefixes.append(moves)  # the final position only checks the last move's legality
+        owner.append(gi)
+    out = engine.rules_eval(prefixes, [0] * len(prefixes), want=("planes", "status"))
+    bad = np.nonzero(out["status"] != 0)[0]
+    if len(bad):
+        raise ValueError("recorded game %d contains an illegal move" % owner[int(bad[0])])
+    res, i = [], 0
+    S = engine.S
+    for winner, moves in games:
+        plays = []
+        for k, mv in enumerate(moves):
+            pi = np.full(S, 0.000001)
+            pi[int(mv)] = 0.99999
+            mover = 1 + (k % 2)
+            z = 0.0 if winner == -1 else (1.0 if mover == winner else -1.0)
+            plays.append((out["planes"][i + k].astype(np.float64), pi, z))
+        i += len(moves) + 1
+        res.append(plays)
+    return res
+
+
+def games_from_steps_log(path):
+    """train.py:446-466 (gen_moves_from_yixin): `{'steps': [...], 'winner': w, ...}` lines -> unique
+    decisive games as [winner, moves] with winner = 2 - len(moves) % 2 (player 1 moves first)."""
+    import ast
+    seen, res = set(), []
+    with open(path, "r") as f:
+        for line in f:
+            line = line.strip()
+            if not line:
+                break
+            rec = ast.literal_eval(line)
+            if rec["winner"] == -1 or tuple(rec["steps"]) in seen:
+                continue
+            seen.add(tuple(rec["steps"]))
+    for steps in sorted(seen):
+        res.append([2 - len(steps) % 2, list(steps)])
+    return res
+
+
 class DeviceReplayBuffer(object):
     """The reference's `deque(maxlen=buffer_size)` + `random.sample` (train.py:82,167) with the samples
     resident on the device: a ring of float32 tensors; `extend` keeps the newest maxlen
@@ -253,7 +303,7 @@ class TrainPipeline():
         games run concurrently and the dihedral images are produced on the device (gz_equi_data);
         the buffer receives the reference's items in the reference's order (game, ply, image)."""
         if len(train_data) != 0:
-            raise NotImplementedError("start_from_train_data (recorded games) is outside the hot path (SURVEY 8f-4)")
+            return self._collect_from_train_data(n_games, train_data)
         if self.device_buffer:
             return self._collect_on_device(n_games)
         e, d = self._play(n_games)
@@ -262,6 +312,27 @@ class TrainPipeline():
         self.data_buffer.extend((st[i], pi[i], float(z[i])) for i in range(len(z)))
         self.episode_len = len(d["zs"])
         return
+
+    def _collect_from_train_data(self, n_games, train_data):
+        """train.py:137-159, recorded-game branch: the first n_games entries of train_data ([winner,
+        moves] each) become samples through one batched rules call, then the usual x8 augmentation."""
+        e = self.policy_value_net._engine  # stateless rules call: any engine of this board size
+        games = samples_from_train_data(e, train_data[:int(n_games)])
+        flat = [s for g in games for s in g]
+        self.episode_len = len(flat)
+        if not flat:
+            return
+        st, pi, z = e.equi_data(np.array([s[0] for s in flat], np.float32), np.array([s[1] for s in flat], np.float32),
+                                np.array([s[2] for s in flat], np.float32))
+        if self.device_buffer:
+            import torch
+            if isinstance(self.data_buffer, deque):
+                self.data_buffer = DeviceReplayBuffer(self.buffer_size, self.board_width, self.board_height, e.device)
+            dev = self.data_buffer.zs.device
+            self.data_buffer.extend(torch.from_numpy(st).to(dev), torch.from_numpy(pi).to(dev), torch.from_numpy(z).to(dev))
+        else:
+            st, pi = st.astype(np.float64), pi.astype(np.float64)
+            self.data_buffer.extend((st[i], pi[i], float(z[i])) for i in range(len(z)))
 
     def _collect_on_device(self, n_games):
         """collect_selfplay_data with every array on the device: the finished games' samples are drained

@@ -15,6 +15,7 @@ Fixtures (all small):
   equi.npz    get_equi_data (train.py:116-135) outputs on random samples.
   train_step.npz  three reference train_step calls (loss, entropy, final parameters) from the shipped
         weights on seeded batches.
+  traindata.npz  Game.start_from_train_data samples of recorded games (game.py:292-358).
   rollout.npz reference _evaluate_rollout outcome counts from fixed positions (distribution
         check for the Philox rollout kernel) and pure-MCTS get_move visit statistics.
 """
@@ -330,6 +331,45 @@ def make_train(weights):
     save("train_step.npz", **kw)
 
 
+def make_traindata():
+    """Game.start_from_train_data (game.py:292-358) of the live reference on recorded games: the first
+    three 15x15 games of human_gomoku.txt ([winner, moves] records) and two hand-made 6x6 games (one
+    tie).  Stores the records and the reference's (state, pi, z) samples."""
+    class _P(object):
+        def reset_player(self):
+            pass
+    games15 = []
+    with open(os.path.join(rh.REF_DIR, "human_gomoku.txt")) as f:
+        for line in f:
+            line = line.strip()
+            if line.startswith("["):
+                d = ast.literal_eval(line)
+                games15.append([int(d[0]), [int(x) for x in d[1]]])
+                if len(games15) >= 3:
+                    break
+    games6 = [[2, [14, 15, 20, 21, 8, 9, 27, 3]], [-1, [0, 35, 5, 30, 17]]]
+    kw = {}
+    for tag, w, n, games in (("15", 15, 5, games15), ("6", 6, 4, games6)):
+        g = G.Game(G.Board(width=w, height=w, n_in_row=n))
+        st, pi, z, offs, flat, winners = [], [], [], [0], [], []
+        for rec in games:
+            winner, data = g.start_from_train_data(_P(), rec)
+            data = list(data)
+            st += [np.ascontiguousarray(d[0]) for d in data]
+            pi += [d[1] for d in data]
+            z += [d[2] for d in data]
+            flat += rec[1]
+            offs.append(len(flat))
+            winners.append(rec[0])
+        kw["td%s_moves" % tag] = np.array(flat, np.int32)
+        kw["td%s_offsets" % tag] = np.array(offs, np.int64)
+        kw["td%s_winners" % tag] = np.array(winners, np.int32)
+        kw["td%s_states" % tag] = np.array(st).astype(np.uint8)
+        kw["td%s_pis" % tag] = np.array(pi, np.float64)
+        kw["td%s_zs" % tag] = np.array(z, np.float64)
+    save("traindata.npz", **kw)
+
+
 if __name__ == "__main__":
     which = sys.argv[1:] or ["weights", "rules", "corpus", "net", "mcts", "rollout"]
     weights = make_weights() if {"weights", "net", "mcts", "train"} & set(which) else None
@@ -340,3 +380,4 @@ if __name__ == "__main__":
     if "rollout" in which: make_rollout()
     if "equi" in which: make_equi()
     if "train" in which: make_train(weights)
+    if "traindata" in which: make_traindata()

@@ -229,3 +229,15 @@ def test_device_replay_buffer_is_deque_plus_random_sample():
         assert np.array_equal(gz.numpy(), np.array([w[2] for w in want]))
         assert np.array_equal(gs.numpy(), np.array([w[0] for w in want]))
         assert np.array_equal(gp.numpy(), np.array([w[1] for w in want]))
+
+
+def test_games_from_steps_log(tmp_path):
+    """train.py:446-466: steps-log lines -> unique decisive games, winner from the parity of the length."""
+    from alphazero_gomoku_b200.train import games_from_steps_log
+    path = tmp_path / "steps.log"
+    path.write_text("{'steps': [112, 97, 125], 'winner': 1, 'start_player': 1}\n"
+                    "{'steps': [1, 2, 3, 4], 'winner': 2, 'start_player': 2}\n"
+                    "{'steps': [5, 6], 'winner': -1, 'start_player': 1}\n"
+                    "{'steps': [112, 97, 125], 'winner': 1, 'start_player': 1}\n"
+                    "\n{'steps': [9], 'winner': 1}\n")
+    assert games_from_steps_log(str(path)) == [[2, [1, 2, 3, 4]], [1, [112, 97, 125]]]

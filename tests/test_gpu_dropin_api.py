@@ -269,3 +269,41 @@ def test_device_equi_data_vs_reference_golden():
             assert (gz_[8 * i:8 * i + 8] == bz[i]).all()
         assert e.equi_data(bs[:0], bp[:0], bz[:0])[0].shape[0] == 0
         e.close()
+
+
+def test_start_from_train_data_vs_reference_golden():
+    """recorded games -> supervised samples (game.py:292-358), one game through the Game
+    API and all games through the batched rules call, against the live reference's outputs."""
+    from alphazero_gomoku_b200 import Board, Game, TrainPipeline
+    from alphazero_gomoku_b200.engine import Engine
+    from alphazero_gomoku_b200.train import samples_from_train_data
+    z = np.load(os.path.join(GOLDEN, "traindata.npz"))
+
+    class _P(object):
+        def reset_player(self):
+            self.was_reset = True
+
+    for tag, w, n in (("15", 15, 5), ("6", 6, 4)):
+        offs = z["td%s_offsets" % tag]
+        games = [[int(z["td%s_winners" % tag][i]), z["td%s_moves" % tag][offs[i]:offs[i + 1]].tolist()]
+                 for i in range(len(offs) - 1)]
+        want_st, want_pi, want_z = z["td%s_states" % tag].astype(np.float64), z["td%s_pis" % tag], z["td%s_zs" % tag]
+        e = Engine(width=w, height=w, n_in_row=n, n_games=1, n_playout=1, nodes_per_game=4)
+        got = samples_from_train_data(e, games)
+        assert [len(g) for g in got] == [len(g[1]) for g in games]
+        flat = [s for g in got for s in g]
+        assert np.array_equal(np.array([s[0] for s in flat]), want_st)
+        assert np.array_equal(np.array([s[1] for s in flat]), want_pi)
+        assert np.array_equal(np.array([s[2] for s in flat]), want_z)
+        p = _P()
+        winner, data = Game(Board(width=w, height=w, n_in_row=n)).start_from_train_data(p, games[0])
+        data = list(data)
+        assert winner == games[0][0] and p.was_reset and len(data) == len(games[0][1])
+        assert all(np.array_equal(d[0], want_st[i]) and np.array_equal(d[1], want_pi[i]) and d[2] == want_z[i]
+                   for i, d in enumerate(data))
+        with pytest.raises(ValueError):
+            samples_from_train_data(e, [[1, [3, 4, 3]]])  # occupied cell
+    tp = TrainPipeline({"board_width": 6, "board_height": 6, "n_in_row": 4, "n_playout": 10, "buffer_size": 500})
+    tp.collect_selfplay_data(2, train_data=games)  # games = the 6x6 records
+    assert tp.episode_len == 13 and len(tp.data_buffer) == 8 * 13
+    assert tp.data_buffer[0][0].shape == (4, 6, 6) and abs(tp.data_buffer[0][1].sum() - (0.99999 + 35e-6)) < 1e-6
