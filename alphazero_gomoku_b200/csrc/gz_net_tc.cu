@@ -30,20 +30,9 @@
 namespace tc {
 constexpr int C1 = 32, C2 = 64, C3 = 128;
 constexpr int ROWS = 256;                 // output rows per group (2 M-tiles of 128)
-constexpr int LEAD = 24;                  // zero rows before row 0 (>= P + 1)
-constexpr int RALLOC = 304;               // LEAD + ROWS + 24 trailing rows
-constexpr int CH = RALLOC * 16;           // bytes of one 8-channel chunk plane
-constexpr int OFF_A0 = 0;                 // input planes: one chunk plane = hi(4 planes) | lo(4 planes) per row
-constexpr int OFF_ACT1 = OFF_A0 + CH;     // conv1 output: 4 hi planes, 4 lo planes
-constexpr int OFF_ACT2 = OFF_ACT1 + 8 * CH; // conv2 output: 8 hi planes, 8 lo planes
-constexpr int OFF_W1 = OFF_ACT2 + 16 * CH;  // conv1 weights, resident: [pass][tap pair 5][chunk 2][32][8]
-constexpr int W1_BYTES = 2 * 5 * 2 * 32 * 16;
+constexpr int W1_BYTES = 2 * 5 * 2 * 32 * 16; // conv1 weights, resident: [pass][tap pair 5][chunk 2][32][8]
 constexpr int NSTAGE = 4, STAGE_BYTES = 16384;
-constexpr int OFF_RING = OFF_W1 + W1_BYTES;
-constexpr int OFF_BAR = OFF_RING + NSTAGE * STAGE_BYTES; // full[4] empty[4] mma_done, tmem base, mma3_done, c3_free, c2_back
-constexpr int OFF_HST = OFF_BAR + 128;    // head activations of one group, fp16: [board][pass hi|lo][16 J halves]
-constexpr int HST_BYTES = 8192;           // NB * J * 64 bytes <= 5632 for every supported board
-constexpr int SMEM_BYTES = OFF_HST + HST_BYTES;
+constexpr int HST_BYTES = 8192;           // NB * J * 64 bytes <= 6144 for every supported board
 constexpr int W2_STAGE = 8192;            // one tap: [chunk 4][128 rows: 64 hi | 64 lo][8]
 constexpr int W3_STAGE = 16384;           // half a tap: [pass][chunk 4][128][8]
 constexpr int N_STAGES_PER_GROUP = 5 + 18; // conv2: two taps per ring stage (4 full + 1 half), conv3: 18
@@ -52,6 +41,34 @@ constexpr int TM_C1 = 0, TM_C2 = 0, TM_C3 = 256;  // TMEM column bases; conv2 (2
                                                   // columns: conv1's epilogue is over before conv2 of the same group starts
 constexpr int THREADS = 576;              // 8 front epilogue warps, MMA warp, copy warp, 8 back epilogue warps
 constexpr int SYNC_THREADS = 288;         // front warps + MMA warp (phase barrier)
+
+// Shared-memory line space of a group.
+//   DENSE = false (any board side): rows of the padded line space are the M rows of the MMAs
+//     (cell (i, j) of board b -> row b * BS + i * P + j); the outputs of padding rows are wasted
+//     (192 of 256 rows are cells at 8x8).
+//   DENSE = true (8x8 boards): a board row is exactly one 8-row core matrix of the UMMA operand, so
+//     the descriptor's stride between core matrices (SBO) is set to NINE rows: the MMA reads 8 cells
+//     and skips the zero pad row that follows them, and all 256 M rows are cells (4 boards per
+//     group instead of 3).  Board rows of the 4 boards are interleaved (slot = 4 * i + b, 9 rows per
+//     slot), so a vertical tap is a shift of 4 slots and one block of 4 zero slots above and below
+//     the group serves every board; M-tile 0 holds board rows 0-3, M-tile 1 board rows 4-7.
+template <bool DENSE> struct Lay {
+    static constexpr int LEAD = DENSE ? 40 : 24;      // zero rows before row 0 (>= largest tap shift)
+    static constexpr int RALLOC = DENSE ? 368 : 304;  // LEAD + rows of the group + trailing zero rows
+    static constexpr int TILE = DENSE ? 144 : 128;    // line-space rows between the two M-tiles
+    static constexpr int SBO = DENSE ? 144 : 128;     // bytes between 8-row core matrices of the A operand
+    static constexpr int VSTEP = 36;                  // DENSE: line-space rows between vertically adjacent cells
+    static constexpr int CH = RALLOC * 16;            // bytes of one 8-channel chunk plane
+    static constexpr int OFF_A0 = 0;                  // input planes: one chunk plane = hi(4 planes) | lo(4 planes) per row
+    static constexpr int OFF_ACT1 = OFF_A0 + CH;      // conv1 output: 4 hi planes, 4 lo planes
+    static constexpr int OFF_ACT2 = OFF_ACT1 + 8 * CH;  // conv2 output: 8 hi planes, 8 lo planes
+    static constexpr int OFF_W1 = OFF_ACT2 + 16 * CH;
+    static constexpr int OFF_RING = OFF_W1 + W1_BYTES;
+    static constexpr int OFF_BAR = OFF_RING + NSTAGE * STAGE_BYTES; // full[4] empty[4] mma_done, tmem base, mma3_done, c3_free, c2_back
+    static constexpr int OFF_HST = OFF_BAR + 128;     // head activations of one group, fp16: [board][pass hi|lo][16 J halves]
+    static constexpr int SMEM_BYTES = OFF_HST + HST_BYTES;
+};
+static_assert(Lay<true>::SMEM_BYTES <= 232448, "dense layout must fit the 227 KB shared-memory limit");
 } // namespace tc
 
 // Per-channel constants of the epilogues, passed BY VALUE as a kernel parameter: they sit in the
@@ -152,10 +169,10 @@ __device__ __forceinline__ void tc_tmem_wait_ld() { asm volatile("tcgen05.wait::
 __device__ __forceinline__ void tc_bar_sync_all() { asm volatile("bar.sync 3, 544;" ::: "memory"); } // front + MMA + back warps
 // K-major, no-swizzle shared-memory matrix descriptor: rows 16 B apart inside an 8-row core
 // matrix, 8-row groups 128 B apart (SBO), the two 8-element K chunks of one MMA lbo bytes apart.
-__device__ __forceinline__ uint64_t tc_desc(uint32_t saddr, uint32_t lbo_bytes)
+__device__ __forceinline__ uint64_t tc_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes = 128u)
 {
     const uint32_t lo = ((saddr >> 4) & 0x3FFFu) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
-    const uint32_t hi = (128u >> 4) | (1u << 14); // SBO = 128 B, descriptor version 1 (sm_100)
+    const uint32_t hi = (sbo_bytes >> 4) | (1u << 14); // SBO (128 B = contiguous rows), descriptor version 1 (sm_100)
     return ((uint64_t)hi << 32) | lo;
 }
 // kind::f16 instruction descriptor: fp16 x fp16 -> fp32, both operands K-major, M = 128
@@ -180,10 +197,12 @@ __device__ __forceinline__ void tc_split8(const float *f, uint4 &hi, uint4 &lo)
 // conv2 epilogue for 16 output channels (half h, quarter sub) of one row: accumulator columns
 // (hi*hi + lo*hi at 0-63, hi*lo at 64-127) -> scale, bias, ReLU, hi/lo split -> act2 planes.
 // Front warps take sub 0, back-end warps sub 1 of the same rows.
+template <bool DENSE>
 __device__ __forceinline__ void tc_ep2_part(uint8_t *smem, uint32_t tmem_tile, uint32_t row_off, const TcConsts &cst,
                                             float inv_s2, int half, int sub, bool valid, float *dbg_row)
 {
     using namespace tc;
+    constexpr int CH = Lay<DENSE>::CH, OFF_ACT2 = Lay<DENSE>::OFF_ACT2;
     uint32_t v[16], v2[16];
     tc_tmem_ld16_nowait(tmem_tile + half * 32 + sub * 16, v);
     tc_tmem_ld16_nowait(tmem_tile + 64 + half * 32 + sub * 16, v2);
@@ -221,6 +240,7 @@ __device__ __forceinline__ void tc_ep2_part(uint8_t *smem, uint32_t tmem_tile, u
 // k = c*S + cell inside the policy section (steps 0..Jp-1) and the value section (steps Jp..J-1).
 // dbg (optional) = act1 [B][S][32] | act2 [B][S][64] | act3 [B][S][128] | head [B][6][S] fp32 for
 // parity tests.
+template <bool DENSE>
 __global__ void __launch_bounds__(tc::THREADS, 1)
 trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wimg,
                 const __grid_constant__ TcConsts cst, float inv_s1, float inv_s2, float inv_s3,
@@ -228,6 +248,11 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                 float *__restrict__ dbg, long long *__restrict__ timeline)
 {
     using namespace tc;
+    using L = Lay<DENSE>;
+    constexpr int LEAD = L::LEAD, CH = L::CH, TILE = L::TILE, OFF_A0 = L::OFF_A0, OFF_ACT1 = L::OFF_ACT1,
+                  OFF_ACT2 = L::OFF_ACT2, OFF_W1 = L::OFF_W1, OFF_RING = L::OFF_RING, OFF_BAR = L::OFF_BAR,
+                  OFF_HST = L::OFF_HST;
+    constexpr uint32_t SBO = L::SBO;
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0); // warp-uniform for the compiler
@@ -295,9 +320,10 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         // group's staging / conv1 / conv2.  TMEM lane quarter of a warp is warp % 4.
         const int tile = (warp - 10) >> 2, q = warp & 3;
         const int r = tile * 128 + q * 32 + lane;
-        const int bq = r / g.BS, rr = r % g.BS;
-        const int ci = rr / g.P, cj = rr % g.P;
-        const bool geo_ok = bq < g.NB && ci < g.W && cj < g.W;
+        // DENSE: M row r = slot (r / 8 = 4 * board row + board) x column (r % 8)
+        const int bq = DENSE ? ((r >> 3) & 3) : r / g.BS, rr = r % g.BS;
+        const int ci = DENSE ? (r >> 5) : rr / g.P, cj = DENSE ? (r & 7) : rr % g.P;
+        const bool geo_ok = DENSE || (bq < g.NB && ci < g.W && cj < g.W);
         const int cell = ci * g.W + cj;
         const uint32_t t_lane = ((uint32_t)(q * 32)) << 16;
         __half *s_hst = reinterpret_cast<__half *>(smem + OFF_HST);
@@ -312,12 +338,12 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             const bool valid = geo_ok && board < B;
             {   // second 16 channels of each conv2 epilogue half (the front warps take the first 16).
                 float *drow = dbg ? dbg + (size_t)maxB * g.S * C1 + ((size_t)board * g.S + cell) * C2 : nullptr;
-                const uint32_t row_off = (uint32_t)(LEAD + r) * 16u;
+                const uint32_t row_off = (uint32_t)(LEAD + (DENSE ? (r >> 3) * 9 + (r & 7) : r)) * 16u;
                 tc_mbar_wait(bar_c2back, ph3);
                 tc_fence_after();
-                tc_ep2_part(smem, tmem + t_lane + TM_C2 + tile * 128, row_off, cst, inv_s2, 0, 1, valid, drow);
+                tc_ep2_part<DENSE>(smem, tmem + t_lane + TM_C2 + tile * 128, row_off, cst, inv_s2, 0, 1, valid, drow);
                 tc_bar_sync_all(); // A
-                tc_ep2_part(smem, tmem + t_lane + TM_C2 + tile * 128, row_off, cst, inv_s2, 1, 1, valid, drow);
+                tc_ep2_part<DENSE>(smem, tmem + t_lane + TM_C2 + tile * 128, row_off, cst, inv_s2, 1, 1, valid, drow);
                 tc_bar_sync_all(); // B
             }
             tc_mbar_wait(bar_mma3, ph3);
@@ -402,21 +428,21 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         // the middle of conv3(g)'s MMA stream), and the back-end warps drain conv3(g-1).
         const int tile = warp >> 2;               // warps 0-3 -> M-tile 0, 4-7 -> M-tile 1
         const int r = tid;                        // output row of an epilogue thread; TMEM lane = r % 128
-        const int bq = r / g.BS, rr = r % g.BS;
-        const int ci = rr / g.P, cj = rr % g.P;
-        const bool geo_ok = warp < 8 && bq < g.NB && ci < g.W && cj < g.W;
+        const int bq = DENSE ? ((r >> 3) & 3) : r / g.BS, rr = r % g.BS;
+        const int ci = DENSE ? (r >> 5) : rr / g.P, cj = DENSE ? (r & 7) : rr % g.P;
+        const bool geo_ok = warp < 8 && (DENSE || (bq < g.NB && ci < g.W && cj < g.W));
         const int cell = ci * g.W + cj;
         const uint32_t t_lane = ((uint32_t)((warp & 3) * 32)) << 16;
-        const uint32_t row_off = (uint32_t)(LEAD + r) * 16u;
+        const uint32_t row_off = (uint32_t)(LEAD + (DENSE ? (r >> 3) * 9 + (r & 7) : r)) * 16u;
         uint32_t mma_phase = 0, it = 0, c3_phase = 0;
         bool first_group = true;
         const uint32_t leader = tc_elect(); // one lane per warp; used by the MMA warp only
         int shift[9];
 #pragma unroll
-        for (int t = 0; t < 9; ++t) shift[t] = (t / 3 - 1) * g.P + (t % 3 - 1);
+        for (int t = 0; t < 9; ++t) shift[t] = (t / 3 - 1) * (DENSE ? L::VSTEP : g.P) + (t % 3 - 1);
         // descriptor bases; a row shift / chunk / slot offset is an add on the 16-byte address field
         const uint64_t dW1 = tc_desc(sbase + OFF_W1, 512);
-        const uint64_t dAct1 = tc_desc(sbase + OFF_ACT1 + LEAD * 16, CH), dAct2 = tc_desc(sbase + OFF_ACT2 + LEAD * 16, CH);
+        const uint64_t dAct1 = tc_desc(sbase + OFF_ACT1 + LEAD * 16, CH, SBO), dAct2 = tc_desc(sbase + OFF_ACT2 + LEAD * 16, CH, SBO);
         const uint64_t dRing2 = tc_desc(sbase + OFF_RING, 2048), dRing3 = tc_desc(sbase + OFF_RING, 2048);
         int tl_i = 0;
 #define TC_MARK()                                                                  \
@@ -459,7 +485,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                 for (int q = 0; q < 5; ++q) {
                     const int t0 = 2 * q;
                     const uint32_t lbo = (q == 4) ? 16u : (uint32_t)(shift[t0 + 1] - shift[t0]) * 16u;
-                    const uint64_t da = tc_desc(sbase + OFF_A0 + (uint32_t)(LEAD + j * 128 + shift[t0]) * 16u, lbo);
+                    const uint64_t da = tc_desc(sbase + OFF_A0 + (uint32_t)(LEAD + j * TILE + shift[t0]) * 16u, lbo, SBO);
 #pragma unroll
                     for (int p = 0; p < 2; ++p)
                         tc_umma_f16(leader, tmem + TM_C1 + j * C1, da, dW1 + (uint32_t)((p * 5 + q) * 64), tc_idesc(C1),
@@ -510,9 +536,9 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
 #pragma unroll
                             for (int ks = 0; ks < 2; ++ks) {
                                 // x_hi * [w_hi | w_lo] in one N = 128 MMA (A read once), then x_lo * w_hi (N = 64)
-                                tc_umma_f16(leader, tmem + TM_C2 + j * 128, da + (uint32_t)(((2 * ks) * CH) / 16 + j * 128),
+                                tc_umma_f16(leader, tmem + TM_C2 + j * 128, da + (uint32_t)(((2 * ks) * CH) / 16 + j * TILE),
                                             db + (uint32_t)(ks * 256), tc_idesc(128), (t | ks) != 0);
-                                tc_umma_f16(leader, tmem + TM_C2 + j * 128, da + (uint32_t)(((4 + 2 * ks) * CH) / 16 + j * 128),
+                                tc_umma_f16(leader, tmem + TM_C2 + j * 128, da + (uint32_t)(((4 + 2 * ks) * CH) / 16 + j * TILE),
                                             db + (uint32_t)(ks * 256), tc_idesc(64), 1u);
                             }
                     }
@@ -525,7 +551,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         // front warps: conv2 accumulators (hi*hi + lo*hi in columns 0-63, hi*lo in 64-127) -> act2,
         // one 32-channel half at a time so conv3 can start on channels 0-31
         auto ep2 = [&](long long board, bool valid, int half) {
-            tc_ep2_part(smem, tmem + t_lane + TM_C2 + tile * 128, row_off, cst, inv_s2, half, 0, valid,
+            tc_ep2_part<DENSE>(smem, tmem + t_lane + TM_C2 + tile * 128, row_off, cst, inv_s2, half, 0, valid,
                         dbg ? dbg + (size_t)maxB * g.S * C1 + ((size_t)board * g.S + cell) * C2 : nullptr);
         };
         // MMA warp: conv3 ring stages [s0, s1), h-major: 9 taps of input channels 0-31, then of 32-63
@@ -544,7 +570,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
 #pragma unroll
                         for (int p = 0; p < 3; ++p) {
                             const int ap = (p == 1), bp = (p == 2);
-                            tc_umma_f16(leader, tmem + TM_C3 + j * C3, da + (uint32_t)(((ap * 8 + 2 * ks) * CH) / 16 + j * 128),
+                            tc_umma_f16(leader, tmem + TM_C3 + j * C3, da + (uint32_t)(((ap * 8 + 2 * ks) * CH) / 16 + j * TILE),
                                         db + (uint32_t)(bp * 512 + ks * 256), tc_idesc(C3), (s | ks | p) != 0);
                         }
                 tc_umma_commit(leader, bar_empty + 8 * slot);
@@ -832,12 +858,20 @@ static bool gz_tc_supported(const gz_engine *e)
     return e->c1 == tc::C1 && e->c2 == tc::C2 && e->c3 == tc::C3 && e->W == e->H && e->W >= 3 && e->W <= 15;
 }
 
+// 8x8 boards take the dense line space (Lay<true>: every M row of the MMAs is a cell, 4 boards per
+// group); GZ_TC_PADDED=1 forces the padded one (3 boards per group) for A/B measurements.
+static bool gz_tc_dense(const gz_engine *e)
+{
+    static const bool padded = getenv("GZ_TC_PADDED") != nullptr;
+    return e->W == 8 && !padded;
+}
+
 static TcGeom gz_tc_geom(const gz_engine *e)
 {
     TcGeom g;
     g.W = e->W; g.S = e->S; g.P = e->W + 1;
     g.BS = e->W * g.P + g.P + 1;
-    g.NB = 1 + (tc::ROWS - e->W * g.P) / g.BS;
+    g.NB = gz_tc_dense(e) ? 4 : 1 + (tc::ROWS - e->W * g.P) / g.BS;
     g.Jp = 2 * ((4 * e->S + 31) / 32); // both FC sections are padded to whole stages of K = 32
     g.J = g.Jp + 2 * ((2 * e->S + 31) / 32);
     return g;
@@ -975,8 +1009,11 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
     if (maxB <= 0) return GZ_OK;
     if (!gz_tc_supported(e)) { e->err = "tcgen05 net path needs a square board and the 32/64/128 trunk"; return GZ_E_INVALID; }
     GZ_TRY(gz_tc_ensure_buffers(e, maxB, want_dbg));
+    const bool dense = gz_tc_dense(e);
+    const int smem_bytes = dense ? Lay<true>::SMEM_BYTES : Lay<false>::SMEM_BYTES;
     if (!(e->attr_done & 1u)) {
-        GZ_CUDA(e, cudaFuncSetAttribute(trunk_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        GZ_CUDA(e, cudaFuncSetAttribute(trunk_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, Lay<false>::SMEM_BYTES));
+        GZ_CUDA(e, cudaFuncSetAttribute(trunk_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, Lay<true>::SMEM_BYTES));
         e->attr_done |= 1u;
     }
     if (e->n_sm <= 0) {
@@ -1000,10 +1037,10 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
         ProfScope ps(e, PC_TRUNK_TC);
         TcConsts cst;
         memcpy(&cst, w.tc_consts.data(), sizeof(TcConsts));
-        trunk_tc_kernel<<<grid, THREADS, SMEM_BYTES, e->stream>>>(d_planes, w.tc_img, cst,
-                                                                   w.tc_inv[0], w.tc_inv[1], w.tc_inv[2],
-                                                                   reinterpret_cast<__half *>(e->tc_head),
-                                                                   d_count, maxB, g, want_dbg ? e->tc_dbg : nullptr, d_tl);
+        auto kern = dense ? trunk_tc_kernel<true> : trunk_tc_kernel<false>;
+        kern<<<grid, THREADS, smem_bytes, e->stream>>>(d_planes, w.tc_img, cst, w.tc_inv[0], w.tc_inv[1], w.tc_inv[2],
+                                                       reinterpret_cast<__half *>(e->tc_head), d_count, maxB, g,
+                                                       want_dbg ? e->tc_dbg : nullptr, d_tl);
     }
     if (d_tl) {
         std::vector<long long> h(2048);
