@@ -358,17 +358,17 @@ def run_ours(args):
                 "peak_source": pk_src + ", sustained bf16 (kernel timed inside a long step)",
                 "traffic": None}
         # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
-        # (profiles/r1_ncu_v5_summary.txt: dram__bytes_read.sum + dram__bytes_write.sum, one launch,
+        # (profiles/r1_ncu_v8_summary.txt: dram__bytes_read.sum + dram__bytes_write.sum, one launch,
         # 16384 leaves at 8x8); only quoted for the configuration it was captured on
         if dom == "trunk_tc" and args.board == 8 and args.games == 16384:
-            roof["traffic"] = 17244160 + 8448
-            roof["traffic_source"] = "profiles/r1_ncu_v5_summary.txt (ncu --set full, 1 launch; algorithmic input planes 16.8 MB)"
+            roof["traffic"] = 17240320 + 0
+            roof["traffic_source"] = "profiles/r1_ncu_v8_summary.txt (ncu --set full, 1 launch; algorithmic input planes 16.8 MB)"
         if dom in fl and dom_ms > 0:
             ach = ctr["leaf_evals"] * fl[dom] / (dom_ms * 1e-3) / 1e12
             roof.update({"achieved": ach, "frac": ach / pk["bf16_tflops_sustained"],
                          "issued_tflops": ach * (3.0 if dom == "trunk_tc" else 1.0),
                          "note": ("algorithmic FLOPs (2*MAC of the fp32 net, dense taps); the kernel issues 3 fp16 MMA passes "
-                                  "per product for fp32-grade accuracy and pads boards to a 9-wide line space (64/82 useful rows)"
+                                  "per product for fp32-grade accuracy; at 8x8 every M row of an MMA is a board cell (dense line space, 4 boards per 256-row group)"
                                   if dom == "trunk_tc" else ""),
                          "flops_per_leaf": fl[dom], "avg_launch_ms": dom_ms / max(dom_n, 1), "launches": dom_n,
                          "share_of_device_time": dom_ms / max(total_prof_ms, 1e-9)})
