@@ -216,7 +216,8 @@ extern "C" void gz_destroy(gz_engine *e)
                     e->sel_probs, e->out_states, e->out_pi, e->out_z, e->out_gid, e->out_ply, e->out_count,
                     e->gout_moves, e->gout_len, e->gout_winner, e->gout_gid, e->gout_count, e->counters,
                     e->roll_results, e->wts.w1, e->wts.w2, e->wts.w3, e->wts.wh, e->wts.wpfc, e->wts.wvfc,
-                    e->wts.bias, e->wts.tc_img, e->wts.tc_fcimg, e->tc_head, e->tc_dbg};
+                    e->wts.bias, e->wts.tc_img, e->wts.tc_fcimg, e->tc_head, e->tc_dbg,
+                    e->wts.tcw_img2, e->wts.tcw_img3, e->tcw_act1, e->tcw_act2, e->tcw_dbg};
     for (void *p : ptrs) if (p) cudaFree(p);
     gz_train_free(e);
     for (int i = 0; i < 16; ++i) if (e->wts.raw[i]) cudaFree(e->wts.raw[i]);
@@ -249,6 +250,7 @@ template <typename T> static int gz_upload(gz_engine *e, T **dst, const std::vec
 }
 
 #include "gz_net_tc.cu"
+#include "gz_net_tcw.cu"
 
 
 static void gz_conv_to_tap_major(const std::vector<float> &w, int cout, int cin, std::vector<float> &o)
@@ -305,6 +307,7 @@ int gz_net_prepare_weights(gz_engine *e, std::vector<float> h[16])
     t[w.off_bv2] = h[15][0];
     GZ_TRY(gz_upload(e, &e->wts.bias, t));
     if (gz_tc_supported(e)) GZ_TRY(gz_tc_prepare_weights(e, h));
+    else if (gz_tcw_supported(e)) GZ_TRY(gz_tcw_prepare_weights(e, h));
     return GZ_OK;
 }
 
@@ -369,9 +372,12 @@ int gzk_net_forward(gz_engine *e, const float *d_planes, const int32_t *d_count,
 {
     if (!e->wts.loaded) { e->err = "gz_set_weights has not been called"; return GZ_E_NOWEIGHTS; }
     GZ_TRY(gz_train_flush(e)); // weights trained on the device since the last forward
-    // net_impl: 0 = tcgen05 path when the trunk is the reference 32/64/128, 1 = fp32 CUDA-core path,
+    // net_impl: 0 = tcgen05 path (fused kernel for the reference trunk 32/64/128, layer-wise kernels of
+    // gz_net_tcw.cu for wider trunks) when it supports the configuration, 1 = fp32 CUDA-core path,
     // 2 = tcgen05 path or an error
     const int impl = e->cfg.net_impl;
+    if (impl != 1 && !gz_tc_supported(e) && gz_tcw_supported(e))
+        return gz_net_forward_tcw(e, d_planes, d_count, maxB, d_probs, d_values, false);
     if (impl == 2 || (impl == 0 && gz_tc_supported(e)))
         return gz_net_forward_tc(e, d_planes, d_count, maxB, d_probs, d_values, false);
     return gz_net_forward_ffma(e, d_planes, d_count, maxB, d_probs, d_values);
@@ -556,9 +562,29 @@ extern "C" int gz_debug_net_layers(gz_engine *e, const float *planes, int64_t B,
 {
     if (!e || !planes || B <= 0) return GZ_E_INVALID;
     if (!e->wts.loaded) { e->err = "gz_set_weights has not been called"; return GZ_E_NOWEIGHTS; }
-    if (!gz_tc_supported(e)) { e->err = "tcgen05 net path needs a square board and the 32/64/128 trunk"; return GZ_E_INVALID; }
+    const bool wide = !gz_tc_supported(e) && gz_tcw_supported(e);
+    if (!gz_tc_supported(e) && !wide) { e->err = "tcgen05 net path: unsupported board or trunk widths"; return GZ_E_INVALID; }
     GZ_CUDA(e, cudaSetDevice(e->cfg.device));
     const size_t S = e->S, N = (size_t)B;
+    if (wide) { // layer-wise kernels: act1 / act3 / head from the kernels' dumps, act2 decoded from its fp16 image
+        const size_t c1 = e->c1, c2 = e->c2, c3 = e->c3;
+        ArgStage a(e);
+        GZ_TRY(a.reserve(N * S * 20 + N * 8 + 2048));
+        const float *dp = a.in(planes, N * 4 * S);
+        float *dpr = a.out(probs, N * S);
+        float *dv = a.out(values, N);
+        if (a.rc) return a.rc;
+        if (!dpr || !dv) { e->err = "gz_debug_net_layers: probs and values are required"; return GZ_E_INVALID; }
+        GZ_TRY(gz_train_flush(e));
+        GZ_TRY(gz_net_forward_tcw(e, dp, nullptr, B, dpr, dv, true));
+        GZ_TRY(a.finish());
+        GZ_CUDA(e, cudaStreamSynchronize(e->stream));
+        if (act1) GZ_CUDA(e, cudaMemcpy(act1, e->tcw_dbg, N * S * c1 * 4, cudaMemcpyDefault));
+        if (act2) GZ_TRY(gz_tcw_decode_act2(e, B, act2));
+        if (act3) GZ_CUDA(e, cudaMemcpy(act3, e->tcw_dbg + N * S * (c1 + c2), N * S * c3 * 4, cudaMemcpyDefault));
+        if (head) GZ_CUDA(e, cudaMemcpy(head, e->tcw_dbg + N * S * (c1 + c2 + c3), N * 6 * S * 4, cudaMemcpyDefault));
+        return GZ_OK;
+    }
     ArgStage a(e);
     GZ_TRY(a.reserve(N * S * 20 + N * 8 + 2048));
     const float *dp = a.in(planes, N * 4 * S);

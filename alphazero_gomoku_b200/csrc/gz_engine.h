@@ -50,6 +50,8 @@ struct NetWeights {
     std::vector<float> tc_consts; // host copy of the tcgen05 trunk's epilogue constants (kernel parameter)
     uint8_t *tc_img = nullptr; // tcgen05 path: fp16 hi/lo conv weight image (gz_net_tc.cu layout)
     float tc_inv[5] = {1.f, 1.f, 1.f, 1.f, 1.f}; // 1 / power-of-two weight scale of conv1..3, policy FC, value FC1
+    uint8_t *tcw_img2 = nullptr, *tcw_img3 = nullptr; // wide-trunk tcgen05 path: conv2 / conv3 weight images (gz_net_tcw.cu)
+    float tcw_inv[2] = {1.f, 1.f};
     bool loaded = false;
 };
 
@@ -94,6 +96,9 @@ struct gz_engine {
     float *tc_head;            // tcgen05 path: ReLU(1x1 head convs), fp16 hi/lo image (see trunk_tc_kernel)
     float *tc_dbg;             // optional per-layer dump for parity tests
     int64_t tc_cap, tc_dbg_cap;
+    uint8_t *tcw_act1, *tcw_act2; // wide-trunk path: fp16 hi/lo activation images of conv1 / conv2 (per group)
+    float *tcw_dbg;
+    int64_t tcw_cap, tcw_dbg_cap; // groups / boards
     int n_sm;
     unsigned attr_done;        // bit i: cudaFuncSetAttribute done for kernel i
     // staging for host<->device argument copies

@@ -866,16 +866,17 @@ static bool gz_tc_dense(const gz_engine *e)
     return e->W == 8 && !padded;
 }
 
-static TcGeom gz_tc_geom(const gz_engine *e)
+static TcGeom gz_tc_geom(const gz_engine *e, bool dense)
 {
     TcGeom g;
     g.W = e->W; g.S = e->S; g.P = e->W + 1;
     g.BS = e->W * g.P + g.P + 1;
-    g.NB = gz_tc_dense(e) ? 4 : 1 + (tc::ROWS - e->W * g.P) / g.BS;
+    g.NB = dense ? 4 : 1 + (tc::ROWS - e->W * g.P) / g.BS;
     g.Jp = 2 * ((4 * e->S + 31) / 32); // both FC sections are padded to whole stages of K = 32
     g.J = g.Jp + 2 * ((2 * e->S + 31) / 32);
     return g;
 }
+static TcGeom gz_tc_geom(const gz_engine *e) { return gz_tc_geom(e, gz_tc_dense(e)); }
 
 // power-of-two scale that puts max|w| * s into [128, 256)
 static float gz_tc_scale(const std::vector<float> &w)
@@ -895,6 +896,7 @@ static void gz_tc_split(float v, float &hi_back, __half &hi, __half &lo)
     lo = __float2half_rn(v - hi_back);
 }
 
+int gz_tc_prepare_fc(gz_engine *e, std::vector<float> h[16]);
 // builds the fp16 weight image (see tc:: layout constants) from torch-layout fp32 conv weights
 int gz_tc_prepare_weights(gz_engine *e, std::vector<float> h[16])
 {
@@ -953,6 +955,14 @@ int gz_tc_prepare_weights(gz_engine *e, std::vector<float> h[16])
         for (int q = 0; q < 4; ++q) b[C1 + C2 + C3 + q] = h[7][q];
         for (int q = 0; q < 2; ++q) b[C1 + C2 + C3 + 4 + q] = h[11][q];
     }
+    GZ_TRY(gz_tc_prepare_fc(e, h));
+    e->wts.tc_inv[0] = 1.f / s1; e->wts.tc_inv[1] = 1.f / s2; e->wts.tc_inv[2] = 1.f / s3;
+    return GZ_OK;
+}
+
+// fp16 hi/lo image of both FC-head weight matrices for heads_tc_kernel
+int gz_tc_prepare_fc(gz_engine *e, std::vector<float> h[16])
+{
     {   // FC image: per K = 16 step [pass hi|lo][8-k chunk 2][N rows][8 halves]; policy steps (N = Np)
         // first, then value FC1 steps (N = 64).  Rows / k beyond the real matrix stay zero.
         const int S = e->S, Np = (S + 15) & ~15;
@@ -974,7 +984,6 @@ int gz_tc_prepare_weights(gz_engine *e, std::vector<float> h[16])
         GZ_TRY(gz_upload(e, &e->wts.tc_fcimg, fimg));
         e->wts.tc_inv[3] = 1.f / sp; e->wts.tc_inv[4] = 1.f / sv;
     }
-    e->wts.tc_inv[0] = 1.f / s1; e->wts.tc_inv[1] = 1.f / s2; e->wts.tc_inv[2] = 1.f / s3;
     return GZ_OK;
 }
 
@@ -1001,6 +1010,9 @@ static int gz_tc_ensure_buffers(gz_engine *e, int64_t B, bool want_dbg)
     }
     return GZ_OK;
 }
+
+static int gz_tc_launch_heads(gz_engine *e, const TcGeom &g, float *d_probs, float *d_values, const int32_t *d_count,
+                              int64_t maxB);
 
 static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t *d_count, int64_t maxB,
                              float *d_probs, float *d_values, bool want_dbg)
@@ -1065,6 +1077,17 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
             fclose(f);
         }
     }
+    GZ_TRY(gz_tc_launch_heads(e, g, d_probs, d_values, d_count, maxB));
+    e->launches += 2;
+    GZ_CUDA(e, cudaGetLastError());
+    return GZ_OK;
+}
+
+// both FC heads on the head activations in e->tc_head (written by the trunk's back end)
+static int gz_tc_launch_heads(gz_engine *e, const TcGeom &g, float *d_probs, float *d_values, const int32_t *d_count,
+                              int64_t maxB)
+{
+    const NetWeights &w = e->wts;
     FcTc fw;
     fw.wimg = w.tc_fcimg; fw.bp = w.bias + w.off_bp; fw.bv = w.bias + w.off_bv;
     fw.wv2 = w.bias + w.off_wv2; fw.bv2 = w.bias + w.off_bv2;
@@ -1083,7 +1106,5 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
         heads_tc_kernel<<<(unsigned)((maxB + 127) / 128), fct::THREADS, fct::OFF_RING + (size_t)fw.ns * slot_bytes, e->stream>>>(
             reinterpret_cast<const uint8_t *>(e->tc_head), fw, d_probs, d_values, d_count, maxB);
     }
-    e->launches += 2;
-    GZ_CUDA(e, cudaGetLastError());
     return GZ_OK;
 }

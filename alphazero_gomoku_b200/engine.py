@@ -193,12 +193,13 @@ class Engine:
         return probs, values
 
     def debug_net_layers(self, planes):
-        """tensor-core path with per-layer activations: dict(act1 [B,S,32], act2 [B,S,64],
-        act3 [B,S,128], head [B,6,S], probs [B,S], values [B])."""
+        """tensor-core path with per-layer activations: dict(act1 [B,S,c1], act2 [B,S,c2],
+        act3 [B,S,c3], head [B,6,S], probs [B,S], values [B])."""
         planes = np.ascontiguousarray(planes, dtype=np.float32)
         B, S = planes.shape[0], self.S
-        out = {"act1": np.zeros((B, S, 32), np.float32), "act2": np.zeros((B, S, 64), np.float32),
-               "act3": np.zeros((B, S, 128), np.float32), "head": np.zeros((B, 6, S), np.float32),
+        c1, c2, c3 = self.trunk
+        out = {"act1": np.zeros((B, S, c1), np.float32), "act2": np.zeros((B, S, c2), np.float32),
+               "act3": np.zeros((B, S, c3), np.float32), "head": np.zeros((B, 6, S), np.float32),
                "probs": np.zeros((B, S), np.float32), "values": np.zeros(B, np.float32)}
         self._ck(self.L.gz_debug_net_layers(self._h, _ptr(planes), B, _ptr(out["act1"]), _ptr(out["act2"]),
                                             _ptr(out["act3"]), _ptr(out["head"]), _ptr(out["probs"]),

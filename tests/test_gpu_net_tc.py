@@ -39,10 +39,10 @@ def _layers_ref(arrs, planes, dtype):
     return res
 
 
-def _random_weights(rng, w, scale=1.0):
+def _random_weights(rng, w, scale=1.0, trunk=(32, 64, 128)):
     from alphazero_gomoku_b200.engine import weight_shapes
     arrs = []
-    for s in weight_shapes(w, w):
+    for s in weight_shapes(w, w, trunk):
         fan = int(np.prod(s[1:])) if len(s) > 1 else 1
         arrs.append((rng.randn(*s) * (scale * np.sqrt(2.0 / fan) if len(s) > 1 else 0.1)).astype(np.float32))
     return arrs
@@ -121,12 +121,44 @@ def test_tc_large_batch_matches_small_batches():
     e.close()
 
 
+@pytest.mark.parametrize("w,B,trunk", [(15, 5, (64, 128, 256)), (8, 700, (64, 128, 256)), (6, 41, (16, 64, 64)),
+                                       (9, 333, (64, 128, 128)), (15, 160, (32, 64, 256)), (3, 1, (128, 128, 192))])
+def test_tc_wide_trunk_layers_vs_torch(w, B, trunk):
+    """Wider trunks (BASELINE config C4) take the layer-wise tcgen05 kernels of gz_net_tcw.cu: same
+    per-layer and output tolerances as the fused kernel, against float64 torch; the fp32 CUDA-core
+    path on the same weights is the second witness."""
+    from alphazero_gomoku_b200 import Engine
+    rng = np.random.RandomState(7000 * w + B)
+    arrs = _random_weights(rng, w, scale=1.3, trunk=trunk)
+    planes = (rng.rand(B, 4, w, w) < 0.35).astype(np.float32)
+    planes[0] = 0.0
+    e = Engine(width=w, height=w, n_in_row=3, net_impl=2, trunk=trunk)
+    e.set_weights(arrs)
+    got = e.debug_net_layers(planes)
+    ref = _layers_ref(arrs, planes, __import__("torch").float64)
+    worst = _report("wide %dx%d B=%d %s" % (w, w, B, trunk), got, ref)
+    for k in ("act1", "act2", "act3", "head"):
+        assert worst[k][1] < 2e-5, (k, worst[k])
+    assert worst["probs"][0] < NET_TOL and worst["values"][0] < NET_TOL
+    probs, vals = e.net_forward(planes)
+    assert np.array_equal(probs, got["probs"]) and np.array_equal(vals, got["values"])
+    # a smaller batch afterwards (stale groups in the activation images must not leak)
+    k = max(1, B // 3)
+    p2, v2 = e.net_forward(planes[:k])
+    assert np.array_equal(p2, probs[:k]) and np.array_equal(v2, vals[:k])
+    e2 = Engine(width=w, height=w, n_in_row=3, net_impl=1, trunk=trunk)
+    e2.set_weights(arrs)
+    p1, v1 = e2.net_forward(planes)
+    assert np.abs(p1 - probs).max() < NET_TOL and np.abs(v1 - vals).max() < NET_TOL
+    e.close(); e2.close()
+
+
 def test_tc_rejects_other_trunks():
     from alphazero_gomoku_b200 import Engine
-    e = Engine(width=6, height=6, n_in_row=4, net_impl=2, trunk=(64, 128, 256))
+    e = Engine(width=6, height=6, n_in_row=4, net_impl=2, trunk=(64, 192, 256))
     rng = np.random.RandomState(0)
     from alphazero_gomoku_b200.engine import weight_shapes
-    e.set_weights([rng.randn(*s).astype(np.float32) * 0.05 for s in weight_shapes(6, 6, (64, 128, 256))])
+    e.set_weights([rng.randn(*s).astype(np.float32) * 0.05 for s in weight_shapes(6, 6, (64, 192, 256))])
     with pytest.raises(Exception):
         e.net_forward(np.zeros((1, 4, 6, 6), np.float32))
     e.close()
