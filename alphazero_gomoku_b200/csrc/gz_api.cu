@@ -217,7 +217,7 @@ extern "C" void gz_destroy(gz_engine *e)
                     e->gout_moves, e->gout_len, e->gout_winner, e->gout_gid, e->gout_count, e->counters,
                     e->roll_results, e->wts.w1, e->wts.w2, e->wts.w3, e->wts.wh, e->wts.wpfc, e->wts.wvfc,
                     e->wts.bias, e->wts.tc_img, e->wts.tc_fcimg, e->tc_head, e->tc_dbg,
-                    e->wts.tcw_img2, e->wts.tcw_img3, e->tcw_act1, e->tcw_act2, e->tcw_dbg};
+                    e->wts.tcw_img1, e->wts.tcw_img2, e->wts.tcw_img3, e->tcw_a0, e->tcw_act1, e->tcw_act2, e->tcw_dbg};
     for (void *p : ptrs) if (p) cudaFree(p);
     gz_train_free(e);
     for (int i = 0; i < 16; ++i) if (e->wts.raw[i]) cudaFree(e->wts.raw[i]);

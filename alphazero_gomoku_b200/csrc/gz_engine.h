@@ -50,8 +50,8 @@ struct NetWeights {
     std::vector<float> tc_consts; // host copy of the tcgen05 trunk's epilogue constants (kernel parameter)
     uint8_t *tc_img = nullptr; // tcgen05 path: fp16 hi/lo conv weight image (gz_net_tc.cu layout)
     float tc_inv[5] = {1.f, 1.f, 1.f, 1.f, 1.f}; // 1 / power-of-two weight scale of conv1..3, policy FC, value FC1
-    uint8_t *tcw_img2 = nullptr, *tcw_img3 = nullptr; // wide-trunk tcgen05 path: conv2 / conv3 weight images (gz_net_tcw.cu)
-    float tcw_inv[2] = {1.f, 1.f};
+    uint8_t *tcw_img1 = nullptr, *tcw_img2 = nullptr, *tcw_img3 = nullptr; // wide-trunk tcgen05 path: conv weight images (gz_net_tcw.cu)
+    float tcw_inv[3] = {1.f, 1.f, 1.f}; // 1 / weight scale of conv2, conv3, conv1
     bool loaded = false;
 };
 
@@ -96,7 +96,7 @@ struct gz_engine {
     float *tc_head;            // tcgen05 path: ReLU(1x1 head convs), fp16 hi/lo image (see trunk_tc_kernel)
     float *tc_dbg;             // optional per-layer dump for parity tests
     int64_t tc_cap, tc_dbg_cap;
-    uint8_t *tcw_act1, *tcw_act2; // wide-trunk path: fp16 hi/lo activation images of conv1 / conv2 (per group)
+    uint8_t *tcw_a0, *tcw_act1, *tcw_act2; // wide-trunk path: fp16 hi/lo images of the planes and of conv1 / conv2's outputs (per group)
     float *tcw_dbg;
     int64_t tcw_cap, tcw_dbg_cap; // groups / boards
     int n_sm;

@@ -41,7 +41,13 @@ def net_flops(S, trunk=(32, 64, 128)):
     return conv
 
 
-def load_weights(width):
+def load_weights(width, trunk=(32, 64, 128)):
+    if tuple(trunk) != (32, 64, 128):  # no shipped weights for wider trunks: seeded He init
+        from alphazero_gomoku_b200.engine import weight_shapes
+        rng = np.random.RandomState(0)
+        arrs = [(rng.randn(*s) * (np.sqrt(2.0 / int(np.prod(s[1:]))) if len(s) > 1 else 0.1)).astype(np.float32)
+                for s in weight_shapes(width, width, tuple(trunk))]
+        return arrs, "seeded random init (no shipped weights for trunk %s)" % (tuple(trunk),)
     path = os.path.join(ROOT, "tests", "golden", "weights_%d_%d_%d.npz" % (width, width, 5 if width >= 8 else 4))
     if os.path.exists(path):
         z = np.load(path)
@@ -209,7 +215,7 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     stream = torch.cuda.Stream(device=dev)
-    arrs, wname = load_weights(args.board)
+    arrs, wname = load_weights(args.board, args.trunk)
     # weights travel the way an update would: rank 0 owns them, NCCL broadcast (NVLink)
     flat = torch.from_numpy(np.concatenate([a.reshape(-1) for a in arrs])).to(dev)
     if world > 1:
@@ -220,7 +226,7 @@ def run_ours(args):
     dev_arrs = list(torch.split(flat, sizes))
     eng = Engine(width=args.board, height=args.board, n_in_row=args.n_in_row, n_games=args.games,
                  n_playout=args.playouts, seed=args.seed + rank, game_id_base=rank << 40, device=local,
-                 stream=stream.cuda_stream, nodes_per_game=args.nodes_per_game)
+                 stream=stream.cuda_stream, nodes_per_game=args.nodes_per_game, trunk=tuple(args.trunk))
     eng.set_weights(dev_arrs)
     eng.selfplay_begin(temp=1.0, recycle=True)
 
@@ -348,7 +354,7 @@ def run_ours(args):
 
     if rank == 0:
         S = args.board * args.board
-        fl = net_flops(S)
+        fl = net_flops(S, tuple(args.trunk))
         pk, pk_src = peaks()
         # dominant kernel = the class with the largest share of device time
         dom = max(prof, key=lambda k: prof[k][0])
@@ -438,6 +444,8 @@ def main():
     ap.add_argument("--n-in-row", type=int, default=5)
     ap.add_argument("--playouts", type=int, default=400)
     ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--trunk", type=int, nargs=3, default=[32, 64, 128],
+                    help="conv trunk widths (BASELINE config C4 'wider trunk': 64 128 256; seeded random weights)")
     ap.add_argument("--cpu-plies", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--prefill-plies", type=int, default=24,
