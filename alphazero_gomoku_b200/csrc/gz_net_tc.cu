@@ -328,7 +328,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         const uint32_t t_lane = ((uint32_t)(q * 32)) << 16;
         __half *s_hst = reinterpret_cast<__half *>(smem + OFF_HST);
         uint32_t ph3 = 0;
-        int tl_b = 0;
+        int tl_b = 0, tl_w = 0; // tl_w: per-warp release times of the conv3 accumulators (first 24 groups)
 #define TC_MARK_BACK() /* back-end marks (3 per group): conv3 done, accumulators released, copy-out done */ \
     do {                                                                           \
         if (timeline && blockIdx.x == 0 && tid == 320 && tl_b < 256) timeline[1024 + tl_b++] = clock64(); \
@@ -402,6 +402,7 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             tc_fence_before();
             __syncwarp();
             if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_c3free) : "memory");
+            if (timeline && blockIdx.x == 0 && lane == 0 && tl_w < 24) timeline[1400 + (warp - 10) * 24 + tl_w++] = clock64();
             TC_MARK_BACK();
             // copy out as 16-byte chunks of heads_tc_kernel's A operand: step j = [pass 2][chunk 2][board 128][8]
             asm volatile("bar.sync 2, 256;" ::: "memory");
@@ -607,8 +608,8 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                     c3_phase ^= 1u;
                 }
                 first_group = false;
-                tc_fence_after();
                 TC_MARK_MMA(); // m3: conv3 accumulators free
+                tc_fence_after();
                 issue_conv3(0, 4);
                 tc_bar_sync_all(); // B: act2 channels 32-63 written, next group's planes staged
                 TC_MARK_MMA(); // m4: barrier B passed
@@ -1073,6 +1074,11 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
             for (int i = 0; i < 256 && h[256 + i]; ++i) fprintf(f, "%lld%c", h[256 + i] - h[0], (i % 7 == 6) ? '\n' : ' ');
             fprintf(f, "\nback\n");
             for (int i = 0; i < 256 && h[1024 + i]; ++i) fprintf(f, "%lld%c", h[1024 + i] - h[0], (i % 3 == 2) ? '\n' : ' ');
+            fprintf(f, "\nrelease (per back-end warp, first 24 groups)\n");
+            for (int wv = 0; wv < 8; ++wv) {
+                for (int i = 0; i < 24 && h[1400 + wv * 24 + i]; ++i) fprintf(f, "%lld ", h[1400 + wv * 24 + i] - h[0]);
+                fprintf(f, "\n");
+            }
             fprintf(f, "\n");
             fclose(f);
         }

@@ -7,6 +7,7 @@ txt = open(sys.argv[1]).read().strip().split('launch ')
 blk = [b for b in txt if b.startswith('B=')][-1]
 front, rest = blk.split('cta_ns')
 cta, mma = rest.split('mma')
+mma = mma.split('back')[0]
 F = [list(map(int, l.split())) for l in front.splitlines()[1:] if len(l.split()) == 4]
 M = [list(map(int, l.split())) for l in mma.splitlines() if len(l.split()) == 7]
 med = lambda x: int(st.median(x))
