@@ -241,11 +241,25 @@ static void gz_weight_sizes(const gz_engine *e, size_t n[16])
     n[12] = 64 * 2 * S; n[13] = 64; n[14] = 64; n[15] = 1;
 }
 
+// Device copy of a host array.  A weight update (gz_set_weights every step of the bench's e2e region,
+// once per policy update in train.py) re-uploads arrays of unchanged size: the allocation is reused then,
+// which keeps cudaFree (a device-wide synchronisation) and cudaMalloc off that path.
 template <typename T> static int gz_upload(gz_engine *e, T **dst, const std::vector<T> &src)
 {
-    if (*dst) { cudaFree(*dst); *dst = nullptr; }
-    GZ_CUDA(e, cudaMalloc((void **)dst, src.size() * sizeof(T)));
-    GZ_CUDA(e, cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
+    const size_t bytes = src.size() * sizeof(T);
+    if (*dst) {
+        auto it = e->upload_bytes.find((void *)*dst);
+        if (it == e->upload_bytes.end() || it->second != bytes) {
+            if (it != e->upload_bytes.end()) e->upload_bytes.erase(it);
+            cudaFree(*dst);
+            *dst = nullptr;
+        }
+    }
+    if (!*dst) {
+        GZ_CUDA(e, cudaMalloc((void **)dst, bytes ? bytes : 1));
+        e->upload_bytes[(void *)*dst] = bytes;
+    }
+    GZ_CUDA(e, cudaMemcpy(*dst, src.data(), bytes, cudaMemcpyHostToDevice));
     return GZ_OK;
 }
 

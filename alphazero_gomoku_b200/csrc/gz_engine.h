@@ -3,6 +3,7 @@
 #include "../../include/gomoku_b200.h"
 #include "gz_common.cuh"
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 // Tree node block (one per expanded node, SoA inside the block, Sp = S rounded up to 32):
@@ -104,6 +105,7 @@ struct gz_engine {
     // staging for host<->device argument copies
     void *stage;
     size_t stage_bytes;
+    std::unordered_map<void *, size_t> upload_bytes; // sizes of the arrays gz_upload allocated (reused on equal size)
     // self-play
     float sp_temp;
     int sp_recycle;

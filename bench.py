@@ -25,6 +25,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
+_JSON_LINE = []  # the one line main() prints to the real stdout at the end
 METRIC = "mcts_playouts_per_sec"
 UNIT = "playouts/s"
 
@@ -184,7 +185,7 @@ def run_reference(args):
                                        % (threads, args.playouts)},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    _JSON_LINE.append(json.dumps(line))
 
 
 def workload_config(args, wname, games):
@@ -279,6 +280,16 @@ def run_ours(args):
     pr = torch.zeros((args.games, args.board * args.board), dtype=torch.float32).pin_memory()
     h2d = sum(a.numel() * 4 for a in host_w)
     d2h_total = 0
+    # pinned host buffers for the finished-game samples of a step (a step finishes about G plies' worth of
+    # samples on average; whatever does not fit stays in the device ring for the next drain)
+    cap = 6 * args.games
+    S_ = args.board * args.board
+    pinned = {"states": torch.zeros((cap, 4, args.board, args.board), dtype=torch.float32).pin_memory(),
+              "pis": torch.zeros((cap, S_), dtype=torch.float32).pin_memory(),
+              "zs": torch.zeros(cap, dtype=torch.float32).pin_memory(),
+              "game_ids": torch.zeros(cap, dtype=torch.int64).pin_memory(),
+              "plies": torch.zeros(cap, dtype=torch.int32).pin_memory()}
+    drain_bufs = {k: v.numpy() for k, v in pinned.items()}
     barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
@@ -286,7 +297,7 @@ def run_ours(args):
         eng.set_weights([a.numpy() for a in host_w])          # H2D: the step's inputs (weights)
         eng.selfplay_step(1)
         eng.selfplay_last(mv.numpy(), pr.numpy())             # D2H: (move, move_probs) of the step
-        d = eng.selfplay_drain()                              # D2H: samples of games that finished
+        d = eng.selfplay_drain(max_samples=cap, bufs=drain_bufs)  # D2H: samples of games that finished
         d2h_total += mv.numel() * 4 + pr.numel() * 4 + sum(v.nbytes for v in d.values())
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
@@ -400,7 +411,7 @@ def run_ours(args):
                     "ms_per_step": e2e_ms_max / max(args.steps, 1),
                     "net_evals_per_playout": float(ctr2["leaf_evals"]) / max(float(ctr2["playouts"]), 1.0),
                     "what": "per step: gz_set_weights from pinned host arrays, gz_selfplay_step(1), "
-                            "gz_selfplay_last + gz_selfplay_drain into host buffers; these steps follow the "
+                            "gz_selfplay_last + gz_selfplay_drain into pinned host buffers; these steps follow the "
                             "device-timed ones in the same games (net_evals_per_playout says how many playouts "
                             "needed the net: terminal leaves do not)"},
             "gpu_launches": int(tot_launch),
@@ -427,7 +438,7 @@ def run_ours(args):
             line["cpu_baseline"] = cpu_baseline(arrs, args.board, args.n_in_row, args.playouts, args.cpu_plies)
         if tot_over:
             line["invalid"] = "tree pool overflowed: raise nodes_per_game"
-        print(json.dumps(line))
+        _JSON_LINE.append(json.dumps(line))
     eng.close()
     if world > 1:
         dist.destroy_process_group()
@@ -458,10 +469,22 @@ def main():
     ap.add_argument("--prof-stride", type=int, default=16,
                     help="CUDA-event pairs around every N-th launch of each kernel class inside the timed region")
     args = ap.parse_args()
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_ours(args)
+    # stdout carries exactly ONE JSON line (the driver parses it): libraries that print to fd 1 (NCCL's
+    # "NCCL version ..." banner, for one) are sent to stderr for the duration of the run
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        if args.impl == "reference":
+            run_reference(args)
+        else:
+            run_ours(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+    if _JSON_LINE:
+        print(_JSON_LINE[-1], flush=True)
 
 
 if __name__ == "__main__":
