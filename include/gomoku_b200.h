@@ -55,11 +55,13 @@ typedef struct {
     float c_puct;            /* 5 */
     float dirichlet_alpha;   /* 0.1 */
     float dirichlet_eps;     /* 0.25 */
-    int32_t trunk[3];        /* conv widths, reference 32/64/128; 0 = reference */
+    int32_t trunk[3];        /* conv widths, reference 32/64/128; 0 = reference.  Wider trunks (every width a
+                                multiple of 32, c1, c2 <= 128, c3 <= 256, e.g. 64/128/256) also run on tcgen05 */
     uint64_t seed;           /* Philox key */
     uint64_t game_id_base;   /* global id of slot 0's first game (rank * G in multi-GPU) */
     int32_t device;          /* CUDA ordinal */
-    int32_t net_impl;        /* 0 = default, 1 = fp32 CUDA-core path, 2 = tcgen05 path */
+    int32_t net_impl;        /* 0 = default (tcgen05 where the trunk is supported, else fp32 CUDA cores),
+                                1 = fp32 CUDA-core path, 2 = tcgen05 path or GZ_E_INVALID */
     void *stream;            /* cudaStream_t to run on; NULL = engine creates its own */
 } gz_config;
 
