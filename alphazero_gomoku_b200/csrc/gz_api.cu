@@ -131,7 +131,8 @@ static int gz_alloc_all(gz_engine *e)
     GZ_TRY(gz_dalloc(e, &e->leaf_state, G));
     GZ_TRY(gz_dalloc(e, &e->leaf_value, G));
     GZ_TRY(gz_dalloc(e, &e->leaf_slot, G));
-    GZ_TRY(gz_dalloc(e, &e->leaf_count, 1));
+    GZ_TRY(gz_dalloc(e, &e->leaf_count_pair, 2));
+    e->leaf_count = e->leaf_count_pair;
     GZ_TRY(gz_dalloc(e, &e->leaf_planes, G * 4 * S));
     GZ_TRY(gz_dalloc(e, &e->leaf_board, G));
     GZ_TRY(gz_dalloc(e, &e->leaf_meta, G));
@@ -211,7 +212,7 @@ extern "C" void gz_destroy(gz_engine *e)
     cudaStreamSynchronize(e->stream);
     void *ptrs[] = {e->boards, e->meta, e->active, e->pool, e->free_stack, e->free_top, e->root_node,
                     e->root_N, e->root_Q, e->path, e->path_len, e->leaf_state, e->leaf_value, e->leaf_slot,
-                    e->leaf_count, e->leaf_planes, e->leaf_board, e->leaf_meta, e->net_probs, e->net_values,
+                    e->leaf_count_pair, e->leaf_planes, e->leaf_board, e->leaf_meta, e->net_probs, e->net_values,
                     e->act1, e->act2, e->act3, e->stage, e->sp_moves, e->sp_pi, e->sp_game_id, e->sel_moves,
                     e->sel_probs, e->out_states, e->out_pi, e->out_z, e->out_gid, e->out_ply, e->out_count,
                     e->gout_moves, e->gout_len, e->gout_winner, e->gout_gid, e->gout_count, e->counters,

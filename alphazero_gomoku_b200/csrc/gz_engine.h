@@ -84,7 +84,8 @@ struct gz_engine {
     int8_t *leaf_state;  // [G] 0 eval, 1 terminal, 2 inactive
     double *leaf_value;  // [G] terminal value (side to move at the leaf)
     int32_t *leaf_slot;  // [G] row in the compacted leaf batch
-    int32_t *leaf_count; // [1]
+    int32_t *leaf_count; // the counter of the current wave: one of leaf_count_pair[2] (gzk_expand_select)
+    int32_t *leaf_count_pair;
     float *leaf_planes;  // [G][4][S] compacted rows
     GameBoard *leaf_board; // [G] leaf position (by game)
     GameMeta *leaf_meta;   // [G]

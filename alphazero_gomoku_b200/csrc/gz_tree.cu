@@ -27,6 +27,7 @@ struct TreeParams {
     int8_t *leaf_state;
     double *leaf_value;
     int32_t *leaf_slot, *leaf_count;
+    int32_t *leaf_zero; // fused wave kernels: the counter of the wave whose leaves were just evaluated, reset for re-use (or null)
     float *leaf_planes;
     GameBoard *leaf_board;
     GameMeta *leaf_meta;
@@ -552,6 +553,7 @@ expand_select_small_kernel(TreeParams p, const float *__restrict__ priors, const
     const int g = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     __shared__ SelStats ss;
     if (threadIdx.x == 0) { ss.levels = 0; ss.children = 0; ss.playouts = 0; ss.done = 0; }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && p.leaf_zero) *p.leaf_zero = 0; // see gzk_expand_select
     __syncthreads();
     unsigned lv = 0, ch = 0, pl = 0;
     if (g < p.G) gz_expand_select_game<NSL, WT>(p, g, lane, priors, values, lv, ch, pl);
@@ -567,6 +569,7 @@ expand_select_kernel(TreeParams p, const float *__restrict__ priors, const float
     const int g = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     __shared__ SelStats ss;
     if (threadIdx.x == 0) { ss.levels = 0; ss.children = 0; ss.playouts = 0; ss.done = 0; }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && p.leaf_zero) *p.leaf_zero = 0; // see gzk_expand_select
     __syncthreads();
     unsigned lv = 0, ch = 0, pl = 0;
     if (g < p.G) {
@@ -671,7 +674,7 @@ static TreeParams gz_tree_params(gz_engine *e)
     p.free_stack = e->free_stack; p.free_top = e->free_top; p.root_node = e->root_node;
     p.root_N = e->root_N; p.root_Q = e->root_Q; p.path = e->path; p.path_len = e->path_len;
     p.leaf_state = e->leaf_state; p.leaf_value = e->leaf_value; p.leaf_slot = e->leaf_slot;
-    p.leaf_count = e->leaf_count; p.leaf_planes = e->leaf_planes; p.leaf_board = e->leaf_board;
+    p.leaf_count = e->leaf_count; p.leaf_zero = nullptr; p.leaf_planes = e->leaf_planes; p.leaf_board = e->leaf_board;
     p.leaf_meta = e->leaf_meta; p.ctr = e->counters;
     p.G = e->G; p.W = e->W; p.H = e->H; p.S = e->S; p.Sp = e->Sp; p.n_in_row = e->n_in_row;
     p.cap = e->cap; p.c_puct = e->cfg.c_puct;
@@ -690,7 +693,9 @@ int gzk_tree_reset(gz_engine *e)
 
 int gzk_select(gz_engine *e, bool pure)
 {
-    GZ_CUDA(e, cudaMemsetAsync(e->leaf_count, 0, sizeof(int32_t), e->stream));
+    // the leaf counter is one of a pair (see gzk_expand_select): a search starts on the first with both clear
+    e->leaf_count = e->leaf_count_pair;
+    GZ_CUDA(e, cudaMemsetAsync(e->leaf_count_pair, 0, 2 * sizeof(int32_t), e->stream));
     TreeParams p = gz_tree_params(e);
     ProfScope ps(e, PC_SELECT);
     if (pure) select_kernel<true><<<gz_warp_blocks(e->G, 4), 128, 0, e->stream>>>(p);
@@ -712,10 +717,16 @@ int gzk_expand_backup(gz_engine *e, const float *d_priors, const float *d_values
 
 int gzk_expand_select(gz_engine *e, const float *d_priors, const float *d_values)
 {
-    GZ_CUDA(e, cudaMemsetAsync(e->leaf_count, 0, sizeof(int32_t), e->stream));
+    // No memset between the net kernels and this one: the leaves of the next wave are counted in the OTHER
+    // counter of the pair (left at zero by the fused kernel before this one, or by gzk_select), and this
+    // kernel resets the counter the net has just consumed.  e->leaf_count always names the counter the next
+    // net call reads.
+    int32_t *consumed = e->leaf_count;
+    e->leaf_count = consumed == e->leaf_count_pair ? e->leaf_count_pair + 1 : e->leaf_count_pair;
     ProfScope ps(e, PC_SELECT);
     const unsigned grid = gz_warp_blocks(e->G, 4);
-    const TreeParams tp = gz_tree_params(e);
+    TreeParams tp = gz_tree_params(e);
+    tp.leaf_zero = consumed;
     const bool sq = e->W == e->H;
     // round-trip-minimal kernel: NSL = Sp / 32 child slots per lane, board side compile-time for the
     // reference's usual sizes; other sizes take the generic fused kernel
