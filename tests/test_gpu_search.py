@@ -167,6 +167,56 @@ def test_search_with_net_vs_oracle_many_games():
     e.close()
 
 
+def test_search_with_wide_trunk_vs_oracle():
+    """BASELINE config C4's 'wider conv trunk' (64/128/256) goes through the layer-wise tcgen05 kernels
+    (gz_net_tcw.cu) inside the search as well: visit distributions against the C oracle's MCTS with its
+    own fp32 net of the same widths, and self-play on top of it produces legal finished games."""
+    from oracle import orc
+    from alphazero_gomoku_b200.engine import weight_shapes
+    w, n, G, P, trunk = 9, 5, 24, 120, (64, 128, 256)
+    wr = np.random.RandomState(21)
+    arrs = [(wr.randn(*sh) * (np.sqrt(2.0 / int(np.prod(sh[1:]))) if len(sh) > 1 else 0.1)).astype(np.float32)
+            for sh in weight_shapes(w, w, trunk)]
+    rng = np.random.RandomState(12)
+    boards, lists = _random_positions(rng, w, n, G, max_plies=16)
+    e = _engine(w, w, n, n_games=G, n_playout=P, trunk=trunk, net_impl=2)
+    e.set_weights(arrs)
+    for g, mv in enumerate(lists):
+        e.boards_set(g, mv)
+    e.search(P)
+    vis, _ = e.root_visits()
+    onet = orc.Net(w, w, arrs)
+    exact, worst = 0, 0.0
+    for g, b in enumerate(boards):
+        m = orc.MCTS(5, P, orc.EVAL_NET, net=onet)
+        acts, ovis, _, _ = m.search(b)
+        a = np.maximum(vis[g], 0)[acts]
+        tv = 0.5 * np.abs(a / a.sum() - ovis / ovis.sum()).sum()
+        worst = max(worst, tv)
+        exact += int(np.array_equal(a, ovis))
+    print("wide-trunk search vs oracle: exact", exact, "of", G, "worst TV", worst)
+    assert worst <= 0.02
+    assert exact >= G // 2
+    e.close()
+    e = _engine(w, w, n, n_games=16, n_playout=40, trunk=trunk, net_impl=2, seed=4)
+    e.set_weights(arrs)
+    e.selfplay_begin(temp=1.0, recycle=False)
+    for _ in range(w * w):
+        e.selfplay_step(1)
+        if e.selfplay_stats()["n_games"] >= 16:
+            break
+    games = e.selfplay_drain_games()
+    assert len(games) == 16
+    for gid, win, mv in games:
+        b = orc.Board(w, w, n)
+        b.init_board(0)
+        for m_ in mv:
+            assert not b.game_end()[0]
+            b.do_move(m_)
+        assert b.game_end() == (True, win)
+    e.close()
+
+
 @pytest.mark.parametrize("w,n,G,P", [(8, 5, 200, 150), (6, 4, 96, 120), (5, 4, 64, 80), (9, 5, 40, 60), (11, 5, 24, 40),
                                      (15, 5, 12, 40), (13, 5, 8, 30), (7, 4, 32, 60)])
 def test_fused_wave_kernel_matches_split_kernels(w, n, G, P):
