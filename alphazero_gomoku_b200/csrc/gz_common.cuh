@@ -104,6 +104,13 @@ __host__ __device__ __forceinline__ bool bb_has_line(const BB &b, int n)
     }
     return win;
 }
+// one direction of the detector above (warp-parallel callers give each of 8 lanes a colour x direction)
+__host__ __device__ __forceinline__ bool bb_has_line_dir(const BB &b, int n, int s)
+{
+    BB t = b;
+    for (int k = 1; k < n; ++k) t = bb_and(b, bb_shr(t, s));
+    return bb_any(t);
+}
 // full-board mask for a W x H board
 __host__ __device__ __forceinline__ BB bb_board_mask(int W, int H)
 {
@@ -114,7 +121,9 @@ __host__ __device__ __forceinline__ BB bb_board_mask(int W, int H)
 }
 __host__ __device__ __forceinline__ uint32_t bb_row(const BB &a, int h)
 {
-    return (uint32_t)(a.w[h >> 2] >> ((h & 3) * 16)) & 0xFFFFu;
+    const int i = h >> 2; // select chain: a dynamic index into w[] would push the board to local memory
+    const uint64_t w = (i == 0) ? a.w[0] : (i == 1) ? a.w[1] : (i == 2) ? a.w[2] : a.w[3];
+    return (uint32_t)(w >> ((h & 3) * 16)) & 0xFFFFu;
 }
 
 // Board.get_move_target (game.py:35-58): bounding box of all stones grown by 2 with the
@@ -150,6 +159,30 @@ __host__ __device__ __forceinline__ BB bb_move_target(const BB &occ, const BB &l
     if (left > 15) return box;
     uint32_t rowmask = (uint32_t)(((1ull << (right + 1)) - 1ull) & ~((1ull << left) - 1ull)) & 0xFFFFu;
     for (int h = bottom; h <= top && h < 16; ++h) box.w[h >> 2] |= (uint64_t)rowmask << ((h & 3) * 16);
+    return bb_and(box, legal);
+}
+
+// the same box computed by a warp: lane h holds board row h (every lane returns the full result)
+__device__ __forceinline__ BB bb_move_target_warp(const BB &occ, const BB &legal, int W, int H, int lane)
+{
+    const uint32_t r = lane < H ? bb_row(occ, lane & 15) : 0u;
+    const unsigned rows = __ballot_sync(0xffffffffu, r != 0u);
+    const uint32_t cols = __reduce_or_sync(0xffffffffu, r);
+    int top = 9, bottom = 5, left = 5, right = 9; // empty board: the reference's hard-coded box (game.py:41)
+    if (rows) {
+        const int rmin = __ffs(rows) - 1, rmax = 31 - __clz(rows), cmin = __ffs(cols) - 1, cmax = 31 - __clz(cols);
+        top = (rmax <= H - 2) ? rmax + 2 : H;
+        bottom = (rmin >= 2) ? rmin - 2 : 0;
+        left = (cmin >= 2) ? cmin - 2 : 0;
+        right = (cmax <= W - 2) ? cmax + 2 : W;
+    }
+    BB box = bb_zero();
+    if (right > 15) right = 15;
+    if (left > 15) return box;
+    const uint64_t rowmask = (((1ull << (right + 1)) - 1ull) & ~((1ull << left) - 1ull)) & 0xFFFFull;
+#pragma unroll
+    for (int h = 0; h < 16; ++h)
+        if (h >= bottom && h <= top) box.w[h >> 2] |= rowmask << ((h & 3) * 16);
     return bb_and(box, legal);
 }
 

@@ -4,35 +4,76 @@
 // outputs coalesced.
 #include "gz_engine.h"
 
-__global__ void rules_eval_kernel(const int32_t *__restrict__ moves, const int64_t *__restrict__ offsets,
-                                  int64_t n_pos, const int8_t *__restrict__ start, int W, int H, int n,
-                                  int32_t *status, int8_t *ended, int8_t *winner, int8_t *haswin,
-                                  uint8_t *legal, float *planes, uint8_t *target, int8_t *cur)
+// A warp per position.  The move list is read 32 moves at a time (one coalesced load): a lane owns one
+// move, earlier occurrences of the same cell inside the chunk are found with match.any, the first
+// illegal move of the list (out of range or occupied, list.remove's ValueError in game.py:122) ends the
+// replay exactly where the reference's sequential loop would, and the stones are OR-reduced into the two
+// bitboards with redux.sync.  Per-cell outputs leave as 4-byte / 16-byte stores when S is a multiple of 4
+// (the bulk of the traffic: 18 * S bytes per position against 4 bytes per ply read).
+// The per-position scalar work is spread over the lanes too (8 lanes test one colour x direction each,
+// lane h holds board row h for the candidate box); WT > 0 makes the board side a compile-time constant
+// for the usual square sizes (cell <-> bit conversions become shifts / multiplies).
+template <int WT>
+__global__ void __launch_bounds__(128)
+rules_eval_kernel(const int32_t *__restrict__ moves, const int64_t *__restrict__ offsets,
+                  int64_t n_pos, const int8_t *__restrict__ start, int W_, int H_, int n, const BB board_mask,
+                  int32_t *status, int8_t *ended, int8_t *winner, int8_t *haswin,
+                  uint8_t *legal, float *planes, uint8_t *target, int8_t *cur)
 {
     const int lane = threadIdx.x & 31;
     const int64_t pos = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (pos >= n_pos) return;
+    const int W = WT > 0 ? WT : W_, H = WT > 0 ? WT : H_;
     const int S = W * H;
     const int64_t b0 = offsets[pos], b1 = offsets[pos + 1];
+    const int sp = start ? start[pos] : 0; // index 0 -> player 1
+    uint32_t acc[2][8]; // the two 256-bit boards as 32-bit pieces (this lane's contribution, reduced per chunk)
     BB st[2] = {bb_zero(), bb_zero()};
-    int sp = start ? start[pos] : 0;
-    int player = sp; // index 0 -> player 1
     int last = -1, ns = 0, bad = 0;
-    for (int64_t i = b0; i < b1; ++i) {
-        int mv = moves[i];
-        if (mv < 0 || mv >= S) { bad = 1; break; }
-        int bit = bb_bit(mv, W);
-        if (bb_test(st[0], bit) || bb_test(st[1], bit)) { bad = 1; break; }
-        bb_set(st[player], bit);
-        player ^= 1;
-        last = mv;
-        ++ns;
+    for (int64_t base = b0; base < b1 && !bad; base += 32) {
+        const bool have = base + lane < b1;
+        const int mv = have ? moves[base + lane] : -1;
+        const bool inr = have && mv >= 0 && mv < S;
+        const int bit = inr ? bb_bit(mv, W) : 0;
+        const bool occupied = inr && (bb_test(st[0], bit) || bb_test(st[1], bit));
+        const unsigned peers = __match_any_sync(0xffffffffu, inr ? mv : -1 - lane);
+        const bool dup = inr && (peers & ((1u << lane) - 1u)) != 0u; // an earlier move of this chunk took the cell
+        const unsigned badmask = __ballot_sync(0xffffffffu, have && (!inr || occupied || dup));
+        const unsigned havemask = __ballot_sync(0xffffffffu, have);
+        const int nvalid = badmask ? __ffs(badmask) - 1 : __popc(havemask);
+        const bool apply = lane < nvalid;
+        const int pl = (sp + ns + lane) & 1;
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+                acc[c][q] = __reduce_or_sync(0xffffffffu, (apply && pl == c && (bit >> 5) == q) ? (1u << (bit & 31)) : 0u);
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) st[c].w[q] |= (uint64_t)acc[c][2 * q] | ((uint64_t)acc[c][2 * q + 1] << 32);
+        if (nvalid > 0) last = __shfl_sync(0xffffffffu, mv, nvalid - 1);
+        ns += nvalid;
+        bad = badmask != 0u;
     }
-    int win;
-    bool hw;
-    bool end = bb_game_end(st[0], st[1], ns, W, H, n, &win, &hw);
+    const int player = (sp + ns) & 1;
+    // game_end / has_a_winner (game.py:129-169) as bb_game_end does it, one colour x direction per lane
+    bool w0 = false, w1 = false;
+    if (ns >= n + 2) {
+        const int d4 = lane & 3;
+        const int dir = (d4 == 0) ? 1 : (d4 == 1) ? 16 : (d4 == 2) ? 17 : 15;
+        bool line = false;
+        if (lane < 8) line = bb_has_line_dir(bb_pick(st[0], st[1], lane < 4), n, dir);
+        const unsigned b = __ballot_sync(0xffffffffu, line);
+        w0 = (b & 0x0Fu) != 0u;
+        w1 = (b & 0xF0u) != 0u;
+    }
+    const bool hw = w0 || w1;
+    const int win = w0 ? 1 : (w1 ? 2 : -1);
+    const bool end = hw || ns >= S;
     BB occ = bb_or(st[0], st[1]);
-    BB leg = bb_andnot(bb_board_mask(W, H), occ);
+    BB leg = bb_andnot(board_mask, occ);
+    const BB own = bb_pick(st[0], st[1], player == 0), opp = bb_pick(st[1], st[0], player == 0); // side to move / other
     if (lane == 0) {
         if (status) status[pos] = bad ? GZ_E_ILLEGAL : 0;
         if (ended) ended[pos] = end ? 1 : 0;
@@ -40,13 +81,48 @@ __global__ void rules_eval_kernel(const int32_t *__restrict__ moves, const int64
         if (haswin) haswin[pos] = hw ? 1 : 0;
         if (cur) cur[pos] = (int8_t)(player + 1);
     }
-    if (legal)
-        for (int m = lane; m < S; m += GZ_WARP) legal[pos * S + m] = bb_test(leg, bb_bit(m, W)) ? 1 : 0;
+    const bool s4 = (S & 3) == 0;
+    auto write_mask = [&](uint8_t *out, const BB &m) { // uint8[S] membership of m
+        if (s4 && (reinterpret_cast<uintptr_t>(out) & 3) == 0) {
+            uint32_t *o = reinterpret_cast<uint32_t *>(out + pos * S);
+            for (int q = lane; q < (S >> 2); q += GZ_WARP) {
+                uint32_t v = 0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) v |= (bb_test(m, bb_bit(4 * q + k, W)) ? 1u : 0u) << (8 * k);
+                o[q] = v;
+            }
+        } else {
+            for (int c = lane; c < S; c += GZ_WARP) out[pos * S + c] = bb_test(m, bb_bit(c, W)) ? 1 : 0;
+        }
+    };
+    if (legal) write_mask(legal, leg);
     if (target) {
-        BB tg = bb_move_target(occ, leg, W, H);
-        for (int m = lane; m < S; m += GZ_WARP) target[pos * S + m] = bb_test(tg, bb_bit(m, W)) ? 1 : 0;
+        const BB tg = bb_move_target_warp(occ, leg, W, H, lane);
+        write_mask(target, tg);
     }
-    if (planes) gz_write_planes(st[player], st[player ^ 1], last, ns, W, H, planes + pos * 4 * S, lane);
+    if (planes) {
+        float *out = planes + pos * 4 * S;
+        if (s4 && (reinterpret_cast<uintptr_t>(planes) & 15) == 0) {
+            // current_state (game.py:92-116), returned orientation, four cells per 16-byte store
+            const float colour = (ns % 2 == 0) ? 1.f : 0.f;
+            const int lr = last >= 0 ? last / W : -1, lc = last >= 0 ? last % H : -1;
+            const int S4 = S >> 2;
+            for (int q = lane; q < S; q += GZ_WARP) { // q = plane * S4 + group of 4 cells
+                const int plane = q / S4, idx0 = (q - plane * S4) * 4;
+                float v[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int idx = idx0 + k, rs = idx / H, c = idx % H, r = W - 1 - rs, bit = r * 16 + c;
+                    v[k] = plane == 0 ? (bb_test(own, bit) ? 1.f : 0.f)
+                         : plane == 1 ? (bb_test(opp, bit) ? 1.f : 0.f)
+                         : plane == 2 ? ((ns > 0 && r == lr && c == lc) ? 1.f : 0.f) : colour;
+                }
+                reinterpret_cast<float4 *>(out)[q] = make_float4(v[0], v[1], v[2], v[3]);
+            }
+        } else {
+            gz_write_planes(own, opp, last, ns, W, H, out, lane);
+        }
+    }
 }
 
 int gzk_rules_eval(gz_engine *e, const int32_t *d_moves, const int64_t *d_offsets, int64_t n_pos,
@@ -57,9 +133,19 @@ int gzk_rules_eval(gz_engine *e, const int32_t *d_moves, const int64_t *d_offset
     if (n_pos <= 0) return GZ_OK;
     const int wpb = 4;
     int64_t blocks = (n_pos + wpb - 1) / wpb;
-    rules_eval_kernel<<<(unsigned)blocks, wpb * 32, 0, e->stream>>>(
-        d_moves, d_offsets, n_pos, d_start, e->W, e->H, e->n_in_row, d_status, d_ended, d_winner,
-        d_haswin, d_legal, d_planes, d_target, d_cur);
+    ProfScope ps(e, PC_OTHER);
+    const BB mask = bb_board_mask(e->W, e->H);
+#define GZ_RULES(WT) rules_eval_kernel<WT><<<(unsigned)blocks, wpb * 32, 0, e->stream>>>( \
+        d_moves, d_offsets, n_pos, d_start, e->W, e->H, e->n_in_row, mask, d_status, d_ended, d_winner, \
+        d_haswin, d_legal, d_planes, d_target, d_cur)
+    const int side = e->W == e->H ? e->W : 0;
+    if (side == 6) GZ_RULES(6);
+    else if (side == 8) GZ_RULES(8);
+    else if (side == 9) GZ_RULES(9);
+    else if (side == 11) GZ_RULES(11);
+    else if (side == 15) GZ_RULES(15);
+    else GZ_RULES(0);
+#undef GZ_RULES
     e->launches++;
     GZ_CUDA(e, cudaGetLastError());
     return GZ_OK;

@@ -59,12 +59,6 @@ __device__ __forceinline__ int warp_argmax_redux(double s, int i)
 }
 
 // n-in-a-row test of one colour in one direction (shift 1 / 16 / 17 / 15), see bb_has_line
-__device__ __forceinline__ bool bb_has_line_dir(const BB &b, int n, int s)
-{
-    BB t = b;
-    for (int k = 1; k < n; ++k) t = bb_and(b, bb_shr(t, s));
-    return bb_any(t);
-}
 
 // per-block statistics without a trailing barrier: warps add into shared counters and the last
 // warp to finish flushes them to the device counters
