@@ -25,6 +25,7 @@ rules_eval_kernel(const int32_t *__restrict__ moves, const int64_t *__restrict__
     if (pos >= n_pos) return;
     const int W = WT > 0 ? WT : W_, H = WT > 0 ? WT : H_;
     const int S = W * H;
+    constexpr int NPIECE = WT > 0 ? ((WT - 1) * 16 + WT + 31) / 32 : 8; // 32-bit pieces of a bitboard that hold cells
     const int64_t b0 = offsets[pos], b1 = offsets[pos + 1];
     const int sp = start ? start[pos] : 0; // index 0 -> player 1
     uint32_t acc[2][8]; // the two 256-bit boards as 32-bit pieces (this lane's contribution, reduced per chunk)
@@ -46,8 +47,8 @@ rules_eval_kernel(const int32_t *__restrict__ moves, const int64_t *__restrict__
 #pragma unroll
         for (int c = 0; c < 2; ++c)
 #pragma unroll
-            for (int q = 0; q < 8; ++q)
-                acc[c][q] = __reduce_or_sync(0xffffffffu, (apply && pl == c && (bit >> 5) == q) ? (1u << (bit & 31)) : 0u);
+            for (int q = 0; q < 8; ++q) // pieces above the board's last row stay empty
+                acc[c][q] = q < NPIECE ? __reduce_or_sync(0xffffffffu, (apply && pl == c && (bit >> 5) == q) ? (1u << (bit & 31)) : 0u) : 0u;
 #pragma unroll
         for (int c = 0; c < 2; ++c)
 #pragma unroll
@@ -87,8 +88,14 @@ rules_eval_kernel(const int32_t *__restrict__ moves, const int64_t *__restrict__
             uint32_t *o = reinterpret_cast<uint32_t *>(out + pos * S);
             for (int q = lane; q < (S >> 2); q += GZ_WARP) {
                 uint32_t v = 0;
+                if ((W & 3) == 0) { // the four cells sit in one board row: a nibble of that row
+                    const int c4 = 4 * q, row = c4 / W, col = c4 - row * W;
+                    const uint32_t nb = (bb_row(m, row) >> col) & 0xFu;
+                    v = (nb & 1u) | ((nb & 2u) << 7) | ((nb & 4u) << 14) | ((nb & 8u) << 21);
+                } else {
 #pragma unroll
-                for (int k = 0; k < 4; ++k) v |= (bb_test(m, bb_bit(4 * q + k, W)) ? 1u : 0u) << (8 * k);
+                    for (int k = 0; k < 4; ++k) v |= (bb_test(m, bb_bit(4 * q + k, W)) ? 1u : 0u) << (8 * k);
+                }
                 o[q] = v;
             }
         } else {
@@ -110,12 +117,22 @@ rules_eval_kernel(const int32_t *__restrict__ moves, const int64_t *__restrict__
             for (int q = lane; q < S; q += GZ_WARP) { // q = plane * S4 + group of 4 cells
                 const int plane = q / S4, idx0 = (q - plane * S4) * 4;
                 float v[4];
+                if ((H & 3) == 0) { // one board row per group of four: a nibble per plane
+                    const int rs = idx0 / H, c = idx0 - rs * H, r = W - 1 - rs;
+                    uint32_t nb;
+                    if (plane < 2) nb = (bb_row(bb_pick(own, opp, plane == 0), r) >> c) & 0xFu;
+                    else if (plane == 2) nb = (ns > 0 && r == lr && lc >= c && lc < c + 4) ? (1u << (lc - c)) : 0u;
+                    else nb = (ns % 2 == 0) ? 0xFu : 0u;
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const int idx = idx0 + k, rs = idx / H, c = idx % H, r = W - 1 - rs, bit = r * 16 + c;
-                    v[k] = plane == 0 ? (bb_test(own, bit) ? 1.f : 0.f)
-                         : plane == 1 ? (bb_test(opp, bit) ? 1.f : 0.f)
-                         : plane == 2 ? ((ns > 0 && r == lr && c == lc) ? 1.f : 0.f) : colour;
+                    for (int k = 0; k < 4; ++k) v[k] = ((nb >> k) & 1u) ? 1.f : 0.f;
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int idx = idx0 + k, rs = idx / H, c = idx % H, r = W - 1 - rs, bit = r * 16 + c;
+                        v[k] = plane == 0 ? (bb_test(own, bit) ? 1.f : 0.f)
+                             : plane == 1 ? (bb_test(opp, bit) ? 1.f : 0.f)
+                             : plane == 2 ? ((ns > 0 && r == lr && c == lc) ? 1.f : 0.f) : colour;
+                    }
                 }
                 reinterpret_cast<float4 *>(out)[q] = make_float4(v[0], v[1], v[2], v[3]);
             }
