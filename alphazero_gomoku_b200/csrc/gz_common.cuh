@@ -163,11 +163,13 @@ __host__ __device__ __forceinline__ BB bb_move_target(const BB &occ, const BB &l
 }
 
 // the same box computed by a warp: lane h holds board row h (every lane returns the full result)
-__device__ __forceinline__ BB bb_move_target_warp(const BB &occ, const BB &legal, int W, int H, int lane)
+// (seg = member mask of the 32- or 16-lane segment working on this board, sh = its first lane)
+__device__ __forceinline__ BB bb_move_target_warp(const BB &occ, const BB &legal, int W, int H, int lane,
+                                                  unsigned seg = 0xffffffffu, int sh = 0)
 {
     const uint32_t r = lane < H ? bb_row(occ, lane & 15) : 0u;
-    const unsigned rows = __ballot_sync(0xffffffffu, r != 0u);
-    const uint32_t cols = __reduce_or_sync(0xffffffffu, r);
+    const unsigned rows = (__ballot_sync(seg, r != 0u) & seg) >> sh;
+    const uint32_t cols = __reduce_or_sync(seg, r);
     int top = 9, bottom = 5, left = 5, right = 9; // empty board: the reference's hard-coded box (game.py:41)
     if (rows) {
         const int rmin = __ffs(rows) - 1, rmax = 31 - __clz(rows), cmin = __ffs(cols) - 1, cmax = 31 - __clz(cols);
@@ -280,13 +282,14 @@ __host__ __device__ __forceinline__ bool bb_game_end(const BB &s0, const BB &s1,
 
 // current_state planes (game.py:92-116) in the RETURNED orientation [4][W][H] (row reversed).
 __device__ __forceinline__ void gz_write_planes(const BB &own, const BB &opp, int last_move,
-                                                int n_stones, int W, int H, float *out, int lane)
+                                                int n_stones, int W, int H, float *out, int lane,
+                                                int stride = GZ_WARP)
 {
     const int S = W * H;
     const float colour = (n_stones % 2 == 0) ? 1.f : 0.f;
     const int lr = last_move >= 0 ? last_move / W : -1;
     const int lc = last_move >= 0 ? last_move % H : -1;
-    for (int idx = lane; idx < S; idx += GZ_WARP) {
+    for (int idx = lane; idx < S; idx += stride) {
         int rs = idx / H, c = idx % H;
         int r = W - 1 - rs;
         int bit = r * 16 + c;

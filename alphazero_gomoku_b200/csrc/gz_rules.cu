@@ -1,6 +1,6 @@
 // gz_rules.cu — Board rules on bitboards (reference game.py:11-172).
 //   K3: do_move, has_a_winner / game_end, legal mask, current_state planes, move_target.
-// One warp per position/game: lanes share the (tiny) bitboard work and write the per-cell
+// A warp (or half a warp) per position/game: lanes share the (tiny) bitboard work and write the per-cell
 // outputs coalesced.
 #include "gz_engine.h"
 
@@ -13,15 +13,20 @@
 // The per-position scalar work is spread over the lanes too (8 lanes test one colour x direction each,
 // lane h holds board row h for the candidate box); WT > 0 makes the board side a compile-time constant
 // for the usual square sizes (cell <-> bit conversions become shifts / multiplies).
-template <int WT>
+// LP = lanes per position: 16 puts two positions in a warp (every warp-wide primitive runs on the half-warp's
+// mask), which halves the issued instructions per position - the kernel is issue-bound, not HBM-bound.
+template <int WT, int LP>
 __global__ void __launch_bounds__(128)
 rules_eval_kernel(const int32_t *__restrict__ moves, const int64_t *__restrict__ offsets,
                   int64_t n_pos, const int8_t *__restrict__ start, int W_, int H_, int n, const BB board_mask,
                   int32_t *status, int8_t *ended, int8_t *winner, int8_t *haswin,
                   uint8_t *legal, float *planes, uint8_t *target, int8_t *cur)
 {
-    const int lane = threadIdx.x & 31;
-    const int64_t pos = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    static_assert(LP == 32 || LP == 16, "a position takes a warp or half a warp");
+    const int lane = threadIdx.x & (LP - 1);                     // lane inside the position's segment
+    const int sh = (threadIdx.x & 31) & ~(LP - 1);               // first warp lane of the segment
+    const unsigned seg = LP == 32 ? 0xffffffffu : (0xffffu << sh); // the segment's member mask
+    const int64_t pos = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / LP;
     if (pos >= n_pos) return;
     const int W = WT > 0 ? WT : W_, H = WT > 0 ? WT : H_;
     const int S = W * H;
@@ -31,16 +36,16 @@ rules_eval_kernel(const int32_t *__restrict__ moves, const int64_t *__restrict__
     uint32_t acc[2][8]; // the two 256-bit boards as 32-bit pieces (this lane's contribution, reduced per chunk)
     BB st[2] = {bb_zero(), bb_zero()};
     int last = -1, ns = 0, bad = 0;
-    for (int64_t base = b0; base < b1 && !bad; base += 32) {
+    for (int64_t base = b0; base < b1 && !bad; base += LP) {
         const bool have = base + lane < b1;
         const int mv = have ? moves[base + lane] : -1;
         const bool inr = have && mv >= 0 && mv < S;
         const int bit = inr ? bb_bit(mv, W) : 0;
         const bool occupied = inr && (bb_test(st[0], bit) || bb_test(st[1], bit));
-        const unsigned peers = __match_any_sync(0xffffffffu, inr ? mv : -1 - lane);
+        const unsigned peers = __match_any_sync(seg, inr ? mv : -1 - lane) >> sh;
         const bool dup = inr && (peers & ((1u << lane) - 1u)) != 0u; // an earlier move of this chunk took the cell
-        const unsigned badmask = __ballot_sync(0xffffffffu, have && (!inr || occupied || dup));
-        const unsigned havemask = __ballot_sync(0xffffffffu, have);
+        const unsigned badmask = (__ballot_sync(seg, have && (!inr || occupied || dup)) & seg) >> sh;
+        const unsigned havemask = (__ballot_sync(seg, have) & seg) >> sh;
         const int nvalid = badmask ? __ffs(badmask) - 1 : __popc(havemask);
         const bool apply = lane < nvalid;
         const int pl = (sp + ns + lane) & 1;
@@ -48,12 +53,12 @@ rules_eval_kernel(const int32_t *__restrict__ moves, const int64_t *__restrict__
         for (int c = 0; c < 2; ++c)
 #pragma unroll
             for (int q = 0; q < 8; ++q) // pieces above the board's last row stay empty
-                acc[c][q] = q < NPIECE ? __reduce_or_sync(0xffffffffu, (apply && pl == c && (bit >> 5) == q) ? (1u << (bit & 31)) : 0u) : 0u;
+                acc[c][q] = q < NPIECE ? __reduce_or_sync(seg, (apply && pl == c && (bit >> 5) == q) ? (1u << (bit & 31)) : 0u) : 0u;
 #pragma unroll
         for (int c = 0; c < 2; ++c)
 #pragma unroll
             for (int q = 0; q < 4; ++q) st[c].w[q] |= (uint64_t)acc[c][2 * q] | ((uint64_t)acc[c][2 * q + 1] << 32);
-        if (nvalid > 0) last = __shfl_sync(0xffffffffu, mv, nvalid - 1);
+        if (nvalid > 0) last = __shfl_sync(seg, mv, nvalid - 1, LP);
         ns += nvalid;
         bad = badmask != 0u;
     }
@@ -65,7 +70,7 @@ rules_eval_kernel(const int32_t *__restrict__ moves, const int64_t *__restrict__
         const int dir = (d4 == 0) ? 1 : (d4 == 1) ? 16 : (d4 == 2) ? 17 : 15;
         bool line = false;
         if (lane < 8) line = bb_has_line_dir(bb_pick(st[0], st[1], lane < 4), n, dir);
-        const unsigned b = __ballot_sync(0xffffffffu, line);
+        const unsigned b = (__ballot_sync(seg, line) & seg) >> sh;
         w0 = (b & 0x0Fu) != 0u;
         w1 = (b & 0xF0u) != 0u;
     }
@@ -86,7 +91,7 @@ rules_eval_kernel(const int32_t *__restrict__ moves, const int64_t *__restrict__
     auto write_mask = [&](uint8_t *out, const BB &m) { // uint8[S] membership of m
         if (s4 && (reinterpret_cast<uintptr_t>(out) & 3) == 0) {
             uint32_t *o = reinterpret_cast<uint32_t *>(out + pos * S);
-            for (int q = lane; q < (S >> 2); q += GZ_WARP) {
+            for (int q = lane; q < (S >> 2); q += LP) {
                 uint32_t v = 0;
                 if ((W & 3) == 0) { // the four cells sit in one board row: a nibble of that row
                     const int c4 = 4 * q, row = c4 / W, col = c4 - row * W;
@@ -99,12 +104,12 @@ rules_eval_kernel(const int32_t *__restrict__ moves, const int64_t *__restrict__
                 o[q] = v;
             }
         } else {
-            for (int c = lane; c < S; c += GZ_WARP) out[pos * S + c] = bb_test(m, bb_bit(c, W)) ? 1 : 0;
+            for (int c = lane; c < S; c += LP) out[pos * S + c] = bb_test(m, bb_bit(c, W)) ? 1 : 0;
         }
     };
     if (legal) write_mask(legal, leg);
     if (target) {
-        const BB tg = bb_move_target_warp(occ, leg, W, H, lane);
+        const BB tg = bb_move_target_warp(occ, leg, W, H, lane, seg, sh);
         write_mask(target, tg);
     }
     if (planes) {
@@ -114,7 +119,7 @@ rules_eval_kernel(const int32_t *__restrict__ moves, const int64_t *__restrict__
             const float colour = (ns % 2 == 0) ? 1.f : 0.f;
             const int lr = last >= 0 ? last / W : -1, lc = last >= 0 ? last % H : -1;
             const int S4 = S >> 2;
-            for (int q = lane; q < S; q += GZ_WARP) { // q = plane * S4 + group of 4 cells
+            for (int q = lane; q < S; q += LP) { // q = plane * S4 + group of 4 cells
                 const int plane = q / S4, idx0 = (q - plane * S4) * 4;
                 float v[4];
                 if ((H & 3) == 0) { // one board row per group of four: a nibble per plane
@@ -137,7 +142,7 @@ rules_eval_kernel(const int32_t *__restrict__ moves, const int64_t *__restrict__
                 reinterpret_cast<float4 *>(out)[q] = make_float4(v[0], v[1], v[2], v[3]);
             }
         } else {
-            gz_write_planes(own, opp, last, ns, W, H, out, lane);
+            gz_write_planes(own, opp, last, ns, W, H, out, lane, LP);
         }
     }
 }
@@ -148,11 +153,14 @@ int gzk_rules_eval(gz_engine *e, const int32_t *d_moves, const int64_t *d_offset
                    int8_t *d_cur)
 {
     if (n_pos <= 0) return GZ_OK;
-    const int wpb = 4;
+    // half a warp per position where the per-cell outputs leave as packed stores (S a multiple of 4: measured
+    // 2.19 vs 1.79 TB/s at 8x8), a whole warp otherwise (1.92 vs 1.73 TB/s at 15x15)
+    const bool half = (e->S & 3) == 0;
+    const int wpb = half ? 8 : 4; // positions per 128-thread block
     int64_t blocks = (n_pos + wpb - 1) / wpb;
     ProfScope ps(e, PC_OTHER);
     const BB mask = bb_board_mask(e->W, e->H);
-#define GZ_RULES(WT) rules_eval_kernel<WT><<<(unsigned)blocks, wpb * 32, 0, e->stream>>>( \
+#define GZ_RULES(WT) (half ? rules_eval_kernel<WT, 16> : rules_eval_kernel<WT, 32>)<<<(unsigned)blocks, 128, 0, e->stream>>>( \
         d_moves, d_offsets, n_pos, d_start, e->W, e->H, e->n_in_row, mask, d_status, d_ended, d_winner, \
         d_haswin, d_legal, d_planes, d_target, d_cur)
     const int side = e->W == e->H ? e->W : 0;
