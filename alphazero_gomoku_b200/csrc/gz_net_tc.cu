@@ -695,6 +695,10 @@ heads_tc_kernel(const uint8_t *__restrict__ head_act, FcTc w, float *__restrict_
     float *s_bp = reinterpret_cast<float *>(smem + OFF_BIAS), *s_bv = s_bp + 256, *s_wv2 = s_bv + 64, *s_bv2 = s_wv2 + 64;
     const int S = w.S, Np = w.Np, nst = w.stages_p + w.stages_v;
     const uint32_t wslot = 128u * (uint32_t)(Np > 64 ? Np : 64), slot_bytes = A_STAGE + wslot;
+    // gridDim.y == 2: the policy head and the value head of a tile run as two CTAs (blockIdx.y = 0 / 1), which
+    // shortens the serial stage pipeline of a tile from stages_p + stages_v to max(stages_p, stages_v)
+    const bool do_pol = gridDim.y == 1 || blockIdx.y == 0, do_val = gridDim.y == 1 || blockIdx.y == 1;
+    const int s_begin = do_pol ? 0 : w.stages_p, s_end = do_val ? nst : w.stages_p;
 
     for (int i = tid; i < 256; i += THREADS) s_bp[i] = i < S ? w.bp[i] : 0.f;
     if (tid < 64) { s_bv[tid] = w.bv[tid]; s_wv2[tid] = w.wv2[tid]; }
@@ -721,8 +725,8 @@ heads_tc_kernel(const uint8_t *__restrict__ head_act, FcTc w, float *__restrict_
     if (warp == 5) {
         if (lane == 0) {
             const uint8_t *asrc = head_act + (size_t)T * nst * A_STAGE;
-            for (int s = 0; s < nst; ++s) {
-                const uint32_t slot = (uint32_t)s % (uint32_t)w.ns, ph = ((uint32_t)s / (uint32_t)w.ns) & 1u;
+            for (int s = s_begin; s < s_end; ++s) {
+                const uint32_t i = (uint32_t)(s - s_begin), slot = i % (uint32_t)w.ns, ph = (i / (uint32_t)w.ns) & 1u;
                 tc_mbar_wait(bar_empty + 8 * slot, ph ^ 1u);
                 const bool pol = s < w.stages_p;
                 const uint32_t wb = pol ? 128u * (uint32_t)Np : 8192u;
@@ -735,8 +739,8 @@ heads_tc_kernel(const uint8_t *__restrict__ head_act, FcTc w, float *__restrict_
         }
     } else if (warp == 4) {
         const uint32_t leader = tc_elect();
-        for (int s = 0; s < nst; ++s) {
-            const uint32_t slot = (uint32_t)s % (uint32_t)w.ns, ph = ((uint32_t)s / (uint32_t)w.ns) & 1u;
+        for (int s = s_begin; s < s_end; ++s) {
+            const uint32_t i = (uint32_t)(s - s_begin), slot = i % (uint32_t)w.ns, ph = (i / (uint32_t)w.ns) & 1u;
             tc_mbar_wait(bar_full + 8 * slot, ph);
             tc_fence_after();
             const bool pol = s < w.stages_p;
@@ -765,7 +769,8 @@ heads_tc_kernel(const uint8_t *__restrict__ head_act, FcTc w, float *__restrict_
         const int nchunk = (S + 31) >> 5;
         float *prow = probs + board * S;
         const bool vec = (S & 3) == 0 && (reinterpret_cast<uintptr_t>(probs) & 15) == 0;
-        if (S <= 64) {
+        if (!do_pol) {
+        } else if (S <= 64) {
             // the whole row of logits fits in registers: one pass over TMEM
             float x[64];
 #pragma unroll
@@ -798,55 +803,67 @@ heads_tc_kernel(const uint8_t *__restrict__ head_act, FcTc w, float *__restrict_
                 }
             }
         } else {
-            float mx = -3.0e38f;
+            // boards of more than 64 cells: the logits go to shared memory (the weight ring is idle by now),
+            // row stride Np + 1 floats (odd: a thread per row writes conflict-free); the softmax itself is done
+            // after the block barrier below by ALL warps, a warp per row, with coalesced reads and writes -
+            // a thread per row would serialise 3 * S dependent exp / max steps on four warps
+            float *sl = reinterpret_cast<float *>(smem + OFF_RING) + (size_t)tid * (Np + 1);
             for (int ch = 0; ch < nchunk; ++ch) {
                 uint32_t v[32];
                 tc_tmem_ld32(tmem + t_lane + TM_P + ch * 32, v);
 #pragma unroll
                 for (int c = 0; c < 32; ++c)
-                    if (ch * 32 + c < S) mx = fmaxf(mx, fmaf(__uint_as_float(v[c]), w.inv_p, s_bp[ch * 32 + c]));
+                    if (ch * 32 + c < S) sl[ch * 32 + c] = fmaf(__uint_as_float(v[c]), w.inv_p, s_bp[ch * 32 + c]);
             }
-            float sum = 0.f;
-            for (int ch = 0; ch < nchunk; ++ch) {
+        }
+        if (do_val) {
+            float acc2 = s_bv2[0];
+#pragma unroll
+            for (int ch = 0; ch < 2; ++ch) {
                 uint32_t v[32];
-                tc_tmem_ld32(tmem + t_lane + TM_P + ch * 32, v);
+                tc_tmem_ld32(tmem + t_lane + TM_V + ch * 32, v);
 #pragma unroll
                 for (int c = 0; c < 32; ++c)
-                    if (ch * 32 + c < S) sum += __expf(fmaf(__uint_as_float(v[c]), w.inv_p, s_bp[ch * 32 + c]) - mx);
+                    acc2 = fmaf(fmaxf(fmaf(__uint_as_float(v[c]), w.inv_v, s_bv[ch * 32 + c]), 0.f), s_wv2[ch * 32 + c], acc2);
             }
-            const float inv = 1.f / sum;
-            for (int ch = 0; ch < nchunk; ++ch) {
-                uint32_t v[32];
-                tc_tmem_ld32(tmem + t_lane + TM_P + ch * 32, v);
-                float p[32];
-#pragma unroll
-                for (int c = 0; c < 32; ++c) p[c] = __expf(fmaf(__uint_as_float(v[c]), w.inv_p, s_bp[ch * 32 + c]) - mx) * inv;
-                if (valid) {
-                    if (vec) {
-#pragma unroll
-                        for (int c = 0; c < 32; c += 4)
-                            if (ch * 32 + c < S) *reinterpret_cast<float4 *>(prow + ch * 32 + c) = make_float4(p[c], p[c + 1], p[c + 2], p[c + 3]);
-                    } else {
-#pragma unroll
-                        for (int c = 0; c < 32; ++c)
-                            if (ch * 32 + c < S) prow[ch * 32 + c] = p[c];
-                    }
-                }
-            }
+            if (valid) values[board] = tanhf(acc2);
         }
-        float acc2 = s_bv2[0];
-#pragma unroll
-        for (int ch = 0; ch < 2; ++ch) {
-            uint32_t v[32];
-            tc_tmem_ld32(tmem + t_lane + TM_V + ch * 32, v);
-#pragma unroll
-            for (int c = 0; c < 32; ++c)
-                acc2 = fmaf(fmaxf(fmaf(__uint_as_float(v[c]), w.inv_v, s_bv[ch * 32 + c]), 0.f), s_wv2[ch * 32 + c], acc2);
-        }
-        if (valid) values[board] = tanhf(acc2);
         tc_fence_before();
     }
     __syncthreads();
+    if (do_pol && S > 64) { // softmax of the staged logits: a warp per board row
+        const float *slb = reinterpret_cast<const float *>(smem + OFF_RING);
+        for (int r = warp; r < 128; r += THREADS / 32) {
+            const long long board = T * 128 + r;
+            if (board >= B) break;
+            const float *row = slb + (size_t)r * (Np + 1);
+            float x[8]; // S <= 225 < 256 = 8 values per lane
+            float mx = -3.0e38f;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int c = lane + 32 * k;
+                x[k] = c < S ? row[c] : -3.0e38f;
+                mx = fmaxf(mx, x[k]);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            float sum = 0.f;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                x[k] = __expf(x[k] - mx); // padding: exp(-huge) = 0
+                sum += x[k];
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            const float inv = 1.f / sum;
+            float *prow = probs + board * S;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int c = lane + 32 * k;
+                if (c < S) prow[c] = x[k] * inv;
+            }
+        }
+    }
     if (warp == 0) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
@@ -1109,7 +1126,10 @@ static int gz_tc_launch_heads(gz_engine *e, const TcGeom &g, float *d_probs, flo
             GZ_CUDA(e, cudaFuncSetAttribute(heads_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
             e->attr_done |= 2u;
         }
-        heads_tc_kernel<<<(unsigned)((maxB + 127) / 128), fct::THREADS, fct::OFF_RING + (size_t)fw.ns * slot_bytes, e->stream>>>(
+        // two CTAs per tile (policy | value) while that still fits the machine in one wave
+        const unsigned tiles = (unsigned)((maxB + 127) / 128);
+        const dim3 hgrid(tiles, 2 * tiles <= (unsigned)(e->n_sm > 0 ? e->n_sm : 148) ? 2 : 1);
+        heads_tc_kernel<<<hgrid, fct::THREADS, fct::OFF_RING + (size_t)fw.ns * slot_bytes, e->stream>>>(
             reinterpret_cast<const uint8_t *>(e->tc_head), fw, d_probs, d_values, d_count, maxB);
     }
     return GZ_OK;
