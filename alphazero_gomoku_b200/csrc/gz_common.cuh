@@ -300,3 +300,29 @@ __device__ __forceinline__ void gz_write_planes(const BB &own, const BB &opp, in
     }
 }
 
+// ---- programmatic dependent launch (the per-wave kernel chain trunk -> heads -> tree -> trunk) ----------
+// A kernel of the chain calls gz_pdl_wait() before it touches anything its predecessor produces or still reads
+// (everything before the wait is private set-up, or reads of state only kernels TWO steps back write) and
+// gz_pdl_trigger() right AFTER its own wait: its successor may then be scheduled as SMs free up, so launch
+// latency, block scheduling and the successor's set-up overlap this kernel's body.  Triggering only after the
+// wait keeps the chain transitive (when my successor starts, my predecessor is complete); triggering first
+// thing let a small tree kernel start while the tree kernel two steps back was still running.
+// Without the launch attribute both are no-ops.
+__device__ __forceinline__ void gz_pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void gz_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+static cudaError_t gz_launch_chain(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                   Args &&...args)
+{
+    static const bool no_pdl = getenv("GZ_NO_PDL") != nullptr; // A/B switch
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = no_pdl ? 0 : 1;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+

@@ -256,8 +256,6 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0); // warp-uniform for the compiler
-    const long long B = __shfl_sync(0xffffffffu, count ? (long long)*count : maxB, 0);
-    const long long n_groups = (B + g.NB - 1) / g.NB;
     const uint32_t sbase = tc_smem_u32(smem);
     const uint32_t bar_full = sbase + OFF_BAR, bar_empty = sbase + OFF_BAR + 32, bar_mma = sbase + OFF_BAR + 64;
     const uint32_t bar_mma3 = sbase + OFF_BAR + 104, bar_c3free = sbase + OFF_BAR + 112, bar_c2back = sbase + OFF_BAR + 120;
@@ -289,6 +287,12 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    // the set-up above touched only this CTA's shared memory, TMEM and the weight image; the leaf count and the
+    // planes come from the tree kernel before this one
+    gz_pdl_wait();
+    gz_pdl_trigger();
+    const long long B = __shfl_sync(0xffffffffu, count ? (long long)*count : maxB, 0);
+    const long long n_groups = (B + g.NB - 1) / g.NB;
     if (timeline && tid == 0) { // per-CTA wall time (ns) after setup; [512 + 2 * cta] = start, + 1 = end
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -686,6 +690,8 @@ heads_tc_kernel(const uint8_t *__restrict__ head_act, FcTc w, float *__restrict_
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    gz_pdl_wait(); // the leaf count and the head activations come from the trunk kernel before this one
+    gz_pdl_trigger();
     const long long B = __shfl_sync(0xffffffffu, count ? (long long)*count : maxB, 0);
     const long long T = blockIdx.x;
     if (T * 128 >= B) return;
@@ -1068,9 +1074,9 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
         TcConsts cst;
         memcpy(&cst, w.tc_consts.data(), sizeof(TcConsts));
         auto kern = dense ? trunk_tc_kernel<true> : trunk_tc_kernel<false>;
-        kern<<<grid, THREADS, smem_bytes, e->stream>>>(d_planes, w.tc_img, cst, w.tc_inv[0], w.tc_inv[1], w.tc_inv[2],
-                                                       reinterpret_cast<__half *>(e->tc_head), d_count, maxB, g,
-                                                       want_dbg ? e->tc_dbg : nullptr, d_tl);
+        GZ_CUDA(e, gz_launch_chain(kern, dim3(grid), dim3(THREADS), (size_t)smem_bytes, e->stream, d_planes, w.tc_img, cst,
+                                   w.tc_inv[0], w.tc_inv[1], w.tc_inv[2], reinterpret_cast<__half *>(e->tc_head), d_count,
+                                   (long long)maxB, g, want_dbg ? e->tc_dbg : nullptr, d_tl));
     }
     if (d_tl) {
         std::vector<long long> h(2048);
@@ -1129,8 +1135,9 @@ static int gz_tc_launch_heads(gz_engine *e, const TcGeom &g, float *d_probs, flo
         // two CTAs per tile (policy | value) while that still fits the machine in one wave
         const unsigned tiles = (unsigned)((maxB + 127) / 128);
         const dim3 hgrid(tiles, 2 * tiles <= (unsigned)(e->n_sm > 0 ? e->n_sm : 148) ? 2 : 1);
-        heads_tc_kernel<<<hgrid, fct::THREADS, fct::OFF_RING + (size_t)fw.ns * slot_bytes, e->stream>>>(
-            reinterpret_cast<const uint8_t *>(e->tc_head), fw, d_probs, d_values, d_count, maxB);
+        GZ_CUDA(e, gz_launch_chain(heads_tc_kernel, hgrid, dim3(fct::THREADS), fct::OFF_RING + (size_t)fw.ns * slot_bytes,
+                                   e->stream, reinterpret_cast<const uint8_t *>(e->tc_head), fw, d_probs, d_values, d_count,
+                                   (long long)maxB));
     }
     return GZ_OK;
 }

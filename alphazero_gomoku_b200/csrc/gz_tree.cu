@@ -348,6 +348,12 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
     const bool do_exp = st == 0, do_bk = st != 2;
     float vnet = 0.f, prr[NSL];
     int newn = -1;
+    // Everything above reads state only tree kernels write; the evaluator's outputs below come from the net
+    // kernels before this one in the chain, and from here on this kernel writes what they read (leaf planes,
+    // leaf counter): programmatic-dependent-launch boundary.
+    gz_pdl_wait();
+    gz_pdl_trigger();
+    if (g == 0 && lane == 0 && p.leaf_zero) *p.leaf_zero = 0; // the counter the net just consumed (gzk_expand_select)
     if (do_exp) {
         vnet = values[slot];
 #pragma unroll
@@ -547,10 +553,10 @@ expand_select_small_kernel(TreeParams p, const float *__restrict__ priors, const
     const int g = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     __shared__ SelStats ss;
     if (threadIdx.x == 0) { ss.levels = 0; ss.children = 0; ss.playouts = 0; ss.done = 0; }
-    if (blockIdx.x == 0 && threadIdx.x == 0 && p.leaf_zero) *p.leaf_zero = 0; // see gzk_expand_select
     __syncthreads();
     unsigned lv = 0, ch = 0, pl = 0;
     if (g < p.G) gz_expand_select_game<NSL, WT>(p, g, lane, priors, values, lv, ch, pl);
+    else { gz_pdl_wait(); gz_pdl_trigger(); }
     gz_stats_finish(&ss, p.ctr, lane, lv, ch, pl);
 }
 
@@ -724,7 +730,7 @@ int gzk_expand_select(gz_engine *e, const float *d_priors, const float *d_values
     const bool sq = e->W == e->H;
     // round-trip-minimal kernel: NSL = Sp / 32 child slots per lane, board side compile-time for the
     // reference's usual sizes; other sizes take the generic fused kernel
-#define GZ_ES(NSL, WT) expand_select_small_kernel<NSL, WT><<<grid, 128, 0, e->stream>>>(tp, d_priors, d_values)
+#define GZ_ES(NSL, WT) GZ_CUDA(e, gz_launch_chain(expand_select_small_kernel<NSL, WT>, dim3(grid), dim3(128), 0, e->stream, tp, d_priors, d_values))
     if (e->Sp == 64 && sq && e->W == 8) GZ_ES(2, 8);
     else if (e->Sp == 64 && sq && e->W == 6) GZ_ES(2, 6);
     else if (e->Sp == 64) GZ_ES(2, 0);
