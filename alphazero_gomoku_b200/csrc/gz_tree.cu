@@ -545,8 +545,11 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
     playouts_out = 1u;
 }
 
+#ifndef GZ_ES_MINB
+#define GZ_ES_MINB 8
+#endif
 template <int NSL, int WT>
-__global__ void __launch_bounds__(128, NSL <= 2 ? 8 : (NSL <= 4 ? 5 : 3))
+__global__ void __launch_bounds__(128, NSL <= 2 ? GZ_ES_MINB : (NSL <= 4 ? 5 : 3))
 expand_select_small_kernel(TreeParams p, const float *__restrict__ priors, const float *__restrict__ values)
 {
     const int lane = threadIdx.x & 31;
