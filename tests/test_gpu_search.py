@@ -533,3 +533,51 @@ def test_degenerate_batches_do_not_disturb_other_games():
     vis, rn = e.root_visits()
     assert (vis == -1).all() and (rn == 7).all()
     e.close()
+
+
+_PDL_SCRIPT = r"""
+import sys
+sys.path.insert(0, {root!r}); sys.path.insert(0, {tests!r})
+import numpy as np
+from helpers import load_golden_weights
+from alphazero_gomoku_b200 import Engine
+out = {{}}
+for name, w, n in (("6_6_4", 6, 4), ("8_8_5", 8, 5)):
+    wts = load_golden_weights("weights_" + name)
+    for G in (1, 3, 64, 700):
+        e = Engine(width=w, height=w, n_in_row=n, n_games=G, n_playout=150, seed=5)
+        e.set_weights(wts)
+        rng = np.random.RandomState(G)
+        for g in range(G):
+            e.boards_set(g, [int(x) for x in rng.permutation(w * w)[:int(rng.randint(0, 5))]])
+        for rep in range(2):  # the second search reuses the tree after a move in every game
+            e.search(150)
+            vis, rn = e.root_visits()
+            out["%s_%d_%d" % (name, G, rep)] = vis
+            e.update_with_move(vis.argmax(axis=1).astype(np.int32))
+        e.close()
+np.savez(sys.argv[1], **out)
+"""
+
+
+def test_dependent_launch_chain_matches_serial_launches(tmp_path):
+    """The wave chain launched with programmatic dependent launch (kernels start before their
+    predecessor has drained) must build the same trees as plain stream-ordered launches
+    (GZ_NO_PDL=1): identical visit counts, small grids included - those are the ones where a
+    successor can become resident early."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = tmp_path / "pdl_case.py"
+    script.write_text(_PDL_SCRIPT.format(root=root, tests=os.path.join(root, "tests")))
+    res = {}
+    for tag, extra in (("pdl", {}), ("serial", {"GZ_NO_PDL": "1"})):
+        env = {k: v for k, v in os.environ.items() if k != "GZ_NO_PDL"}
+        env.update(extra)
+        out = tmp_path / (tag + ".npz")
+        subprocess.check_call([sys.executable, str(script), str(out)], env=env, timeout=600)
+        res[tag] = np.load(out)
+    assert sorted(res["pdl"].files) == sorted(res["serial"].files) and len(res["pdl"].files) == 16
+    for k in res["pdl"].files:
+        assert res["pdl"][k].sum() > 0, k
+        assert np.array_equal(res["pdl"][k], res["serial"][k]), k
