@@ -375,11 +375,11 @@ def run_ours(args):
                 "peak_source": pk_src + ", sustained bf16 (kernel timed inside a long step)",
                 "traffic": None}
         # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
-        # (profiles/r1_ncu_v8_summary.txt: dram__bytes_read.sum + dram__bytes_write.sum, one launch,
+        # (profiles/r1_ncu_v11_summary.txt: dram__bytes_read.sum + dram__bytes_write.sum, one launch,
         # 16384 leaves at 8x8); only quoted for the configuration it was captured on
         if dom == "trunk_tc" and args.board == 8 and args.games == 16384:
-            roof["traffic"] = 17240320 + 0
-            roof["traffic_source"] = "profiles/r1_ncu_v8_summary.txt (ncu --set full, 1 launch; algorithmic input planes 16.8 MB)"
+            roof["traffic"] = 17241856 + 512
+            roof["traffic_source"] = "profiles/r1_ncu_v11_summary.txt (ncu --set full, 1 launch; algorithmic input planes 16.8 MB)"
         if dom in fl and dom_ms > 0:
             ach = ctr["leaf_evals"] * fl[dom] / (dom_ms * 1e-3) / 1e12
             roof.update({"achieved": ach, "frac": ach / pk["bf16_tflops_sustained"],
