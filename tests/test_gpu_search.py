@@ -541,11 +541,21 @@ sys.path.insert(0, {root!r}); sys.path.insert(0, {tests!r})
 import numpy as np
 from helpers import load_golden_weights
 from alphazero_gomoku_b200 import Engine
+from alphazero_gomoku_b200.engine import weight_shapes
 out = {{}}
-for name, w, n in (("6_6_4", 6, 4), ("8_8_5", 8, 5)):
-    wts = load_golden_weights("weights_" + name)
+# shipped weights at 6x6 / 8x8; seeded He weights at 9x9 / 15x15 (other tree-kernel instantiations, the
+# large-board heads path) and for a wide trunk at 8x8 (layer-wise kernels, launched outside the chain)
+for name, w, n, trunk in (("6_6_4", 6, 4, None), ("8_8_5", 8, 5, None), ("9", 9, 5, None), ("15", 15, 5, None),
+                          ("8w", 8, 5, (64, 64, 128))):
+    if name in ("6_6_4", "8_8_5"):
+        wts = load_golden_weights("weights_" + name)
+    else:
+        rng = np.random.RandomState(w)
+        wts = [(rng.randn(*s) * (np.sqrt(2.0 / int(np.prod(s[1:]))) if len(s) > 1 else 0.1)).astype(np.float32)
+               for s in weight_shapes(w, w, trunk or (32, 64, 128))]
     for G in (1, 3, 64, 700):
-        e = Engine(width=w, height=w, n_in_row=n, n_games=G, n_playout=150, seed=5)
+        kw = dict(trunk=trunk) if trunk else dict()
+        e = Engine(width=w, height=w, n_in_row=n, n_games=G, n_playout=150, seed=5, **kw)
         e.set_weights(wts)
         rng = np.random.RandomState(G)
         for g in range(G):
@@ -577,7 +587,7 @@ def test_dependent_launch_chain_matches_serial_launches(tmp_path):
         out = tmp_path / (tag + ".npz")
         subprocess.check_call([sys.executable, str(script), str(out)], env=env, timeout=600)
         res[tag] = np.load(out)
-    assert sorted(res["pdl"].files) == sorted(res["serial"].files) and len(res["pdl"].files) == 16
+    assert sorted(res["pdl"].files) == sorted(res["serial"].files) and len(res["pdl"].files) == 40
     for k in res["pdl"].files:
         assert res["pdl"][k].sum() > 0, k
         assert np.array_equal(res["pdl"][k], res["serial"][k]), k
