@@ -3,11 +3,13 @@ one stream against K engines of G / K games on K streams of the same GPU, the wa
 interleaved on the host in chunks (the launch queue is finite).  The trunk kernel keeps every SM's
 shared memory; a 128-thread tree block (16 B static) fits beside it only just.
 usage: python tools/overlap_engines.py [games] [playouts] [chunk]"""
+import os
 import sys
 import time
 
-sys.path.insert(0, '/root/repo')
-sys.path.insert(0, '/root/repo/tests')
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, 'tests'))
 import numpy as np
 import torch
 from helpers import load_golden_weights
