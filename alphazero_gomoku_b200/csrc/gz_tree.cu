@@ -638,17 +638,31 @@ __device__ void gz_reroot(const TreeParams &p, int g, int mv, int lane)
     if (lane == 0) fs[top] = r;
     ++top;
     __syncwarp();
+    // Breadth-first over the dropped subtree, RU queued nodes per round: their child arrays are loaded
+    // together (one dependent DRAM round trip per round instead of one per node - a steady-state tree
+    // drops ~1500 nodes per move), then pushed from registers.
+    constexpr int RU = 8;
     while (scan < top) {
-        int node = fs[scan++];
-        NodeView v = gz_node_view(p.pool, nbase + node, p.Sp);
+        const int nb = min(RU, top - scan);
+        const int mine = lane < nb ? fs[scan + lane] : -1;
         for (int i0 = 0; i0 < p.Sp; i0 += GZ_WARP) {
-            int i = i0 + lane;
-            int c = v.child[i];
-            bool push = c >= 0 && !(node == r && is_child && i == mv);
-            unsigned b = __ballot_sync(0xffffffffu, push);
-            if (push) fs[top + __popc(b & ((1u << lane) - 1u))] = c;
-            top += __popc(b);
+            const int i = i0 + lane;
+            int c[RU];
+#pragma unroll
+            for (int u = 0; u < RU; ++u) {
+                const int node = __shfl_sync(0xffffffffu, mine, u);
+                c[u] = node >= 0 ? gz_node_view(p.pool, nbase + node, p.Sp).child[i] : -1;
+                if (node == r && is_child && i == mv) c[u] = -1; // the kept subtree stays
+            }
+#pragma unroll
+            for (int u = 0; u < RU; ++u) {
+                const bool push = c[u] >= 0;
+                const unsigned b = __ballot_sync(0xffffffffu, push);
+                if (push) fs[top + __popc(b & ((1u << lane) - 1u))] = c[u];
+                top += __popc(b);
+            }
         }
+        scan += nb;
         __syncwarp();
     }
     if (lane == 0) {
