@@ -79,8 +79,52 @@ class ClockSampler:
     def __init__(self, index):
         self.index = index
         self.proc = None
+        self.nvml = None
+
+    def _nvml_start(self):
+        """NVML polled every 10 ms from a thread (the main thread sits in cudaStreamSynchronize with the GIL
+        released): a short timed region still gets samples, which nvidia-smi's 200 ms loop does not."""
+        import pynvml as nv
+        import torch
+        nv.nvmlInit()
+        try:
+            uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+            h = nv.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+        except Exception:
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+        reasons_fn = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+            nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        mx = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+        st = {"sm": [], "mask": 0, "stop": False, "max": mx}
+
+        def loop():
+            while not st["stop"]:
+                try:
+                    st["sm"].append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                    st["mask"] |= int(reasons_fn(h))
+                except Exception:
+                    pass
+                time.sleep(0.01)
+        st["thread"] = threading.Thread(target=loop, daemon=True)
+        st["thread"].start()
+        self.nvml = st
+
+    def _nvml_stop(self):
+        st = self.nvml
+        st["stop"] = True
+        st["thread"].join(timeout=2)
+        # nvml.h: SwPowerCap 0x4, HwSlowdown 0x8, SwThermalSlowdown 0x20, HwThermalSlowdown 0x40
+        bits = {"sw_power_cap": 0x4, "hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40}
+        return {"sm_mhz": float(np.median(st["sm"])) if st["sm"] else None, "sm_max_mhz": st["max"],
+                "samples": len(st["sm"]), "reasons": sorted(k for k, b in bits.items() if st["mask"] & b),
+                "source": "nvml, 10 ms period"}
 
     def start(self):
+        try:
+            self._nvml_start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits", "-lms", "200"],
@@ -89,6 +133,8 @@ class ClockSampler:
             self.proc = None
 
     def stop(self):
+        if self.nvml is not None:
+            return self._nvml_stop()
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
