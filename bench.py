@@ -161,15 +161,20 @@ class ClockSampler:
 
 
 # ---- CPU legs (oracle port of the reference's CPU path) ----------------------------------------
-def cpu_selfplay_worker(arrs, width, n_in_row, n_playout, n_plies, out, idx, seed):
+def cpu_selfplay_worker(arrs, width, n_in_row, n_playout, n_plies, out, idx, seed, budget_s=None):
+    """n_plies of single-game self-play on the oracle port; with budget_s, stop after the first ply that
+    ends past that many seconds (at least 2 plies)."""
     from oracle import orc
+    t_start = time.perf_counter()
     net = orc.Net(width, width, arrs)
     b = orc.Board(width, width, n_in_row)
     b.init_board(0)
     m = orc.MCTS(5, n_playout, orc.EVAL_NET, net=net)
     rng = np.random.RandomState(seed)
     done = 0
-    for _ in range(n_plies):
+    for ply in range(n_plies):
+        if budget_s is not None and ply >= 2 and time.perf_counter() - t_start >= budget_s:
+            break
         acts, vis, _, _ = m.search(b)  # the C call releases the GIL
         done += n_playout
         p = vis / vis.sum()
@@ -182,15 +187,17 @@ def cpu_selfplay_worker(arrs, width, n_in_row, n_playout, n_plies, out, idx, see
     out[idx] = done
 
 
-def cpu_baseline(arrs, width, n_in_row, n_playout, n_plies=4):
-    """Single-thread oracle port (reference = single-threaded Python) on a bounded sample."""
+def cpu_baseline(arrs, width, n_in_row, n_playout, n_plies=64, budget_s=12.0):
+    """Single-thread oracle port (reference = single-threaded Python) on a bounded sample: self-play plies
+    from the empty board until budget_s seconds of CPU work are done (n_plies at most)."""
     out = [0]
     t0 = time.perf_counter()
-    cpu_selfplay_worker(arrs, width, n_in_row, n_playout, n_plies, out, 0, 0)
+    cpu_selfplay_worker(arrs, width, n_in_row, n_playout, n_plies, out, 0, 0, budget_s)
     dt = time.perf_counter() - t0
     return {"value": out[0] / dt, "unit": UNIT, "cores": 1, "kind": "port",
-            "sample": "oracle/ C port of mcts_alphaZero.MCTS + Net forward, 1 game, first %d plies x %d "
-                      "playouts from the empty %dx%d board, %.1f s" % (n_plies, n_playout, width, width, dt)}
+            "sample": "oracle/ C port of mcts_alphaZero.MCTS + Net forward, 1 thread, single-game self-play from the "
+                      "empty %dx%d board (a new game when one ends), %d plies x %d playouts, %.1f s"
+                      % (width, width, out[0] // n_playout, n_playout, dt)}
 
 
 def run_reference(args):
@@ -481,7 +488,7 @@ def run_ours(args):
         if world == 1 and not args.no_cpu_baseline:
             from oracle import orc
             orc.build()
-            line["cpu_baseline"] = cpu_baseline(arrs, args.board, args.n_in_row, args.playouts, args.cpu_plies)
+            line["cpu_baseline"] = cpu_baseline(arrs, args.board, args.n_in_row, args.playouts, args.cpu_plies, args.cpu_seconds)
         if tot_over:
             line["invalid"] = "tree pool overflowed: raise nodes_per_game"
         _JSON_LINE.append(json.dumps(line))
@@ -503,7 +510,8 @@ def main():
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--trunk", type=int, nargs=3, default=[32, 64, 128],
                     help="conv trunk widths (BASELINE config C4 'wider trunk': 64 128 256; seeded random weights)")
-    ap.add_argument("--cpu-plies", type=int, default=4)
+    ap.add_argument("--cpu-plies", type=int, default=64, help="cpu_baseline: at most this many plies")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="cpu_baseline: stop after this much CPU work")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--prefill-plies", type=int, default=24,
                     help="untimed setup plies before the warm-up that bring the slots to mixed game phases (0 = time the "
