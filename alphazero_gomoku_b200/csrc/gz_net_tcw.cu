@@ -54,6 +54,8 @@ stage_tcw_kernel(const float *__restrict__ planes, uint8_t *__restrict__ a0, con
                  long long maxB, TcGeom g)
 {
     using namespace tcw;
+    gz_pdl_wait(); // the leaf count and the planes come from the tree kernel before this one
+    gz_pdl_trigger();
     const long long B = count ? (long long)*count : maxB;
     const long long grp = blockIdx.x;
     if (grp * g.NB >= B) return;
@@ -100,8 +102,6 @@ conv_tcw_kernel(const uint8_t *__restrict__ act_in, const TcwLayer L, uint8_t *_
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
-    const long long B = __shfl_sync(0xffffffffu, count ? (long long)*count : maxB, 0);
-    const long long n_groups = (B + g.NB - 1) / g.NB;
     const uint32_t sbase = tc_smem_u32(smem);
     const uint32_t bar_a = sbase + OFF_BAR, bar_full = sbase + OFF_BAR + 128, bar_empty = sbase + OFF_BAR + 192;
     const uint32_t bar_done = sbase + OFF_BAR + 256, bar_free = sbase + OFF_BAR + 272; // one per accumulator buffer
@@ -145,6 +145,12 @@ conv_tcw_kernel(const uint8_t *__restrict__ act_in, const TcwLayer L, uint8_t *_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+    // the set-up above read only this layer's constants; the input image and the leaf count come from the
+    // kernels before this one in the chain (gz_common.cuh, gz_launch_chain)
+    gz_pdl_wait();
+    gz_pdl_trigger();
+    const long long B = __shfl_sync(0xffffffffu, count ? (long long)*count : maxB, 0);
+    const long long n_groups = (B + g.NB - 1) / g.NB;
 
     // Work units u = 0, 1, ... of this CTA = (group, chunk) pairs in order; unit u accumulates in TMEM
     // buffer u & 1 and is phase u >> 1 of that buffer's done / free barriers.
@@ -463,14 +469,16 @@ static int gz_net_forward_tcw(gz_engine *e, const float *d_planes, const int32_t
     if (L2.ns < 2 || L3.ns < 2) { e->err = "tcgen05 wide-trunk path: weight ring does not fit"; return GZ_E_INVALID; }
     {
         ProfScope ps(e, PC_TRUNK_TC);
-        stage_tcw_kernel<<<(unsigned)groups, 256, 0, e->stream>>>(d_planes, e->tcw_a0, d_count, maxB, g);
-        conv_tcw_kernel<0><<<grid, THREADS, OFF_A + (size_t)L1.nabuf * (L1.cin / 4) * CH + (size_t)L1.ns * 64 * L1.nc, e->stream>>>(
-            e->tcw_a0, L1, e->tcw_act1, nullptr, d_count, maxB, g, dbg1, nullptr, d_tl);
-        conv_tcw_kernel<0><<<grid, THREADS, OFF_A + (size_t)L2.nabuf * (L2.cin / 4) * CH + (size_t)L2.ns * 64 * L2.nc, e->stream>>>(
-            e->tcw_act1, L2, e->tcw_act2, nullptr, d_count, maxB, g, nullptr, nullptr, d_tl ? d_tl + 8 : nullptr);
-        conv_tcw_kernel<1><<<grid, THREADS, OFF_A + (size_t)L3.nabuf * (L3.cin / 4) * CH + (size_t)L3.ns * 64 * L3.nc, e->stream>>>(
-            e->tcw_act2, L3, nullptr, reinterpret_cast<__half *>(e->tc_head), d_count, maxB, g, dbg3, dbgh,
-            d_tl ? d_tl + 16 : nullptr);
+        auto lsmem = [](const TcwLayer &L) { return OFF_A + (size_t)L.nabuf * (L.cin / 4) * CH + (size_t)L.ns * 64 * L.nc; };
+        GZ_CUDA(e, gz_launch_chain(stage_tcw_kernel, dim3((unsigned)groups), dim3(256), 0, e->stream, d_planes, e->tcw_a0,
+                                   d_count, maxB, g));
+        GZ_CUDA(e, gz_launch_chain(conv_tcw_kernel<0>, dim3(grid), dim3(THREADS), lsmem(L1), e->stream, e->tcw_a0, L1,
+                                   e->tcw_act1, nullptr, d_count, maxB, g, dbg1, nullptr, d_tl));
+        GZ_CUDA(e, gz_launch_chain(conv_tcw_kernel<0>, dim3(grid), dim3(THREADS), lsmem(L2), e->stream, e->tcw_act1, L2,
+                                   e->tcw_act2, nullptr, d_count, maxB, g, nullptr, nullptr, d_tl ? d_tl + 8 : nullptr));
+        GZ_CUDA(e, gz_launch_chain(conv_tcw_kernel<1>, dim3(grid), dim3(THREADS), lsmem(L3), e->stream, e->tcw_act2, L3,
+                                   nullptr, reinterpret_cast<__half *>(e->tc_head), d_count, maxB, g, dbg3, dbgh,
+                                   d_tl ? d_tl + 16 : nullptr));
     }
     if (d_tl) {
         long long h[24];
