@@ -944,11 +944,7 @@ extern "C" int gz_pure_search(gz_engine *e, int32_t n_playout, uint32_t search_i
 {
     if (!e || n_playout < 0) return GZ_E_INVALID;
     GZ_CUDA(e, cudaSetDevice(e->cfg.device));
-    for (int i = 0; i < n_playout; ++i) {
-        GZ_TRY(gzk_select(e, true));
-        GZ_TRY(gzk_pure_expand_rollout_backup(e, search_id, (uint32_t)i));
-    }
-    return GZ_OK;
+    return gzk_pure_playouts(e, n_playout, search_id);
 }
 
 extern "C" int gz_pure_best_move(gz_engine *e, int32_t *moves)

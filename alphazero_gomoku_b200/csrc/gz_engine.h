@@ -202,7 +202,7 @@ int gzk_tree_reset(gz_engine *e);
 int gzk_select(gz_engine *e, bool pure);
 int gzk_expand_backup(gz_engine *e, const float *d_priors, const float *d_values, bool compacted);
 int gzk_expand_select(gz_engine *e, const float *d_priors, const float *d_values);
-int gzk_pure_expand_rollout_backup(gz_engine *e, uint32_t search_id, uint32_t playout_idx);
+int gzk_pure_playouts(gz_engine *e, int n, uint32_t search_id);
 int gzk_root_visits(gz_engine *e, int32_t *d_visits, double *d_q, int32_t *d_rootn);
 int gzk_update_with_move(gz_engine *e, const int32_t *d_moves);
 int gzk_root_select_move(gz_engine *e, float temp, int selfplay, int32_t *d_moves, float *d_probs,

@@ -181,7 +181,7 @@ __device__ __forceinline__ void gz_select_game(const TreeParams &p, int g, int l
     } else {
         int slot = 0;
         if (lane == 0) {
-            slot = atomicAdd(p.leaf_count, 1);
+            if (!PURE) slot = atomicAdd(p.leaf_count, 1); // pure MCTS rolls out in place: no leaf batch
             p.leaf_state[g] = 0;
             p.leaf_slot[g] = slot;
         }
