@@ -82,6 +82,7 @@ _PROTOS = {
     "gz_search": (C.c_int, [_P, C.c_int32]),
     "gz_search_select": (C.c_int, [_P, _P, _P, _P, _P]),
     "gz_search_expand_backup": (C.c_int, [_P, _P, _P]),
+    "gz_search_paths": (C.c_int, [_P, _P, _P]),
     "gz_root_visits": (C.c_int, [_P, _P, _P, _P]),
     "gz_update_with_move": (C.c_int, [_P, _P]),
     "gz_set_active": (C.c_int, [_P, _P]),

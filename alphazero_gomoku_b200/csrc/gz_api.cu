@@ -3,6 +3,7 @@
 #include "gz_engine.h"
 #include <cmath>
 #include <cstdio>
+#include <algorithm>
 #include <cstring>
 #include <new>
 
@@ -186,6 +187,7 @@ extern "C" int gz_create(const gz_config *cfg, gz_engine **out)
         delete e;
         return GZ_E_CUDA;
     }
+    if (cudaDeviceGetAttribute(&e->n_sm, cudaDevAttrMultiProcessorCount, cfg->device) != cudaSuccess) e->n_sm = 0;
     if (cfg->stream) { e->stream = (cudaStream_t)cfg->stream; e->own_stream = false; }
     else {
         if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess) {
@@ -710,6 +712,32 @@ extern "C" int gz_search_expand_backup(gz_engine *e, const float *priors, const 
     return a.finish();
 }
 
+__global__ void paths_export_kernel(const uint32_t *path, const int32_t *path_len, int G, int S, int Sp,
+                                    int32_t *moves_out, int32_t *len_out)
+{
+    const int g = blockIdx.x;
+    const int d = path_len[g];
+    for (int k = threadIdx.x; k < S; k += blockDim.x)
+        moves_out[(size_t)g * S + k] = k < d ? (int32_t)(path[(size_t)g * S + k] % (uint32_t)Sp) : -1;
+    if (threadIdx.x == 0 && len_out) len_out[g] = d;
+}
+
+extern "C" int gz_search_paths(gz_engine *e, int32_t *path_moves, int32_t *path_len)
+{
+    if (!e || !path_moves) return GZ_E_INVALID;
+    GZ_CUDA(e, cudaSetDevice(e->cfg.device));
+    const size_t G = e->G, S = e->S;
+    ArgStage a(e);
+    GZ_TRY(a.reserve(G * S * 4 + G * 4 + 1024));
+    int32_t *dm = a.out(path_moves, G * S);
+    int32_t *dl = a.out(path_len, G);
+    if (a.rc) return a.rc;
+    paths_export_kernel<<<e->G, 64, 0, e->stream>>>(e->path, e->path_len, e->G, e->S, e->Sp, dm, dl);
+    e->launches++;
+    GZ_CUDA(e, cudaGetLastError());
+    return a.finish();
+}
+
 extern "C" int gz_root_visits(gz_engine *e, int32_t *visits, double *q, int32_t *root_n)
 {
     if (!e) return GZ_E_INVALID;
@@ -791,8 +819,20 @@ extern "C" int gz_selfplay_begin(gz_engine *e, float temp, int32_t recycle)
         GZ_TRY(gz_dalloc(e, &e->gout_winner, (size_t)e->gout_cap));
         GZ_TRY(gz_dalloc(e, &e->gout_gid, (size_t)e->gout_cap));
     }
+    // Game ids key the Philox streams of the Dirichlet noise and the move sampling (gz_move.cu), so they must
+    // never repeat on one engine: a second begin continues after the largest id any slot has reached
+    // (recycling hands out id + G), instead of replaying ids 0..G-1 and with them the same noise.
     std::vector<int64_t> ids(G);
-    for (size_t g = 0; g < G; ++g) ids[g] = (int64_t)(e->cfg.game_id_base + g);
+    if (e->sp_ids_live) {
+        GZ_CUDA(e, cudaStreamSynchronize(e->stream));
+        GZ_CUDA(e, cudaMemcpy(ids.data(), e->sp_game_id, G * sizeof(int64_t), cudaMemcpyDeviceToHost));
+        int64_t mx = -1;
+        for (size_t g = 0; g < G; ++g) mx = std::max(mx, ids[g] - (int64_t)e->cfg.game_id_base);
+        e->sp_next_serial = std::max(e->sp_next_serial, mx + 1);
+    }
+    for (size_t g = 0; g < G; ++g) ids[g] = (int64_t)(e->cfg.game_id_base + (uint64_t)e->sp_next_serial + g);
+    e->sp_next_serial += (int64_t)G;
+    e->sp_ids_live = true;
     GZ_CUDA(e, cudaMemcpyAsync(e->sp_game_id, ids.data(), G * sizeof(int64_t), cudaMemcpyHostToDevice, e->stream));
     GZ_CUDA(e, cudaStreamSynchronize(e->stream));
     GZ_TRY(gzk_boards_reset(e, nullptr));
@@ -940,6 +980,20 @@ extern "C" int gz_selfplay_last(gz_engine *e, int32_t *moves, float *probs)
 }
 
 // ---- pure MCTS ----------------------------------------------------------------------------------
+// Board.get_move_target on an EMPTY board is the hard-coded box rows/cols 5..9 (game.py:41); on a board narrower
+// than 6 it holds no cell and the reference raises (max() of an empty sequence, mcts_pure.py:205).  The
+// kernels end such a rollout / skip such an expansion and count it; the next synchronising pure-MCTS call
+// reports it as an error instead of returning a move chosen from nothing.
+static int gz_check_empty_box(gz_engine *e)
+{
+    unsigned long long n = 0;
+    GZ_CUDA(e, cudaMemcpy(&n, &e->counters->empty_box, sizeof(n), cudaMemcpyDeviceToHost));
+    if (n == 0) return GZ_OK;
+    GZ_CUDA(e, cudaMemset(&e->counters->empty_box, 0, sizeof(n)));
+    e->err = "pure MCTS: empty candidate box (empty board narrower than 6: game.py:41 hard-codes rows/cols 5..9)";
+    return GZ_E_INVALID;
+}
+
 extern "C" int gz_pure_search(gz_engine *e, int32_t n_playout, uint32_t search_id)
 {
     if (!e || n_playout < 0) return GZ_E_INVALID;
@@ -956,7 +1010,8 @@ extern "C" int gz_pure_best_move(gz_engine *e, int32_t *moves)
     int32_t *dm = a.out(moves, e->G);
     if (a.rc) return a.rc;
     GZ_TRY(gzk_root_select_move(e, 1.0f, 0, dm, nullptr, true));
-    return a.finish();
+    GZ_TRY(a.finish());
+    return gz_check_empty_box(e);
 }
 
 extern "C" int gz_rollouts(gz_engine *e, int32_t n_rollouts, uint32_t search_id, int8_t *results,
@@ -976,7 +1031,7 @@ extern "C" int gz_rollouts(gz_engine *e, int32_t n_rollouts, uint32_t search_id,
     GZ_TRY(a.finish());
     GZ_CUDA(e, cudaMemcpy(&c1, e->counters, sizeof(c1), cudaMemcpyDeviceToHost));
     if (total_plies) *total_plies = (int64_t)(c1.rollout_plies - c0.rollout_plies);
-    return GZ_OK;
+    return gz_check_empty_box(e);
 }
 
 extern "C" int gz_get_counters(gz_engine *e, gz_counters *out, int32_t reset)

@@ -126,40 +126,67 @@ __host__ __device__ __forceinline__ uint32_t bb_row(const BB &a, int h)
     return (uint32_t)(w >> ((h & 3) * 16)) & 0xFFFFu;
 }
 
-// Board.get_move_target (game.py:35-58): bounding box of all stones grown by 2 with the
-// reference's clipping; empty board -> rows 5..9 x cols 5..9.  Returns box & legal.
-__host__ __device__ __forceinline__ BB bb_move_target(const BB &occ, const BB &legal, int W, int H)
+// Bounding box of the stones of a 256-bit occupancy word, branch-free: rows from the lowest / highest
+// set bit (bit = 16 * row + col), columns from the OR of all rows folded onto 16 bits.
+struct BBox {
+    int rmin, rmax, cmin, cmax; // rmax < 0: no stone
+};
+__device__ __forceinline__ BBox bb_bbox(const BB &occ)
 {
-    int top, bottom, left, right;
-    uint32_t cols = 0;
-    int rmin = 99, rmax = -1;
-    for (int h = 0; h < H; ++h) {
-        uint32_t r = bb_row(occ, h);
-        cols |= r;
-        if (r) {
-            if (h < rmin) rmin = h;
-            rmax = h;
-        }
+    BBox b;
+    const uint64_t any = occ.w[0] | occ.w[1] | occ.w[2] | occ.w[3];
+    const int lo = occ.w[0] ? __ffsll((long long)occ.w[0]) - 1
+                 : occ.w[1] ? 63 + __ffsll((long long)occ.w[1])
+                 : occ.w[2] ? 127 + __ffsll((long long)occ.w[2])
+                            : 191 + __ffsll((long long)occ.w[3]);
+    const int hi = occ.w[3] ? 255 - __clzll((long long)occ.w[3])
+                 : occ.w[2] ? 191 - __clzll((long long)occ.w[2])
+                 : occ.w[1] ? 127 - __clzll((long long)occ.w[1])
+                            : 63 - __clzll((long long)occ.w[0]);
+    uint32_t c = (uint32_t)any | (uint32_t)(any >> 32);
+    c = (c | (c >> 16)) & 0xFFFFu;
+    b.rmin = lo >> 4;
+    b.rmax = any ? (hi >> 4) : -1;
+    b.cmin = __ffs((int)c) - 1;
+    b.cmax = 31 - __clz((int)c);
+    return b;
+}
+__device__ __forceinline__ void bbox_add(BBox &b, int bit)
+{
+    const int r = bit >> 4, c = bit & 15;
+    if (b.rmax < 0) { b.rmin = b.rmax = r; b.cmin = b.cmax = c; return; }
+    b.rmin = min(b.rmin, r); b.rmax = max(b.rmax, r);
+    b.cmin = min(b.cmin, c); b.cmax = max(b.cmax, c);
+}
+// Board.get_move_target (game.py:35-58) from a bounding box: the box grown by 2 with the reference's
+// clipping (:48-52; `top` / `right` may land one past the board, where `legal` is empty), no stone ->
+// rows 5..9 x cols 5..9 (:41).  Returns box & legal.  Straight-line code: every row of the board is
+// 16 bits, so the box is one 16-bit column pattern replicated over the rows bottom..top.
+__device__ __forceinline__ BB bb_target_from_bbox(const BBox &bx, const BB &legal, int W, int H)
+{
+    int top = 9, bottom = 5, left = 5, right = 9;
+    if (bx.rmax >= 0) {
+        top = (bx.rmax <= H - 2) ? bx.rmax + 2 : H;
+        bottom = (bx.rmin >= 2) ? bx.rmin - 2 : 0;
+        left = (bx.cmin >= 2) ? bx.cmin - 2 : 0;
+        right = (bx.cmax <= W - 2) ? bx.cmax + 2 : W;
     }
-    if (rmax < 0) {
-        top = 9; bottom = 5; left = 5; right = 9;
-    } else {
-        int cmin = 0, cmax = 0;
-        for (int c = 0; c < 16; ++c)
-            if ((cols >> c) & 1u) { cmin = c; break; }
-        for (int c = 15; c >= 0; --c)
-            if ((cols >> c) & 1u) { cmax = c; break; }
-        top = (rmax <= H - 2) ? rmax + 2 : H;
-        bottom = (rmin >= 2) ? rmin - 2 : 0;
-        left = (cmin >= 2) ? cmin - 2 : 0;
-        right = (cmax <= W - 2) ? cmax + 2 : W;
+    right = min(right, 15);
+    top = min(top, 15);
+    const uint32_t rowmask = ((2u << right) - 1u) & ~((1u << left) - 1u) & 0xFFFFu;
+    const uint64_t rep = (uint64_t)rowmask * 0x0001000100010001ull;
+    BB t;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int lo = max(bottom - 4 * i, 0), hi = min(top - 4 * i, 3);
+        const uint64_t m = (hi >= lo) ? ((~0ull >> (48 - 16 * max(hi, 0))) & (~0ull << (16 * min(lo, 3)))) : 0ull;
+        t.w[i] = rep & m & legal.w[i];
     }
-    BB box = bb_zero();
-    if (right > 15) right = 15;
-    if (left > 15) return box;
-    uint32_t rowmask = (uint32_t)(((1ull << (right + 1)) - 1ull) & ~((1ull << left) - 1ull)) & 0xFFFFu;
-    for (int h = bottom; h <= top && h < 16; ++h) box.w[h >> 2] |= (uint64_t)rowmask << ((h & 3) * 16);
-    return bb_and(box, legal);
+    return t;
+}
+__device__ __forceinline__ BB bb_move_target(const BB &occ, const BB &legal, int W, int H)
+{
+    return bb_target_from_bbox(bb_bbox(occ), legal, W, H);
 }
 
 // the same box computed by a warp: lane h holds board row h (every lane returns the full result)
@@ -188,22 +215,76 @@ __device__ __forceinline__ BB bb_move_target_warp(const BB &occ, const BB &legal
     return bb_and(box, legal);
 }
 
-// index (bit position) of the k-th set bit (k from 0) of a 256-bit word
+// index (bit position) of the k-th set bit (k from 0) of a 256-bit word, -1 when there are not that
+// many: word by prefix popcounts, then a popcount binary search inside the word (32 / 16 / 8 / 4 / 2 / 1),
+// straight-line selects instead of a clear-lowest-bit loop (up to 63 dependent, divergent iterations).
 __device__ __forceinline__ int bb_select(const BB &a, int k)
 {
-    int base = 0;
+    const int c0 = __popcll(a.w[0]), c1 = __popcll(a.w[1]), c2 = __popcll(a.w[2]), c3 = __popcll(a.w[3]);
+    const int p1 = c0, p2 = c0 + c1, p3 = p2 + c2;
+    if (k < 0 || k >= p3 + c3) return -1;
+    const int i = (k >= p1) + (k >= p2) + (k >= p3);
+    k -= (i == 0) ? 0 : (i == 1) ? p1 : (i == 2) ? p2 : p3;
+    const uint64_t x = (i == 0) ? a.w[0] : (i == 1) ? a.w[1] : (i == 2) ? a.w[2] : a.w[3];
+    uint32_t y = (uint32_t)x;
+    int base = 64 * i;
+    int c = __popc(y);
+    if (k >= c) { k -= c; y = (uint32_t)(x >> 32); base += 32; }
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) {
+        const uint32_t lowm = (1u << s) - 1u;
+        c = __popc(y & lowm);
+        const bool up = k >= c;
+        k -= up ? c : 0;
+        y = up ? (y >> s) : y;
+        y &= lowm;
+        base += up ? s : 0;
+    }
+    return base;
+}
+// logical right shift by a compile-time amount 0 < S < 256
+template <int S> __device__ __forceinline__ BB bb_shr_c(const BB &a)
+{
+    constexpr int q = S >> 6, r = S & 63;
+    BB o;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        int c = __popcll(a.w[i]);
-        if (k < c) {
-            uint64_t x = a.w[i];
-            for (int j = 0; j < k; ++j) x &= x - 1ull;
-            return base + __ffsll((long long)x) - 1;
-        }
-        k -= c;
-        base += 64;
+        const uint64_t lo = (i + q < 4) ? a.w[(i + q) & 3] : 0ull;
+        const uint64_t hi = (i + q + 1 < 4) ? a.w[(i + q + 1) & 3] : 0ull;
+        o.w[i] = r ? ((lo >> r) | (hi << ((64 - r) & 63))) : lo;
     }
-    return -1;
+    return o;
+}
+// n-in-a-row of one colour in direction S with n a compile-time constant: run lengths double
+// (pairs, quads, ...) instead of growing by one per step: 3 shift/AND steps for five in a row.
+template <int N, int S> __device__ __forceinline__ BB bb_runs_c(const BB &b)
+{
+    static_assert(N >= 2 && N <= 8, "n_in_row");
+    BB t = bb_and(b, bb_shr_c<S>(b)); // runs of 2
+    if (N == 2) return t;
+    if (N == 3) return bb_and(t, bb_shr_c<2 * S>(b));
+    BB u = bb_and(t, bb_shr_c<2 * S>(t)); // runs of 4
+    if (N == 4) return u;
+    if (N == 5) return bb_and(u, bb_shr_c<4 * S>(b));
+    if (N == 6) return bb_and(u, bb_shr_c<4 * S>(t));
+    if (N == 7) return bb_and(bb_and(u, bb_shr_c<4 * S>(t)), bb_shr_c<6 * S>(b));
+    return bb_and(u, bb_shr_c<4 * S>(u));
+}
+template <int N> __device__ __forceinline__ bool bb_has_line_c(const BB &b)
+{
+    const BB e = bb_runs_c<N, 1>(b), n = bb_runs_c<N, 16>(b), ne = bb_runs_c<N, 17>(b), nw = bb_runs_c<N, 15>(b);
+    return bb_any(bb_or(bb_or(e, n), bb_or(ne, nw)));
+}
+// n-in-a-row for the side that just moved: compile-time n for the usual 3..6, else the generic detector
+__device__ __forceinline__ bool bb_has_line_n(const BB &b, int n)
+{
+    switch (n) {
+    case 3: return bb_has_line_c<3>(b);
+    case 4: return bb_has_line_c<4>(b);
+    case 5: return bb_has_line_c<5>(b);
+    case 6: return bb_has_line_c<6>(b);
+    default: return bb_has_line(b, n);
+    }
 }
 __host__ __device__ __forceinline__ int bb_bit_to_move(int bit, int W) { return (bit >> 4) * W + (bit & 15); }
 

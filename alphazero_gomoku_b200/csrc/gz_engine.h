@@ -32,7 +32,7 @@ __host__ __device__ __forceinline__ NodeView gz_node_view(uint8_t *pool, size_t 
 // device-side counters (one struct in device memory, updated with warp-aggregated atomics)
 struct DevCounters {
     unsigned long long select_levels, select_children, playouts, leaf_evals, expanded_children,
-        rollout_plies, pool_overflows, plies, games_finished, samples_out, dropped, wins[3], max_nodes;
+        rollout_plies, pool_overflows, plies, games_finished, samples_out, dropped, wins[3], max_nodes, empty_box;
 };
 
 struct NetWeights {
@@ -114,6 +114,8 @@ struct gz_engine {
     int32_t *sp_moves;   // [G][S] moves of the game in progress
     float *sp_pi;        // [G][S][S] pi per ply of the game in progress
     int64_t *sp_game_id; // [G]
+    int64_t sp_next_serial; // next unused game serial (ids = game_id_base + serial): never reset
+    bool sp_ids_live;       // sp_game_id holds ids of an earlier begin
     int32_t *sel_moves;  // [G] scratch: chosen moves
     float *sel_probs;    // [G][S] scratch: pi
     // finished-game output ring (device), drained by the host

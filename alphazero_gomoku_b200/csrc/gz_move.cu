@@ -110,7 +110,11 @@ root_select_kernel(TreeParams p, MoveParams mp, int32_t *moves, float *probs)
         return;
     }
     const uint32_t ply = (uint32_t)p.meta[g].n_stones;
-    const uint32_t gid = (uint32_t)(mp.game_id ? (uint64_t)mp.game_id[g] : mp.game_id_base + (uint64_t)g);
+    // both halves of the 64-bit game id enter the stream: low word in the counter, high word in the key
+    // (ranks use game_id_base = rank << 40, which a 32-bit truncation would drop)
+    const uint64_t gid64 = mp.game_id ? (uint64_t)mp.game_id[g] : mp.game_id_base + (uint64_t)g;
+    const uint32_t gid = (uint32_t)gid64;
+    const uint32_t k1g = mp.k1 ^ (uint32_t)(gid64 >> 32);
     if (mp.selfplay) {
         double gm[GZ_MAXCH];
         double gsum = 0.0;
@@ -118,7 +122,7 @@ root_select_kernel(TreeParams p, MoveParams mp, int32_t *moves, float *probs)
         for (int j = 0; j < GZ_MAXCH; ++j) {
             gm[j] = 0.0;
             if (isch[j]) {
-                gm[j] = gz_gamma((double)mp.alpha, mp.k0, mp.k1, (uint32_t)(j * GZ_WARP + lane), ply, gid,
+                gm[j] = gz_gamma((double)mp.alpha, mp.k0, k1g, (uint32_t)(j * GZ_WARP + lane), ply, gid,
                                  0xD1A00000u);
                 gsum += gm[j];
             }
@@ -142,7 +146,7 @@ root_select_kernel(TreeParams p, MoveParams mp, int32_t *moves, float *probs)
     for (int j = 0; j < GZ_MAXCH; ++j) tot += x[j];
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, off);
-    Philox4 rr = philox4x32(mp.k0, mp.k1, 0u, ply, gid, 0x5A3B0000u);
+    Philox4 rr = philox4x32(mp.k0, k1g, 0u, ply, gid, 0x5A3B0000u);
     const double target = gz_u01(rr.x) * tot;
     double run = 0.0;
     int chosen = -1, lastch = -1;

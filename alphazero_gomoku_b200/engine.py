@@ -224,6 +224,13 @@ class Engine:
         va = values if hasattr(values, "data_ptr") else np.ascontiguousarray(values, dtype=np.float32)
         self._ck(self.L.gz_search_expand_backup(self._h, _ptr(pr), _ptr(va)))
 
+    def search_paths(self):
+        """(path_moves [G,S] with -1 padding, path_len [G]) of the last search_select descent."""
+        mv = np.zeros((self.G, self.S), np.int32)
+        ln = np.zeros(self.G, np.int32)
+        self._ck(self.L.gz_search_paths(self._h, _ptr(mv), _ptr(ln)))
+        return mv, ln
+
     def root_visits(self, want_q=False):
         G, S = self.G, self.S
         vis = np.zeros((G, S), np.int32)

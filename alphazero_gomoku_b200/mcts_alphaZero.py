@@ -34,6 +34,26 @@ def _net_of(fn):
     return None
 
 
+def tree_pool_nodes(S, n_playout, budget_bytes=2 << 30):
+    """Node blocks for a one-game tree that is re-rooted with subtree reuse (update_with_move(move)): a
+    search adds at most n_playout nodes and a game has at most S searches, so S * n_playout can never
+    overflow; that bound is taken while it fits `budget_bytes` of HBM (20 * Sp bytes per block), else the
+    budget, never less than the engine default 8 * n_playout + 8 (measured high-water mark 6.9 * n_playout).
+    A search that does run out raises (check_pool) instead of silently leaving leaves unexpanded."""
+    sp = (S + 31) // 32 * 32
+    return int(max(8 * n_playout + 8, min(S * n_playout + 8, budget_bytes // (20 * sp))))
+
+
+def check_pool(owner, engine):
+    """Raise if the search just run dropped an expansion because the tree pool was full (the reference
+    never drops one: mcts_alphaZero.py:137 always expands a non-terminal leaf)."""
+    n = engine.selfplay_stats()["pool_overflows"]
+    if n > getattr(owner, "_overflows", 0):
+        owner._overflows = n
+        raise MemoryError("gomoku_b200: the device tree pool of this search is exhausted (%d expansions dropped); "
+                          "create the player with a smaller n_playout or reset it with update_with_move(-1)" % n)
+
+
 class MCTS(object):
     """mcts_alphaZero.py:95-192 over a one-slot device tree."""
 
@@ -52,10 +72,10 @@ class MCTS(object):
         if self._engine is None or geom != self._geom:
             if self._engine is not None:
                 self._engine.close()
-            # node pool: tree reuse keeps a subtree and adds n_playout nodes per move
             self._engine = Engine(width=geom[0], height=geom[1], n_in_row=geom[2], n_games=1,
                                   n_playout=self._n_playout, c_puct=float(self._c_puct),
-                                  nodes_per_game=4 * self._n_playout + 8)
+                                  nodes_per_game=tree_pool_nodes(geom[0] * geom[1], self._n_playout))
+            self._overflows = 0
             self._geom = geom
             self._weights_version = -1
         if self._net is not None and self._weights_version != self._net.version:
@@ -76,6 +96,7 @@ class MCTS(object):
         else:
             for _ in range(self._n_playout):
                 self._playout_external(e, state)
+        check_pool(self, e)
         vis, _ = e.root_visits()
         acts = np.nonzero(vis[0] >= 0)[0]
         visits = vis[0][acts].astype(np.float64)

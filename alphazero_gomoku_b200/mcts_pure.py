@@ -9,6 +9,7 @@ import logging
 import numpy as np
 
 from .engine import Engine
+from .mcts_alphaZero import check_pool, tree_pool_nodes
 
 _logger = logging.getLogger(__name__)
 
@@ -30,6 +31,9 @@ class MCTS(object):
     """mcts_pure.py:124-246 over a one-slot device tree."""
 
     def __init__(self, policy_value_fn=policy_value_fn, c_puct=5, n_playout=1000, seed=None):
+        if policy_value_fn is not globals()["policy_value_fn"]:
+            # the device search hard-wires mcts_pure.policy_value_fn (uniform priors over move_target)
+            raise ValueError("mcts_pure.MCTS runs on the device with mcts_pure.policy_value_fn only")
         self._policy = policy_value_fn
         self._c_puct = c_puct
         self._n_playout = int(n_playout)
@@ -45,7 +49,9 @@ class MCTS(object):
                 self._engine.close()
             self._engine = Engine(width=geom[0], height=geom[1], n_in_row=geom[2], n_games=1,
                                   n_playout=self._n_playout, c_puct=float(self._c_puct),
-                                  nodes_per_game=self._n_playout + 8, seed=self._seed)
+                                  nodes_per_game=tree_pool_nodes(geom[0] * geom[1], self._n_playout),
+                                  seed=self._seed)
+            self._overflows = 0
             self._geom = geom
         return self._engine
 
@@ -55,7 +61,9 @@ class MCTS(object):
         e.boards_set(0, list(board.states.keys()), getattr(board, "_start", 0))
         self._search_id += 1
         e.pure_search(self._n_playout, self._search_id)
-        return int(e.pure_best_move()[0])
+        move = int(e.pure_best_move()[0])
+        check_pool(self, e)
+        return move
 
     def root_visits(self):
         vis, _ = self._engine.root_visits()

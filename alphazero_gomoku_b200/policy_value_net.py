@@ -34,13 +34,22 @@ def load_model_file(path, width, height):
     """Reads a torch state_dict (policy_value_net_pytorch.py:76-78) or a Theano/Lasagne pickle of
     16 arrays (policy_value_net.py:118-121); returns (arrays, layout)."""
     from . import _lib
-    try:
+    with open(path, "rb") as f:
+        head = f.read(8)
+    # torch.save writes a zip archive (PK\x03\x04) or, before torch 1.6, a pickle of the magic number
+    # 0x1950a86a20f9469cfc6c; anything else is treated as a Theano/Lasagne pickle.  A torch archive that
+    # fails to load raises its own error instead of falling through to an unrelated unpickling error.
+    is_torch = head[:4] == b"PK\x03\x04"
+    if not is_torch and head[:2] == b"\x80\x02":
+        with open(path, "rb") as f:
+            is_torch = b"\x8a\x0a\x6c\xfc\x9c\x46\xf9\x20\x6a\xa8\x50\x19" in f.read(32)
+    if is_torch:
         import torch
-        sd = torch.load(path, map_location="cpu")
-        if isinstance(sd, dict) and STATE_DICT_KEYS[0] in sd:
-            return [sd[k].detach().cpu().float().numpy() for k in STATE_DICT_KEYS], _lib.LAYOUT_TORCH
-    except Exception:
-        pass
+        sd = torch.load(path, map_location="cpu", weights_only=True)
+        if not (isinstance(sd, dict) and all(k in sd for k in STATE_DICT_KEYS)):
+            raise Exception("model file %s: not a state_dict of the reference Net (keys %s...)"
+                            % (path, list(sd)[:3] if isinstance(sd, dict) else type(sd)))
+        return [sd[k].detach().cpu().float().numpy() for k in STATE_DICT_KEYS], _lib.LAYOUT_TORCH
     with open(path, "rb") as f:
         params = pickle.load(f, encoding="bytes")
     if len(params) != 16:

@@ -128,6 +128,11 @@ int gz_search(gz_engine *e, int32_t n_playout);
 int gz_search_select(gz_engine *e, int8_t *leaf_state, float *leaf_planes /*[G,4,W,H]*/,
                      int8_t *leaf_cells /*[G,S] or NULL*/, int8_t *leaf_player /*[G] or NULL*/);
 int gz_search_expand_backup(gz_engine *e, const float *priors, const float *values);
+/* The descent of the last gz_search_select, i.e. the (action, node) = node.select(c_puct) sequence of
+ * one _playout (mcts_alphaZero.py:118-129): path_moves[G,S] holds the chosen move of every level (first
+ * path_len[g] entries of row g), path_len[G] the depth.  Lets a test replay every single select decision
+ * of the device against the reference's arithmetic, not only compare final visit counts.            */
+int gz_search_paths(gz_engine *e, int32_t *path_moves /*[G,S]*/, int32_t *path_len /*[G]*/);
 int gz_root_visits(gz_engine *e, int32_t *visits /*[G,S], -1 = not a child*/,
                    double *q /*[G,S] or NULL*/, int32_t *root_n /*[G] or NULL*/);
 /* MCTS.update_with_move (mcts_alphaZero.py:183-192): moves[G]; a move that is a root

@@ -39,6 +39,12 @@ class CNet(C.Structure):
                 ("c3", C.c_int), ("p", C.POINTER(C.c_float) * 16)]
 
 
+class CReplayStats(C.Structure):
+    _fields_ = [("max_regret_rel", C.c_double), ("max_regret_margin", C.c_double), ("min_gap_rel", C.c_double),
+                ("min_gap_margin", C.c_double), ("n_decisions", C.c_longlong), ("n_deviations", C.c_longlong),
+                ("n_tie_order", C.c_longlong)]
+
+
 EVAL_CB = C.CFUNCTYPE(None, C.POINTER(CBoard), C.POINTER(C.c_float), C.POINTER(C.c_float))
 
 _lib = None
@@ -56,6 +62,8 @@ def lib():
         L.orc_mcts_set_stream.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
         L.orc_mcts_search.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                       C.c_void_p, C.c_void_p]
+        L.orc_mcts_replay.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_replay_stats_init.argtypes = [C.c_void_p]
         L.orc_mcts_root_visits.argtypes = [C.c_void_p]
         L.orc_mcts_root_q.argtypes = [C.c_void_p]
         L.orc_mcts_root_q.restype = C.c_double
@@ -208,7 +216,7 @@ class MCTS:
         visits = np.zeros(MAXS, dtype=np.int32)
         q = np.zeros(MAXS, dtype=np.float64)
         p = np.zeros(MAXS, dtype=np.float64)
-        k = lib().orc_mcts_search(self.h, C.addressof(board.c), n_playout, acts.ctypes.data,
+        k = lib().orc_mcts_search(self.h, C.addressof(board.c) if board is not None else None, n_playout, acts.ctypes.data,
                                   visits.ctypes.data, q.ctypes.data, p.ctypes.data)
         return acts[:k].copy(), visits[:k].copy(), q[:k].copy(), p[:k].copy()
 
@@ -219,6 +227,28 @@ class MCTS:
         probs = np.exp(x - np.max(x))
         probs /= np.sum(probs)
         return tuple(int(a) for a in acts), probs
+
+    def replay(self, board, tlen, trace):
+        """Decision-level replay of a recorded search (orc_mcts_replay): tlen uint8 [n_playout] = depth of
+        every playout, trace uint8 = the chosen moves back to back.  Returns the statistics dict; raises
+        AssertionError when a recorded path is not a root-to-leaf path of the oracle's tree."""
+        tlen = np.ascontiguousarray(tlen, dtype=np.uint8)
+        trace = np.ascontiguousarray(trace, dtype=np.uint8)
+        assert int(tlen.sum()) == trace.size, (int(tlen.sum()), trace.size)
+        st = CReplayStats()
+        lib().orc_replay_stats_init(C.byref(st))
+        tr = trace if trace.size else np.zeros(1, np.uint8)
+        rc = lib().orc_mcts_replay(self.h, C.addressof(board.c), tlen.ctypes.data, tr.ctypes.data,
+                                   int(tlen.size), C.byref(st))
+        if rc != 0:
+            raise AssertionError("recorded path of playout %d is not a root-to-leaf path of the oracle tree "
+                                 "(code %d: 1 = runs past a leaf, 2 = move is not a child, 3 = stops above the leaf)"
+                                 % ((-rc) // 8 - 1, (-rc) % 8))
+        return {k: getattr(st, k) for k, _ in CReplayStats._fields_}
+
+    def root_children(self):
+        """(acts, visits, Q, P) of the root children without running playouts."""
+        return self.search(None, n_playout=0)
 
     def update_with_move(self, move):
         lib().orc_mcts_update_with_move(self.h, int(move))

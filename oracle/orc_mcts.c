@@ -152,19 +152,24 @@ static void eval_net(orc_mcts *m, const orc_board *b, float *probs, float *value
 /* mcts_pure.py:193-212 _evaluate_rollout with rollout_policy_fn (:15-30): each ply a
  * uniformly random move of the current move_target box.  The reference draws
  * np.random.rand per candidate and takes the argmax (= uniform choice); here the choice
- * is index = mulhi32(philox(...)[0], n_target), bit-identical to the CUDA rollout kernel. */
+ * is index = mulhi32(r[ply % 4], n_target) with r = philox(key, (playout, ply / 4, game, search)),
+ * one Philox4x32 call per four plies, bit-identical to the CUDA rollout kernel
+ * (csrc/gz_rollout.cu).  An empty candidate box (empty board narrower than 6, game.py:41: the
+ * reference raises in max([])) ends the rollout as a tie. */
 static int evaluate_rollout(orc_mcts *m, orc_board *b, int limit)
 {
     int player = b->current_player;
     int winner = -1, end = 0;
+    uint32_t r[4] = {0, 0, 0, 0};
     for (int i = 0; i < limit; ++i) {
         end = orc_board_game_end(b, &winner);
         if (end) break;
         orc_board_get_move_target(b);
-        uint32_t r[4];
-        orc_philox4x32((uint32_t)m->salt, (uint32_t)(m->salt >> 32), m->playout_idx, (uint32_t)i,
-                       m->game_id, m->search_id, r);
-        uint32_t idx = (uint32_t)(((uint64_t)r[0] * (uint64_t)b->n_target) >> 32);
+        if (b->n_target == 0) { end = 1; winner = -1; break; }
+        if ((i & 3) == 0)
+            orc_philox4x32((uint32_t)m->salt, (uint32_t)(m->salt >> 32), m->playout_idx, (uint32_t)(i >> 2),
+                           m->game_id, m->search_id, r);
+        uint32_t idx = (uint32_t)(((uint64_t)r[i & 3] * (uint64_t)b->n_target) >> 32);
         orc_board_do_move(b, b->move_target[idx]);
         m->n_rollout_plies++;
     }
@@ -172,6 +177,8 @@ static int evaluate_rollout(orc_mcts *m, orc_board *b, int limit)
     if (winner == -1) return 0;
     return winner == player ? 1 : -1;
 }
+
+static void playout_leaf(orc_mcts *m, orc_board *state, orc_node *node);
 
 /* mcts_alphaZero.py:113-148 _playout / mcts_pure.py:156-191 _playout. */
 static void playout(orc_mcts *m, orc_board *state)
@@ -182,6 +189,12 @@ static void playout(orc_mcts *m, orc_board *state)
         orc_board_do_move(state, node->acts[i]);
         node = node->kids[i];
     }
+    playout_leaf(m, state, node);
+}
+
+/* the part of _playout after the descent: evaluate, expand, back up (:131-148) */
+static void playout_leaf(orc_mcts *m, orc_board *state, orc_node *node)
+{
     int acts[ORC_MAXS];
     double probs[ORC_MAXS];
     float pf[ORC_MAXS];
@@ -214,6 +227,91 @@ static void playout(orc_mcts *m, orc_board *state)
         else leaf_value = (winner == state->current_player) ? 1.0 : -1.0;
     }
     node_update_recursive(node, -leaf_value);
+}
+
+/* Decision-level replay (test infrastructure for the search tier): run one playout whose descent follows
+ * a RECORDED path (the moves another implementation's select calls returned: the reference's, captured by
+ * tests/golden/make_golden2.py, or the CUDA engine's, gz_search_paths) instead of this tree's own argmax,
+ * and measure at every level how far the recorded choice is from the oracle's:
+ *   regret  = score(oracle argmax) - score(recorded move)  >= 0, in the reference's arithmetic (:75-83)
+ *   gap     = score(best) - score(second best)               (SURVEY App. B near-tie measure)
+ * both relative to max(1, |best score|), and divided by the sensitivity of a score difference to an error
+ * eps of the evaluator, sens = c_puct * sqrt(N_parent) * (1/(1+n_a) + 1/(1+n_b)) + 2 ("margin": the largest
+ * uniform net error that provably cannot flip this decision).  n_tie_order counts recorded moves that tie
+ * the best score exactly but are not the FIRST maximum (mcts_alphaZero.py:55: Python max keeps the first).
+ * The leaf is then evaluated, expanded and backed up exactly like playout(), so after n playouts the oracle
+ * tree is the tree the recorded search built.  Returns 0, or <0 when the path is not a root-to-leaf path
+ * of this tree (a structural divergence: that is a parity failure, not a near-tie). */
+typedef struct {
+    double max_regret_rel, max_regret_margin, min_gap_rel, min_gap_margin;
+    long long n_decisions, n_deviations, n_tie_order;
+} orc_replay_stats;
+
+void orc_replay_stats_init(orc_replay_stats *st)
+{
+    memset(st, 0, sizeof(*st));
+    st->min_gap_rel = 1e300;
+    st->min_gap_margin = 1e300;
+}
+
+int orc_mcts_playout_forced(orc_mcts *m, const orc_board *b, const uint8_t *path, int len,
+                            orc_replay_stats *st)
+{
+    orc_board state = *b;
+    orc_node *node = m->root;
+    for (int j = 0; j < len; ++j) {
+        if (node->n_children == 0) return -1;            /* recorded path runs past this tree's leaf */
+        int best = 0, second = -1, forced = -1;
+        double bv = -1e300, sv = -1e300;
+        for (int i = 0; i < node->n_children; ++i) {
+            double v = node_get_value(node->kids[i], m->c_puct);
+            if (node->acts[i] == (int)path[j]) forced = i;
+            if (i == 0) { bv = v; best = 0; }
+            else if (v > bv) { sv = bv; second = best; bv = v; best = i; }   /* strict: first maximum wins */
+            else if (second < 0 || v > sv) { sv = v; second = i; }
+        }
+        if (forced < 0) return -2;                       /* recorded move is not a child here */
+        double fv = node->kids[forced]->Q + node->kids[forced]->u;
+        double sq = sqrt((double)node->n_visits);
+        double scale = fabs(bv) > 1.0 ? fabs(bv) : 1.0;
+        st->n_decisions++;
+        if (forced != best) {
+            double regret = bv - fv;
+            double sens = m->c_puct * sq * (1.0 / (1 + node->kids[best]->n_visits) +
+                                            1.0 / (1 + node->kids[forced]->n_visits)) + 2.0;
+            st->n_deviations++;
+            if (regret == 0.0) st->n_tie_order++;        /* equal score, but not the first maximum */
+            if (regret / scale > st->max_regret_rel) st->max_regret_rel = regret / scale;
+            if (regret / sens > st->max_regret_margin) st->max_regret_margin = regret / sens;
+        }
+        if (second >= 0) {
+            double gap = bv - sv;
+            double sens = m->c_puct * sq * (1.0 / (1 + node->kids[best]->n_visits) +
+                                            1.0 / (1 + node->kids[second]->n_visits)) + 2.0;
+            if (gap / scale < st->min_gap_rel) st->min_gap_rel = gap / scale;
+            if (gap / sens < st->min_gap_margin) st->min_gap_margin = gap / sens;
+        }
+        orc_board_do_move(&state, node->acts[forced]);
+        node = node->kids[forced];
+    }
+    if (node->n_children != 0) return -3;                /* recorded path stops above this tree's leaf */
+    playout_leaf(m, &state, node);
+    return 0;
+}
+
+/* n playouts along recorded paths: tlen[k] moves of playout k, stored back to back in trace.
+ * Returns 0, or -(8 * (k + 1) + c) for the first bad playout k with c = 1..3 (see orc_mcts_playout_forced). */
+int orc_mcts_replay(orc_mcts *m, const orc_board *b, const uint8_t *tlen, const uint8_t *trace, int n,
+                    orc_replay_stats *st)
+{
+    int off = 0;
+    for (int k = 0; k < n; ++k) {
+        m->playout_idx = (uint32_t)k;
+        int rc = orc_mcts_playout_forced(m, b, trace + off, (int)tlen[k], st);
+        if (rc != 0) return -((k + 1) * 8) + rc;        /* rc in -1..-3 */
+        off += (int)tlen[k];
+    }
+    return 0;
 }
 
 orc_mcts *orc_mcts_new(double c_puct, int n_playout, int eval_kind, const orc_net *net,

@@ -23,32 +23,68 @@ typedef struct {
     const float *p[16];
 } orc_net;
 
-static void conv3x3_relu(const float *in, int cin, const float *w, const float *bias,
+/* Textbook cross-correlation with zero padding; per output (co, y, x) the terms are added in the order
+ * ci -> ky -> kx in double.  The loops are arranged pixel-outermost with the output channels innermost over
+ * a [ci][ky][kx][co] copy of the filter (contiguous doubles: vectorisable), and a zero input (about half
+ * of the post-ReLU activations) skips its row of multiply-adds, which leaves every sum unchanged. */
+#if defined(__GNUC__) && defined(__x86_64__)
+__attribute__((target_clones("avx2", "default")))
+#endif
+static void conv3x3_relu(const float *in, int cin, const double *wt, const float *bias,
                          int cout, int H, int W, float *out)
 {
-    /* same sums as the textbook 7-deep loop, reordered so the innermost loop runs over a
-     * contiguous row (vectorisable); accumulation stays in double */
-    double acc[ORC_NET_MAXS];
-    for (int co = 0; co < cout; ++co) {
-        for (int i = 0; i < H * W; ++i) acc[i] = bias[co];
-        for (int ci = 0; ci < cin; ++ci)
-            for (int ky = 0; ky < 3; ++ky)
-                for (int kx = 0; kx < 3; ++kx) {
-                    const double wv = (double)w[((co * cin + ci) * 3 + ky) * 3 + kx];
-                    const int x0 = kx == 0 ? 1 : 0, x1 = kx == 2 ? W - 1 : W;
-                    for (int y = 0; y < H; ++y) {
-                        const int yy = y + ky - 1;
-                        if (yy < 0 || yy >= H) continue;
-                        const float *src = in + (ci * H + yy) * W + (kx - 1);
-                        double *dst = acc + y * W;
-                        for (int x = x0; x < x1; ++x) dst[x] += (double)src[x] * wv;
+    double acc[256];
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x) {
+            for (int co = 0; co < cout; ++co) acc[co] = bias[co];
+            for (int ci = 0; ci < cin; ++ci)
+                for (int ky = 0; ky < 3; ++ky) {
+                    const int yy = y + ky - 1;
+                    if (yy < 0 || yy >= H) continue;
+                    for (int kx = 0; kx < 3; ++kx) {
+                        const int xx = x + kx - 1;
+                        if (xx < 0 || xx >= W) continue;
+                        const double v = (double)in[(ci * H + yy) * W + xx];
+                        if (v == 0.0) continue;
+                        const double *wr = wt + ((size_t)ci * 9 + ky * 3 + kx) * cout;
+                        for (int co = 0; co < cout; ++co) acc[co] += v * wr[co];
                     }
                 }
-        for (int i = 0; i < H * W; ++i) {
-            float v = (float)acc[i];
-            out[co * H * W + i] = v > 0.f ? v : 0.f;
+            for (int co = 0; co < cout; ++co) {
+                float v = (float)acc[co];
+                out[co * H * W + y * W + x] = v > 0.f ? v : 0.f;
+            }
         }
-    }
+}
+
+/* OIHW float filter -> [ci][tap][co] double.  Searches call the net one board at a time, so the
+ * converted filters are kept in a small per-thread cache, validated against a copy of the float
+ * weights on every use (weights may be updated in place by the caller). */
+#define ORC_WCACHE 6
+typedef struct { const float *src; int cin, cout; float *copy; double *wt; } orc_wcache;
+static __thread orc_wcache g_wc[ORC_WCACHE];
+static __thread int g_wc_next;
+
+static const double *conv_filter_t(const float *w, int cin, int cout)
+{
+    const size_t n = (size_t)cin * 9 * cout;
+    for (int i = 0; i < ORC_WCACHE; ++i)
+        if (g_wc[i].src == w && g_wc[i].cin == cin && g_wc[i].cout == cout &&
+            memcmp(g_wc[i].copy, w, n * sizeof(float)) == 0)
+            return g_wc[i].wt;
+    orc_wcache *c = &g_wc[g_wc_next];
+    g_wc_next = (g_wc_next + 1) % ORC_WCACHE;
+    free(c->copy); free(c->wt);
+    c->copy = (float *)malloc(n * sizeof(float));
+    c->wt = (double *)malloc(n * sizeof(double));
+    if (!c->copy || !c->wt) { free(c->copy); free(c->wt); memset(c, 0, sizeof(*c)); return NULL; }
+    memcpy(c->copy, w, n * sizeof(float));
+    c->src = w; c->cin = cin; c->cout = cout;
+    for (int co = 0; co < cout; ++co)
+        for (int ci = 0; ci < cin; ++ci)
+            for (int t = 0; t < 9; ++t)
+                c->wt[((size_t)ci * 9 + t) * cout + co] = (double)w[((size_t)co * cin + ci) * 9 + t];
+    return c->wt;
 }
 
 static void conv1x1_relu(const float *in, int cin, const float *w, const float *bias,
@@ -87,12 +123,15 @@ int orc_net_forward(const orc_net *net, const float *planes, int B, float *logp,
     float *hv = (float *)malloc(sizeof(float) * 2 * S);
     float *lg = (float *)malloc(sizeof(float) * S);
     float v1[64], v2[1];
-    if (!a || !b || !hp || !hv || !lg) return -1;
+    if (net->c1 > 256 || net->c2 > 256 || net->c3 > 256) return -2;
+    const double *w1 = conv_filter_t(net->p[0], 4, net->c1), *w2 = conv_filter_t(net->p[2], net->c1, net->c2),
+                 *w3 = conv_filter_t(net->p[4], net->c2, net->c3);
+    if (!a || !b || !hp || !hv || !lg || !w1 || !w2 || !w3) return -1;
     for (int n = 0; n < B; ++n) {
         const float *x = planes + (size_t)n * 4 * S;
-        conv3x3_relu(x, 4, net->p[0], net->p[1], net->c1, H, W, a);
-        conv3x3_relu(a, net->c1, net->p[2], net->p[3], net->c2, H, W, b);
-        conv3x3_relu(b, net->c2, net->p[4], net->p[5], net->c3, H, W, a);
+        conv3x3_relu(x, 4, w1, net->p[1], net->c1, H, W, a);
+        conv3x3_relu(a, net->c1, w2, net->p[3], net->c2, H, W, b);
+        conv3x3_relu(b, net->c2, w3, net->p[5], net->c3, H, W, a);
         /* policy head (:49-51) */
         conv1x1_relu(a, net->c3, net->p[6], net->p[7], 4, S, hp);
         linear(hp, 4 * S, net->p[8], net->p[9], S, lg);

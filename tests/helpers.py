@@ -49,3 +49,125 @@ def load_golden_weights(name):
     """tests/golden/<name>.npz: 16 arrays in torch state_dict order/layout."""
     z = np.load(os.path.join(GOLDEN, name + ".npz"))
     return [z["p%02d" % i] for i in range(16)]
+
+
+# ---- round-2 fixtures --------------------------------------------------------------------------------------
+def seed0_net_arrays(width, height=None, trunk=(32, 64, 128)):
+    """The reference Net's parameters under torch.manual_seed(0) (policy_value_net_pytorch.py:25-41; SURVEY
+    8d C4/C5: no 9x9 / 15x15 weights ship), rebuilt WITHOUT the reference: the same layers constructed in
+    the same order consume the same generator stream.  tests check them against the checksums that
+    tests/golden/make_golden2.py stored from the live reference (`<tag>_wsum` in mcts2.npz)."""
+    import torch
+    from torch import nn
+    height = width if height is None else height
+    S = width * height
+    c1, c2, c3 = trunk
+    torch.manual_seed(0)
+    layers = [nn.Conv2d(4, c1, kernel_size=3, padding=1), nn.Conv2d(c1, c2, kernel_size=3, padding=1),
+              nn.Conv2d(c2, c3, kernel_size=3, padding=1), nn.Conv2d(c3, 4, kernel_size=1), nn.Linear(4 * S, S),
+              nn.Conv2d(c3, 2, kernel_size=1), nn.Linear(2 * S, 64), nn.Linear(64, 1)]
+    out = []
+    for l in layers:
+        out += [l.weight.detach().numpy().astype(np.float32).copy(), l.bias.detach().numpy().astype(np.float32).copy()]
+    return out
+
+
+def golden_net_arrays(tag, z=None):
+    """Weights of an mcts2.npz configuration: shipped 6x6 / 8x8 fixtures, seed-0 reference Net for 9x9 / 15x15
+    (checked against the stored checksums)."""
+    if tag in ("6_6_4", "8_8_5"):
+        return load_golden_weights("weights_" + tag)
+    w = int(tag.split("_")[0])
+    arrs = seed0_net_arrays(w)
+    if z is None:
+        z = np.load(os.path.join(GOLDEN, "mcts2.npz"))
+    ws = np.array([[a.astype(np.float64).sum(), np.abs(a.astype(np.float64)).sum()] for a in arrs])
+    assert np.allclose(ws, z[tag + "_wsum"], rtol=0, atol=1e-9), "seed-0 Net differs from the reference's (torch version?)"
+    return arrs
+
+
+class Mcts2:
+    """Accessor for tests/golden/mcts2.npz (reference searches with per-playout decision traces)."""
+
+    def __init__(self, tag):
+        self.z = np.load(os.path.join(GOLDEN, "mcts2.npz"))
+        self.tag = tag
+        self.w, _, self.n = [int(x) for x in tag.split("_")]
+        self.S = self.w * self.w
+        self.n_playout = int(self.z[tag + "_n_playout"])
+        self.offsets = self.z[tag + "_offsets"]
+        self.n_pos = len(self.offsets) - 1
+
+    def moves(self, i):
+        return [int(m) for m in self.z[self.tag + "_moves"][self.offsets[i]:self.offsets[i + 1]]]
+
+    def visits(self, s, i):
+        return self.z["%s_visits%d" % (self.tag, s)][i]
+
+    def best_move(self, i):
+        return int(self.z[self.tag + "_move"][i])
+
+    def gap(self, s, i):
+        """smallest (best - second) / max(1, |best|) over the reference's select calls"""
+        return float(self.z["%s_gap%d" % (self.tag, s)][i])
+
+    def margin(self, s, i):
+        return float(self.z["%s_margin%d" % (self.tag, s)][i])
+
+    def trace(self, s, i):
+        """(tlen uint8 [n_playout], moves uint8 flat) of search s (1 or 2) at position i"""
+        to = self.z["%s_troff%d" % (self.tag, s)]
+        return self.z["%s_tlen%d" % (self.tag, s)][i], self.z["%s_trace%d" % (self.tag, s)][to[i]:to[i + 1]]
+
+    def paths(self, s, i):
+        tl, tr = self.trace(s, i)
+        out, o = [], 0
+        for d in tl:
+            out.append([int(x) for x in tr[o:o + int(d)]])
+            o += int(d)
+        return out
+
+    def has_search2(self, i):
+        return bool((self.visits(2, i) >= 0).any())
+
+
+def tv_distance(a, b):
+    a = np.maximum(np.asarray(a, np.float64), 0)
+    b = np.maximum(np.asarray(b, np.float64), 0)
+    return 0.5 * np.abs(a / a.sum() - b / b.sum()).sum()
+
+
+def oracle_arena(orc, net, w, n, az_playout, pure_playout, start_player, n_games, seed, c_puct=5):
+    """The reference arena (train.py:216-276 -> game.py:211-290) on the oracle: MCTSPlayer (net, fresh tree
+    every move, move ~ softmax(log(visits)/1e-3), mcts_alphaZero.py:244-255; off 15x15 the A-13 opening
+    override is skipped) as player 1 vs mcts_pure.MCTSPlayer (most visited child, mcts_pure.py:261-270) as
+    player 2.  Returns winners (1, 2, -1) per game."""
+    rng = np.random.RandomState(seed)
+    winners = []
+    for g in range(n_games):
+        b = orc.Board(w, w, n)
+        b.init_board(start_player)
+        ply = 0
+        while True:
+            if b.current_player == 1:
+                m = orc.MCTS(c_puct, az_playout, orc.EVAL_NET, net=net)
+                acts, probs = m.get_move_probs(b, temp=1e-3)
+                move = int(rng.choice(acts, p=probs))
+            else:
+                m = orc.MCTS(c_puct, pure_playout, orc.EVAL_PURE, salt=seed)
+                m.set_stream(g, 1000 * start_player + ply)
+                move = m.pure_get_move(b)
+            b.do_move(move)
+            ply += 1
+            end, winner = b.game_end()
+            if end:
+                winners.append(winner)
+                break
+    return np.array(winners, np.int8)
+
+
+def binomial_band_ok(k1, n1, k2, n2, sigmas=4.0):
+    """two-sample test of proportions with a pooled, Laplace-smoothed variance (robust at p = 0 or 1)"""
+    p = (k1 + k2 + 1.0) / (n1 + n2 + 2.0)
+    sd = np.sqrt(p * (1 - p) * (1.0 / n1 + 1.0 / n2))
+    return abs(k1 / n1 - k2 / n2) <= sigmas * sd + 1e-12
