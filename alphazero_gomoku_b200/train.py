@@ -27,20 +27,6 @@ DEFAULT_CONF = {"board_width": 15, "board_height": 15, "n_in_row": 5, "learn_rat
                 "game_batch_num": 5000}
 
 
-def equi_data(play_data, board_width, board_height):
-    """train.py:116-135: the 8 dihedral images of every (state, pi, z)."""
-    extend_data = []
-    for state, mcts_porb, winner in play_data:
-        for i in [1, 2, 3, 4]:
-            equi_state = np.array([np.rot90(s, i) for s in state])
-            equi_mcts_prob = np.rot90(np.flipud(mcts_porb.reshape(board_height, board_width)), i)
-            extend_data.append((equi_state, np.flipud(equi_mcts_prob).flatten(), winner))
-            equi_state = np.array([np.fliplr(s) for s in equi_state])
-            equi_mcts_prob = np.fliplr(equi_mcts_prob)
-            extend_data.append((equi_state, np.flipud(equi_mcts_prob).flatten(), winner))
-    return extend_data
-
-
 def shard_games(n_games, rank, world):
     """Games [0, n_games) split over ranks: contiguous, sizes differ by at most one."""
     base, rem = divmod(int(n_games), int(world))
@@ -254,7 +240,16 @@ class TrainPipeline():
         self.last_games = []
 
     def get_equi_data(self, play_data):
-        return equi_data(play_data, self.board_width, self.board_height)
+        """train.py:116-135: [(state, pi, z), ...] -> the 8 dihedral images of every sample, in the reference's
+        order, produced by the device kernel (gz_equi_data) and handed back as float64 arrays."""
+        play_data = list(play_data)
+        if not play_data:
+            return []
+        st, pi, z = self.policy_value_net._engine.equi_data(
+            np.array([d[0] for d in play_data], np.float32), np.array([d[1] for d in play_data], np.float32),
+            np.array([d[2] for d in play_data], np.float32))
+        st, pi = st.astype(np.float64), pi.astype(np.float64)
+        return [(st[i], pi[i], float(z[i])) for i in range(len(z))]
 
     def _selfplay_engine(self, n_slots):
         if self._engine is None or self._engine.G != n_slots:

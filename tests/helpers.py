@@ -90,7 +90,8 @@ class Mcts2:
     """Accessor for tests/golden/mcts2.npz (reference searches with per-playout decision traces)."""
 
     def __init__(self, tag):
-        self.z = np.load(os.path.join(GOLDEN, "mcts2.npz"))
+        with np.load(os.path.join(GOLDEN, "mcts2.npz")) as z:  # read eagerly: NpzFile is not thread-safe
+            self.z = {k: z[k] for k in z.files if k.startswith(tag + "_")}
         self.tag = tag
         self.w, _, self.n = [int(x) for x in tag.split("_")]
         self.S = self.w * self.w
@@ -171,3 +172,46 @@ def binomial_band_ok(k1, n1, k2, n2, sigmas=4.0):
     p = (k1 + k2 + 1.0) / (n1 + n2 + 2.0)
     sd = np.sqrt(p * (1 - p) * (1.0 / n1 + 1.0 / n2))
     return abs(k1 / n1 - k2 / n2) <= sigmas * sd + 1e-12
+
+
+def chi_square_two_sample(a, b, what, min_expected=8.0):
+    """chi-square homogeneity test of two histograms; bins are pooled until both expect >= min_expected"""
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    order = np.argsort(-(a + b))
+    bins, cur = [], np.zeros(2)
+    for i in order:
+        cur += (a[i], b[i])
+        tot = cur.sum()
+        if min(tot * a.sum(), tot * b.sum()) / (a.sum() + b.sum()) >= min_expected:
+            bins.append(cur)
+            cur = np.zeros(2)
+    if cur.sum() > 0:
+        if bins:
+            bins[-1] = bins[-1] + cur
+        else:
+            bins.append(cur)
+    t = np.array(bins)
+    dof = len(t) - 1
+    if dof < 1:
+        return
+    exp = t.sum(axis=1, keepdims=True) * t.sum(axis=0, keepdims=True) / t.sum()
+    chi = ((t - exp) ** 2 / exp).sum()
+    # p ~ 1e-5 bound: chi < dof + 4.3 * sqrt(2 dof) + 12 (Wilson-Hilferty-ish, loose on purpose)
+    assert chi < dof + 4.3 * np.sqrt(2 * dof) + 12, (what, chi, dof, t.tolist())
+    print("%s: chi2 = %.1f at %d dof" % (what, chi, dof))
+
+
+def dihedral_images(state, pi, z, width, height):
+    """Numpy checker for the 8-fold augmentation (reference train.py:116-135, SURVEY A-19), test infrastructure:
+    for k = 1..4 quarter turns, without and then with a left-right mirror, the image T of every state plane, and
+    for pi - which is indexed by raw move id while the planes are stored row-reversed (A-3) - the same T applied
+    between two up-down flips.  Pinned against the live reference's output in tests/golden/equi.npz."""
+    out = []
+    grid = np.asarray(pi).reshape(height, width)[::-1]
+    for k in (1, 2, 3, 4):
+        for mirror in (False, True):
+            def T(a):
+                a = np.rot90(a, k)
+                return a[:, ::-1] if mirror else a
+            out.append((np.array([T(p) for p in state]), T(grid)[::-1].flatten(), z))
+    return out

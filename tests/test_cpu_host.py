@@ -106,7 +106,7 @@ def test_pack_unpack_samples_roundtrip():
 
 def test_equi_data_is_the_dihedral_orbit():
     """train.py:116-135: 8 images; a one-hot pi keeps pointing at the image of the same stone."""
-    from alphazero_gomoku_b200.train import equi_data
+    from helpers import dihedral_images
     w = 6
     rng = np.random.RandomState(1)
     move = 2 * w + 5                      # cell (h=2, w=5)
@@ -114,7 +114,7 @@ def test_equi_data_is_the_dihedral_orbit():
     state[0][w - 1 - move // w, move % w] = 1.0   # stored row-reversed (game.py:116)
     state[1] = (rng.rand(w, w) < 0.3)
     pi = np.zeros(w * w); pi[move] = 1.0
-    out = equi_data([(state, pi, 1.0)], w, w)
+    out = dihedral_images(state, pi, 1.0, w, w)
     assert len(out) == 8
     seen = set()
     for s, p, z in out:
@@ -190,13 +190,13 @@ def test_bench_reference_arm_contract():
 
 
 def test_equi_data_host_vs_reference_golden():
-    """train.equi_data (host mirror of train.py:116-135) against fixtures generated by the live
-    reference's TrainPipeline.get_equi_data (tests/golden/make_golden.py equi)."""
-    from alphazero_gomoku_b200.train import equi_data
+    """The numpy checker tests/helpers.py:dihedral_images against fixtures generated by the live reference's
+    TrainPipeline.get_equi_data (tests/golden/make_golden.py equi); the product path is gz_equi_data (GPU tests)."""
+    from helpers import dihedral_images
     z = np.load(os.path.join(ROOT, "tests", "golden", "equi.npz"))
     for w in (6, 8, 9, 15):
         st, pi, zs = z["w%d_states" % w], z["w%d_pis" % w], z["w%d_zs" % w]
-        out = equi_data([(st[i], pi[i], zs[i]) for i in range(len(zs))], w, w)
+        out = [o for i in range(len(zs)) for o in dihedral_images(st[i], pi[i], zs[i], w, w)]
         assert np.array_equal(np.array([o[0] for o in out]), z["w%d_out_states" % w])
         assert np.array_equal(np.array([o[1] for o in out]), z["w%d_out_pis" % w])
         assert np.array_equal(np.array([o[2] for o in out]), z["w%d_out_zs" % w])

@@ -261,9 +261,9 @@ def test_device_equi_data_vs_reference_golden():
         bp = rng.rand(n, w * w).astype(np.float32)
         bz = rng.choice([-1.0, 0.0, 1.0], size=n).astype(np.float32)
         gs, gp, gz_ = e.equi_data(bs, bp, bz)
-        from alphazero_gomoku_b200.train import equi_data
+        from helpers import dihedral_images
         for i in (0, 1499, 3000):
-            ref = equi_data([(bs[i], bp[i], bz[i])], w, w)
+            ref = dihedral_images(bs[i], bp[i], bz[i], w, w)
             assert np.array_equal(gs[8 * i:8 * i + 8], np.array([r[0] for r in ref]))
             assert np.array_equal(gp[8 * i:8 * i + 8], np.array([r[1] for r in ref]))
             assert (gz_[8 * i:8 * i + 8] == bz[i]).all()
