@@ -1103,3 +1103,4 @@ extern "C" int gz_profile_read(gz_engine *e, double *ms, int64_t *launches, int3
 
 #include "gz_augment.cu"
 #include "gz_train.cu"
+#include "gz_noalloc.cu"

@@ -192,6 +192,15 @@ class Engine:
         self._ck(self.L.gz_net_forward(self._h, _ptr(planes), B, _ptr(probs), _ptr(values)))
         return probs, values
 
+    def net_forward_noalloc(self, planes, probs, values):
+        """gz_net_forward_noalloc: planes [B,4,W,H], probs [B,S], values [B] are caller-owned float32 CUDA tensors;
+        nothing is allocated (static 8 MiB device scratch, B limited accordingly) and nothing is synchronised:
+        the work is queued on the engine stream (sync() before reading)."""
+        for t in (planes, probs, values):
+            if not hasattr(t, "data_ptr"):
+                raise TypeError("net_forward_noalloc takes torch CUDA tensors (device pointers)")
+        self._ck(self.L.gz_net_forward_noalloc(self._h, _ptr(planes), int(planes.shape[0]), _ptr(probs), _ptr(values)))
+
     def debug_net_layers(self, planes):
         """tensor-core path with per-layer activations: dict(act1 [B,S,c1], act2 [B,S,c2],
         act3 [B,S,c3], head [B,6,S], probs [B,S], values [B])."""

@@ -110,6 +110,19 @@ int gz_boards_cells(gz_engine *e, int8_t *out /*[G,S]: 0 empty, 1, 2*/);
  * planes float[B,4,W,H]; probs float[B,S] = exp(log_softmax); values float[B] = tanh.    */
 int gz_net_forward(gz_engine *e, const float *planes, int64_t B, float *probs, float *values);
 
+/* gz_net_forward for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.
+ * Same arithmetic and outputs as gz_net_forward on the fused tcgen05 path (square board, trunk 32/64/128), but the
+ * scratch between its two kernels (the head-activation image, ceil(B / 128) * J * 8192 bytes; 1.5 KB per board at
+ * 8x8) is a file-scope device array of 8 MiB that every GPU loading the library holds until exit, so the call
+ * makes no cudaMalloc / cudaFree / allocating library call.  Limits: planes, probs, values must be DEVICE pointers;
+ * B is rejected (GZ_E_INVALID, gz_last_error names the limit) when its image exceeds 8 MiB - at most 8192 boards
+ * at 6x6, 5376 at 8x8, 3840 at 9x9, 1408 at 15x15; not after device-side training until gz_net_forward /
+ * gz_get_weights has refreshed the inference weights once.  Stream-ordered on the engine stream WITHOUT a trailing
+ * synchronisation: gz_sync() before the outputs are read from elsewhere.  All calls on a device share the array
+ * (the part a call uses is cleared first; it keeps the last call's contents): calls that overlap on the GPU
+ * (several engines or streams) race and must be serialised by the caller.                                  */
+int gz_net_forward_noalloc(gz_engine *e, const float *planes, int64_t B, float *probs, float *values);
 /* Diagnostic for parity tests: runs the tensor-core path and also returns the activations after
  * each ReLU: act1 [B,S,32], act2 [B,S,64], act3 [B,S,128] (cell-major, channel-minor) and
  * head [B,6,S] (the two 1x1 head convs, policy_value_net_pytorch.py:49,53).  Any output may be NULL. */
