@@ -9,7 +9,8 @@ import subprocess
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_PKG)
-LIB_PATH = os.path.join(_PKG, "lib", "libgomoku_b200.so")
+# GZ_LIB_PATH: load another build of the same library (A/B runs of compile-time variants); never a fallback
+LIB_PATH = os.environ.get("GZ_LIB_PATH") or os.path.join(_PKG, "lib", "libgomoku_b200.so")
 CSRC = os.path.join(_PKG, "csrc")
 HEADER = os.path.join(_ROOT, "include", "gomoku_b200.h")
 
@@ -102,6 +103,7 @@ _PROTOS = {
     "gz_selfplay_drain_games": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P, _P, _P, C.POINTER(C.c_int64)]),
     "gz_selfplay_get_stats": (C.c_int, [_P, C.POINTER(GzSelfplayStats), C.c_int32]),
     "gz_selfplay_last": (C.c_int, [_P, _P, _P]),
+    "gz_selfplay_state": (C.c_int, [_P, _P, C.POINTER(C.c_int64)]),
     "gz_pure_search": (C.c_int, [_P, C.c_int32, C.c_uint32]),
     "gz_pure_best_move": (C.c_int, [_P, _P]),
     "gz_rollouts": (C.c_int, [_P, C.c_int32, C.c_uint32, _P, C.POINTER(C.c_int64)]),

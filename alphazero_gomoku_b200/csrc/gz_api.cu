@@ -100,7 +100,6 @@ template <typename T> static int gz_dalloc(gz_engine *e, T **p, size_t n)
     GZ_CUDA(e, cudaMemsetAsync(*p, 0, (n ? n : 1) * sizeof(T), e->stream));
     return GZ_OK;
 }
-#define GZ_TRY(x) do { int _rc = (x); if (_rc != GZ_OK) return _rc; } while (0)
 
 // ---- lifecycle ------------------------------------------------------------------------------
 extern "C" const char *gz_version(void) { return "gomoku_b200 0.1 (sm_100a)"; }
@@ -215,7 +214,7 @@ extern "C" void gz_destroy(gz_engine *e)
     void *ptrs[] = {e->boards, e->meta, e->active, e->pool, e->free_stack, e->free_top, e->root_node,
                     e->root_N, e->root_Q, e->path, e->path_len, e->leaf_state, e->leaf_value, e->leaf_slot,
                     e->leaf_count_pair, e->leaf_planes, e->leaf_board, e->leaf_meta, e->net_probs, e->net_values,
-                    e->act1, e->act2, e->act3, e->stage, e->sp_moves, e->sp_pi, e->sp_game_id, e->sel_moves,
+                    e->act1, e->act2, e->act3, e->stage, e->sp_moves, e->sp_pi, e->sp_game_id, e->sp_fin_flag, e->sp_serial, e->sel_moves,
                     e->sel_probs, e->out_states, e->out_pi, e->out_z, e->out_gid, e->out_ply, e->out_count,
                     e->gout_moves, e->gout_len, e->gout_winner, e->gout_gid, e->gout_count, e->counters,
                     e->roll_results, e->wts.w1, e->wts.w2, e->wts.w3, e->wts.wh, e->wts.wpfc, e->wts.wvfc,
@@ -225,6 +224,14 @@ extern "C" void gz_destroy(gz_engine *e)
     gz_train_free(e);
     for (int i = 0; i < 16; ++i) if (e->wts.raw[i]) cudaFree(e->wts.raw[i]);
     for (int c = 0; c < GZ_PROF_CLASSES; ++c) for (cudaEvent_t ev : e->prof_ev[c]) cudaEventDestroy(ev);
+    if (e->pure_st[0]) {
+        for (int i = 0; i < GZ_PURE_MAXPARTS; ++i) {
+            if (e->pure_st[i]) cudaStreamDestroy(e->pure_st[i]);
+            if (e->pure_hi[i]) cudaStreamDestroy(e->pure_hi[i]);
+            for (int k = 0; k < 4; ++k) if (e->pure_ev[i][k]) cudaEventDestroy(e->pure_ev[i][k]);
+        }
+        if (e->ev_fork) cudaEventDestroy(e->ev_fork);
+    }
     if (e->own_stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -807,6 +814,8 @@ extern "C" int gz_selfplay_begin(gz_engine *e, float temp, int32_t recycle)
         GZ_TRY(gz_dalloc(e, &e->sp_moves, G * S));
         GZ_TRY(gz_dalloc(e, &e->sp_pi, G * S * S));
         GZ_TRY(gz_dalloc(e, &e->sp_game_id, G));
+        GZ_TRY(gz_dalloc(e, &e->sp_fin_flag, G));
+        GZ_TRY(gz_dalloc(e, &e->sp_serial, 1));
         e->out_cap = (int64_t)(G * S);
         GZ_TRY(gz_dalloc(e, &e->out_states, (size_t)e->out_cap * 4 * S));
         GZ_TRY(gz_dalloc(e, &e->out_pi, (size_t)e->out_cap * S));
@@ -833,6 +842,9 @@ extern "C" int gz_selfplay_begin(gz_engine *e, float temp, int32_t recycle)
     for (size_t g = 0; g < G; ++g) ids[g] = (int64_t)(e->cfg.game_id_base + (uint64_t)e->sp_next_serial + g);
     e->sp_next_serial += (int64_t)G;
     e->sp_ids_live = true;
+    const unsigned long long dev_serial = (unsigned long long)e->sp_next_serial; // recycle mode 2 continues from here
+    GZ_CUDA(e, cudaMemcpyAsync(e->sp_serial, &dev_serial, sizeof(dev_serial), cudaMemcpyHostToDevice, e->stream));
+    GZ_CUDA(e, cudaMemsetAsync(e->sp_fin_flag, 0, G * sizeof(int32_t), e->stream));
     GZ_CUDA(e, cudaMemcpyAsync(e->sp_game_id, ids.data(), G * sizeof(int64_t), cudaMemcpyHostToDevice, e->stream));
     GZ_CUDA(e, cudaStreamSynchronize(e->stream));
     GZ_TRY(gzk_boards_reset(e, nullptr));
@@ -843,7 +855,7 @@ extern "C" int gz_selfplay_begin(gz_engine *e, float temp, int32_t recycle)
     e->out_drained = 0;
     e->gout_drained = 0;
     e->sp_temp = temp;
-    e->sp_recycle = recycle ? 1 : 0;
+    e->sp_recycle = recycle == 2 ? 2 : (recycle ? 1 : 0);
     e->sp_begun = true;
     GZ_CUDA(e, cudaStreamSynchronize(e->stream));
     return GZ_OK;
@@ -965,6 +977,20 @@ extern "C" int gz_selfplay_get_stats(gz_engine *e, gz_selfplay_stats *out, int32
     for (int i = 0; i < 3; ++i) out->n_wins[i] = (int64_t)c.wins[i];
     out->max_tree_nodes = (int64_t)c.max_nodes;
     if (reset) GZ_CUDA(e, cudaMemset(e->counters, 0, sizeof(DevCounters)));
+    return GZ_OK;
+}
+
+extern "C" int gz_selfplay_state(gz_engine *e, int64_t *game_ids, int64_t *dropped_samples)
+{
+    if (!e || !e->sp_begun) return GZ_E_INVALID;
+    GZ_CUDA(e, cudaSetDevice(e->cfg.device));
+    GZ_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (game_ids) GZ_CUDA(e, cudaMemcpy(game_ids, e->sp_game_id, (size_t)e->G * sizeof(int64_t), cudaMemcpyDefault));
+    if (dropped_samples) {
+        unsigned long long d = 0;
+        GZ_CUDA(e, cudaMemcpy(&d, &e->counters->dropped, sizeof(d), cudaMemcpyDeviceToHost));
+        *dropped_samples = (int64_t)d;
+    }
     return GZ_OK;
 }
 

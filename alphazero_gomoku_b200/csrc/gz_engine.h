@@ -57,6 +57,7 @@ struct NetWeights {
 };
 
 struct TrainState; // gz_train.cu
+#define GZ_PURE_MAXPARTS 4
 
 struct gz_engine {
     gz_config cfg;
@@ -64,6 +65,10 @@ struct gz_engine {
     int c1, c2, c3;
     cudaStream_t stream;
     bool own_stream;
+    // pure-MCTS search split over parts of the games (gz_rollout.cu), created on first use: per part a stream for the
+    // wave kernels, an urgent one for the rollout kernels, and events (wave done, rollout done, first wave done, part done)
+    cudaStream_t pure_st[GZ_PURE_MAXPARTS], pure_hi[GZ_PURE_MAXPARTS];
+    cudaEvent_t pure_ev[GZ_PURE_MAXPARTS][4], ev_fork;
     std::string err;
     long long launches;
 
@@ -114,6 +119,8 @@ struct gz_engine {
     int32_t *sp_moves;   // [G][S] moves of the game in progress
     float *sp_pi;        // [G][S][S] pi per ply of the game in progress
     int64_t *sp_game_id; // [G]
+    int32_t *sp_fin_flag;           // [G] recycle mode 2: finished this ply, next id pending
+    unsigned long long *sp_serial;  // [1] recycle mode 2: next game serial on the device
     int64_t sp_next_serial; // next unused game serial (ids = game_id_base + serial): never reset
     bool sp_ids_live;       // sp_game_id holds ids of an earlier begin
     int32_t *sel_moves;  // [G] scratch: chosen moves
@@ -189,6 +196,8 @@ struct ProfScope {
             return GZ_E_CUDA;                                                                \
         }                                                                                    \
     } while (0)
+
+#define GZ_TRY(x) do { int _rc = (x); if (_rc != GZ_OK) return _rc; } while (0)
 
 // kernels' launchers (each returns a GZ_* code)
 int gzk_rules_eval(gz_engine *e, const int32_t *d_moves, const int64_t *d_offsets, int64_t n_pos,

@@ -198,7 +198,8 @@ struct SelfplayParams {
     int32_t *sp_moves;
     float *sp_pi;
     int64_t *sp_game_id;
-    int recycle;
+    int recycle;          // 0 idle after a game, 1 next id = id + G, 2 next id = next start serial (selfplay_assign_ids_kernel)
+    int32_t *fin_flag;    // [G] recycle == 2: slot finished a game in this ply and waits for its next id
     int64_t out_cap;
     float *out_states, *out_pi, *out_z;
     int64_t *out_gid;
@@ -317,7 +318,8 @@ __global__ void __launch_bounds__(128) selfplay_advance_kernel(TreeParams p, Sel
         GameMeta z;
         z.n_stones = 0; z.last_move = -1; z.start_player = 0; z.flags = 0;
         sp.meta[g] = z;
-        if (sp.recycle) sp.sp_game_id[g] = gid + (int64_t)p.G;
+        if (sp.recycle == 2) sp.fin_flag[g] = 1;
+        else if (sp.recycle) sp.sp_game_id[g] = gid + (int64_t)p.G;
         else sp.active[g] = 0;
         atomicAdd(&p.ctr->plies, 1ull);
         atomicAdd(&p.ctr->games_finished, 1ull);
@@ -326,12 +328,44 @@ __global__ void __launch_bounds__(128) selfplay_advance_kernel(TreeParams p, Sel
     }
 }
 
+// recycle mode 2 ("serial ids", the continuous collect mode of train.py): the slots that finished a game in this
+// ply get the next game serials in SLOT ORDER (block-wide scan over the flags: deterministic, unlike an atomic
+// counter), so that game ids order the games by when they STARTED.  A consumer that releases finished games in id
+// order then hands out every game exactly once, in start order, however long it took - short games are not
+// over-represented the way they are when the first n games to FINISH are taken.
+__global__ void __launch_bounds__(1024) selfplay_assign_ids_kernel(int32_t *fin_flag, int64_t *game_id,
+                                                                   unsigned long long *serial, int G, uint64_t base)
+{
+    __shared__ unsigned warp_sum[32];
+    __shared__ unsigned long long next;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (threadIdx.x == 0) next = *serial;
+    __syncthreads();
+    for (int g0 = 0; g0 < G; g0 += 1024) {
+        const int g = g0 + (int)threadIdx.x;
+        const bool f = g < G && fin_flag[g] != 0;
+        const unsigned b = __ballot_sync(0xffffffffu, f);
+        if (lane == 0) warp_sum[wid] = __popc(b);
+        __syncthreads();
+        unsigned before = 0, total = 0;
+        for (int w = 0; w < 32; ++w) { before += w < wid ? warp_sum[w] : 0u; total += warp_sum[w]; }
+        if (f) {
+            game_id[g] = (int64_t)(base + next + before + __popc(b & ((1u << lane) - 1u)));
+            fin_flag[g] = 0;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) next += total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *serial = next;
+}
+
 int gzk_selfplay_advance(gz_engine *e)
 {
     SelfplayParams sp;
     sp.boards = e->boards; sp.meta = e->meta; sp.active = e->active; sp.sel_moves = e->sel_moves;
     sp.sel_probs = e->sel_probs; sp.sp_moves = e->sp_moves; sp.sp_pi = e->sp_pi;
-    sp.sp_game_id = e->sp_game_id; sp.recycle = e->sp_recycle; sp.out_cap = e->out_cap;
+    sp.sp_game_id = e->sp_game_id; sp.recycle = e->sp_recycle; sp.fin_flag = e->sp_fin_flag; sp.out_cap = e->out_cap;
     sp.out_states = e->out_states; sp.out_pi = e->out_pi; sp.out_z = e->out_z; sp.out_gid = e->out_gid;
     sp.out_ply = e->out_ply; sp.out_count = e->out_count; sp.gout_cap = e->gout_cap;
     sp.gout_moves = e->gout_moves; sp.gout_len = e->gout_len; sp.gout_winner = e->gout_winner;
@@ -340,6 +374,11 @@ int gzk_selfplay_advance(gz_engine *e)
     ProfScope ps(e, PC_ADVANCE);
     selfplay_advance_kernel<<<gz_warp_blocks(e->G, 4), 128, 0, e->stream>>>(gz_tree_params(e), sp);
     e->launches++;
+    if (e->sp_recycle == 2) {
+        selfplay_assign_ids_kernel<<<1, 1024, 0, e->stream>>>(e->sp_fin_flag, e->sp_game_id, e->sp_serial, e->G,
+                                                              e->cfg.game_id_base);
+        e->launches++;
+    }
     GZ_CUDA(e, cudaGetLastError());
     return GZ_OK;
 }

@@ -34,6 +34,7 @@ struct TreeParams {
     DevCounters *ctr;
     int G, W, H, S, Sp, n_in_row, cap;
     float c_puct;
+    int g0; // first game of the launch (kernels that work on a slice of the games: [g0, G))
 };
 
 __device__ __forceinline__ void warp_argmax(double &s, int &i)
@@ -378,7 +379,8 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
 #pragma unroll
         for (int j = 0; j < NSL; ++j) {
             const int i = lane + 32 * j;
-            rP[j] = rv.P[i]; rN[j] = rv.N[i]; rQ[j] = rv.Q[i]; rC[j] = rv.child[i];
+            if (i < BS) { rP[j] = rv.P[i]; rN[j] = rv.N[i]; rQ[j] = rv.Q[i]; rC[j] = rv.child[i]; }
+            else rP[j] = -1.f; // padding slots are never children: their sectors are not fetched
         }
     }
     // ---- expand (mcts_alphaZero.py:38-45) and link
@@ -493,7 +495,8 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
 #pragma unroll
             for (int j = 0; j < NSL; ++j) {
                 const int i = lane + 32 * j;
-                rP[j] = v.P[i]; rN[j] = v.N[i]; rQ[j] = v.Q[i]; rC[j] = v.child[i];
+                if (i < BS) { rP[j] = v.P[i]; rN[j] = v.N[i]; rQ[j] = v.Q[i]; rC[j] = v.child[i]; }
+                else rP[j] = -1.f;
             }
         }
         {
@@ -694,7 +697,7 @@ static TreeParams gz_tree_params(gz_engine *e)
     p.leaf_count = e->leaf_count; p.leaf_zero = nullptr; p.leaf_planes = e->leaf_planes; p.leaf_board = e->leaf_board;
     p.leaf_meta = e->leaf_meta; p.ctr = e->counters;
     p.G = e->G; p.W = e->W; p.H = e->H; p.S = e->S; p.Sp = e->Sp; p.n_in_row = e->n_in_row;
-    p.cap = e->cap; p.c_puct = e->cfg.c_puct;
+    p.cap = e->cap; p.c_puct = e->cfg.c_puct; p.g0 = 0;
     return p;
 }
 

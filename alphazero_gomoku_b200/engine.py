@@ -62,6 +62,7 @@ class Engine:
         self.n_playout = cfg.n_playout
         self.trunk = tuple(int(t) for t in trunk)
         self.device = cfg.device
+        self.game_id_base = int(game_id_base)
 
     def close(self):
         if getattr(self, "_h", None):
@@ -356,7 +357,9 @@ class Engine:
 
     # ---- self-play -------------------------------------------------------------------------
     def selfplay_begin(self, temp=1.0, recycle=False):
-        self._ck(self.L.gz_selfplay_begin(self._h, float(temp), int(bool(recycle))))
+        """recycle: False = a slot idles after its game, True / 1 = next game id = id + G, 2 = next id = next start
+        serial (ids order the games by when they began; TrainPipeline's continuous mode)."""
+        self._ck(self.L.gz_selfplay_begin(self._h, float(temp), 2 if recycle == 2 else int(bool(recycle))))
 
     def selfplay_step(self, n_plies=1):
         self._ck(self.L.gz_selfplay_step(self._h, int(n_plies)))
@@ -394,6 +397,22 @@ class Engine:
                                                 _ptr(offsets), _ptr(winners), _ptr(gids), C.byref(n)))
         n = n.value
         return [(int(gids[i]), int(winners[i]), moves[offsets[i]:offsets[i + 1]].tolist()) for i in range(n)]
+
+    def selfplay_game_ids(self):
+        """ids of the games in progress, one per slot"""
+        ids = np.zeros(self.G, np.int64)
+        self._ck(self.L.gz_selfplay_state(self._h, _ptr(ids), None))
+        return ids
+
+    def selfplay_first_serial(self):
+        """smallest game serial (id - game_id_base) in flight: right after selfplay_begin, the first of the run"""
+        return int(self.selfplay_game_ids().min()) - self.game_id_base
+
+    def selfplay_dropped(self):
+        """samples lost because the device sample ring was full (0 unless the caller stopped draining)"""
+        d = C.c_int64()
+        self._ck(self.L.gz_selfplay_state(self._h, None, C.byref(d)))
+        return int(d.value)
 
     def selfplay_last(self, moves=None, probs=None):
         moves = np.zeros(self.G, np.int32) if moves is None else moves

@@ -78,6 +78,34 @@ def all_gather_samples(rec, group=None):
     return np.concatenate([o[:c].cpu().numpy() for o, c in zip(out, counts)], axis=0)
 
 
+def all_gather_samples_device(states, pis, zs, group=None):
+    """all_gather_samples for device-resident samples (torch CUDA tensors in, union out, ordered by rank): the
+    counts travel first, then one padded all-gather of [z | pi | state] rows over NCCL; nothing touches the host
+    except the counts."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return states, pis, zs
+    world = dist.get_world_size(group)
+    n, S = int(zs.shape[0]), int(pis.shape[1])
+    dev = zs.device
+    cnt = torch.tensor([n], dtype=torch.int64, device=dev)
+    cnts = torch.zeros(world, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(cnts, cnt, group=group)
+    counts = [int(c) for c in cnts.tolist()]
+    m = max(max(counts), 1)
+    rec = torch.zeros((m, 1 + 5 * S), dtype=torch.float32, device=dev)
+    if n:
+        rec[:n, 0] = zs
+        rec[:n, 1:1 + S] = pis
+        rec[:n, 1 + S:] = states.reshape(n, -1)
+    out = torch.empty((world * m, 1 + 5 * S), dtype=torch.float32, device=dev)  # rank r's rows at [r * m, (r + 1) * m)
+    dist.all_gather_into_tensor(out, rec, group=group)
+    rows = torch.cat([out[r * m:r * m + c] for r, c in enumerate(counts)], dim=0)
+    return (rows[:, 1 + S:].reshape((-1,) + tuple(states.shape[1:])).contiguous(), rows[:, 1:1 + S].contiguous(),
+            rows[:, 0].contiguous())
+
+
 def broadcast_weights(arrays, src=0, group=None):
     """One flat broadcast of the 16 weight tensors (NVLink/NCCL when available)."""
     import torch
@@ -206,10 +234,13 @@ def allreduce_mean(x, group=None):
 
 class TrainPipeline():
     def __init__(self, conf=None, init_model=None, best_model="best_policy.model", seed=0, device_buffer=False,
-                 device=None):
+                 device=None, continuous=False, selfplay_slots=None):
         """device_buffer=True keeps the replay buffer on the device (DeviceReplayBuffer): samples go
         self-play ring -> augmentation -> buffer -> train step without touching the host.
-        device: CUDA ordinal of this process (default: LOCAL_RANK, one process per GPU)."""
+        device: CUDA ordinal of this process (default: LOCAL_RANK, one process per GPU).
+        continuous=True: collect_selfplay_data keeps `selfplay_slots` games in flight ACROSS calls (slots
+        recycle, weight updates are picked up by the games in progress) instead of draining every batch to its
+        last game; see _collect_continuous.  Default: the reference's shape, n_games from empty boards per call."""
         import os
         self.device = int(os.environ.get("LOCAL_RANK", "0")) if device is None else int(device)
         c = dict(DEFAULT_CONF)
@@ -238,6 +269,9 @@ class TrainPipeline():
         self._engine_version = -1
         self._games_played = 0
         self.last_games = []
+        self.continuous = bool(continuous)
+        self.selfplay_slots = selfplay_slots
+        self._cont = None  # continuous mode: {"next": first unreleased game serial, "games": {...}, "chunks": [...]}
 
     def get_equi_data(self, play_data):
         """train.py:116-135: [(state, pi, z), ...] -> the 8 dihedral images of every sample, in the reference's
@@ -299,14 +333,57 @@ class TrainPipeline():
         the buffer receives the reference's items in the reference's order (game, ply, image)."""
         if len(train_data) != 0:
             return self._collect_from_train_data(n_games, train_data)
+        st, pi, z = self._raw_samples(n_games)
+        self.episode_len = int(z.shape[0])
+        self._extend_buffer(st, pi, z)
+        return
+
+    def _raw_samples(self, n_games):
+        """The (state, pi, z) records of n_games finished games in (game, ply) order, before augmentation: numpy
+        arrays, or torch CUDA tensors when device_buffer; batch or continuous mode."""
+        if self.continuous:
+            return self._collect_continuous(n_games)
         if self.device_buffer:
             return self._collect_on_device(n_games)
         e, d = self._play(n_games)
-        st, pi, z = e.equi_data(d["states"], d["pis"], d["zs"])
-        st, pi = st.astype(np.float64), pi.astype(np.float64)
-        self.data_buffer.extend((st[i], pi[i], float(z[i])) for i in range(len(z)))
-        self.episode_len = len(d["zs"])
-        return
+        return d["states"], d["pis"], d["zs"]
+
+    def _extend_buffer(self, st, pi, z):
+        """x8 dihedral images on the device (gz_equi_data), then data_buffer.extend in the reference's order"""
+        if int(z.shape[0]) == 0:
+            return
+        e = self._engine if self._engine is not None else self.policy_value_net._engine
+        st, pi, z = e.equi_data(st, pi, z)
+        if hasattr(st, "data_ptr"):
+            if isinstance(self.data_buffer, deque):
+                self.data_buffer = DeviceReplayBuffer(self.buffer_size, self.board_width, self.board_height, e.device)
+            self.data_buffer.extend(st, pi, z)
+        else:
+            st, pi = st.astype(np.float64), pi.astype(np.float64)
+            self.data_buffer.extend((st[i], pi[i], float(z[i])) for i in range(len(z)))
+
+    def collect_selfplay_data_sharded(self, n_games, group=None):
+        """collect_selfplay_data over several GPUs the way SURVEY 8e lays it out: every rank plays its shard of the
+        n_games (train.shard_games), the raw samples are all-gathered over NCCL on the device (counts, then padded
+        records) and the trainer rank (0) augments the union and extends ITS buffer in (rank, game, ply) order - the
+        order train.py:155 would have produced playing the games one after another.  Needs device_buffer=True."""
+        import torch.distributed as dist
+        world = dist.get_world_size(group) if dist.is_initialized() else 1
+        rank = dist.get_rank(group) if dist.is_initialized() else 0
+        lo, hi = shard_games(n_games, rank, world)
+        st, pi, z = self._raw_samples(hi - lo)
+        import time
+        import torch
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        local_rows = int(z.shape[0])
+        st, pi, z = all_gather_samples_device(st, pi, z, group)
+        torch.cuda.synchronize()
+        self.last_allgather = {"seconds": time.perf_counter() - t0, "local_samples": local_rows,
+                               "union_samples": int(z.shape[0]), "bytes_per_sample": 4 * (1 + 5 * int(pi.shape[1]))}
+        self.episode_len = int(z.shape[0])
+        if rank == 0:
+            self._extend_buffer(st, pi, z)
 
     def _collect_from_train_data(self, n_games, train_data):
         """train.py:137-159, recorded-game branch: the first n_games entries of train_data ([winner,
@@ -330,9 +407,8 @@ class TrainPipeline():
             self.data_buffer.extend((st[i], pi[i], float(z[i])) for i in range(len(z)))
 
     def _collect_on_device(self, n_games):
-        """collect_selfplay_data with every array on the device: the finished games' samples are drained
-        into torch tensors, augmented by gz_equi_data and appended to the DeviceReplayBuffer in the
-        engine's output order (games in finishing order, plies ascending inside a game)."""
+        """Batch mode with every array on the device: the finished games' samples are drained into torch tensors
+        in the engine's output order (games in finishing order, plies ascending inside a game)."""
         import torch
         e = self._selfplay_engine(int(n_games))
         e.selfplay_begin(temp=float(self.temp), recycle=False)
@@ -350,11 +426,77 @@ class TrainPipeline():
         d = e.selfplay_drain(n, bufs)
         self.last_games = e.selfplay_drain_games()
         self._games_played += len(self.last_games)
-        if isinstance(self.data_buffer, deque):
-            self.data_buffer = DeviceReplayBuffer(self.buffer_size, self.board_width, self.board_height, e.device)
-        st, pi, z = e.equi_data(d["states"], d["pis"], d["zs"])
-        self.data_buffer.extend(st, pi, z)
-        self.episode_len = int(d["zs"].shape[0])
+        return d["states"], d["pis"], d["zs"]
+
+    def _collect_continuous(self, n_games):
+        """collect_selfplay_data without the tail: train.py:137-159 plays its n games one after another, the batch
+        mode here plays them side by side and waits for the longest - at the end of every batch most slots idle.
+        Here the engine's slots never idle (gz_selfplay_begin(recycle=2) once; a slot that finishes starts the next
+        game at once, with the weights current at that moment) and games in flight survive across calls and across
+        weight updates.  Every game carries a START serial; a call hands out the n games with the next n serials,
+        in that order, as soon as all of them have finished - every game exactly once, in the order the reference's
+        loop would have started them, whatever its length: taking the first n games to FINISH instead would
+        over-represent short games.  Finished games with later serials wait (on the device when device_buffer) for
+        a later call.  Returns the released games' raw samples in (serial, ply) order."""
+        n_games = int(n_games)
+        slots = int(self.selfplay_slots or n_games)
+        e = self._selfplay_engine(slots)
+        S = self.board_width * self.board_height
+        if self._cont is None or self._cont["engine"] is not e:
+            e.selfplay_begin(temp=float(self.temp), recycle=2)
+            first = e.selfplay_first_serial()
+            self._cont = {"engine": e, "next": first, "done": {}, "chunks": [], "plies": 0}
+        c = self._cont
+        lo, hi = c["next"], c["next"] + n_games
+        on_device = self.device_buffer
+        if on_device:
+            import torch
+            dev = torch.device("cuda", e.device)
+
+        def have():
+            return sum(1 for g in range(lo, hi) if g in c["done"])
+        while have() < n_games:
+            e.selfplay_step(1)
+            c["plies"] += 1
+            n = int(e.selfplay_pending()[0])
+            if n == 0:
+                continue
+            if on_device:
+                bufs = {"states": torch.empty((n, 4, self.board_width, self.board_height), dtype=torch.float32, device=dev),
+                        "pis": torch.empty((n, S), dtype=torch.float32, device=dev),
+                        "zs": torch.empty((n,), dtype=torch.float32, device=dev),
+                        "game_ids": torch.empty((n,), dtype=torch.int64, device=dev),
+                        "plies": torch.empty((n,), dtype=torch.int32, device=dev)}
+                d = e.selfplay_drain(n, bufs)
+            else:
+                d = e.selfplay_drain(n)
+            c["chunks"].append(d)
+            for gid, winner, moves in e.selfplay_drain_games():
+                c["done"][gid - e.game_id_base] = (gid, winner, moves)
+            if e.selfplay_stats()["pool_overflows"] or e.selfplay_dropped():
+                raise MemoryError("continuous self-play: device sample ring or tree pool exhausted")
+        # release serials [lo, hi) in order; later games stay pending
+        self.last_games = [c["done"].pop(g) for g in range(lo, hi)]
+        c["next"] = hi
+        for gid, winner, moves in self.last_games:
+            _logger.warning("{'steps':[%s],'winner':%d}" % (",".join(map(str, moves)), winner))  # game.py:411
+        self._games_played += n_games
+        lo_id, hi_id = lo + e.game_id_base, hi + e.game_id_base
+        if on_device:
+            cat = {k: torch.cat([d[k] for d in c["chunks"]]) for k in c["chunks"][0]}
+            sel = (cat["game_ids"] >= lo_id) & (cat["game_ids"] < hi_id)
+            keep = ~sel
+            c["chunks"] = [{k: v[keep] for k, v in cat.items()}] if bool(keep.any()) else []
+            rel = {k: v[sel] for k, v in cat.items()}
+            order = torch.argsort(rel["game_ids"] * 1024 + rel["plies"].to(torch.int64))
+            return rel["states"][order].contiguous(), rel["pis"][order].contiguous(), rel["zs"][order].contiguous()
+        else:
+            cat = {k: np.concatenate([d[k] for d in c["chunks"]]) for k in c["chunks"][0]}
+            sel = (cat["game_ids"] >= lo_id) & (cat["game_ids"] < hi_id)
+            c["chunks"] = [{k: v[~sel] for k, v in cat.items()}] if (~sel).any() else []
+            rel = {k: v[sel] for k, v in cat.items()}
+            order = np.lexsort((rel["plies"], rel["game_ids"]))
+            return rel["states"][order], rel["pis"][order], rel["zs"][order]
 
     def _minibatch(self, k):
         """(states, pis, zs, zs as numpy): random.sample of the buffer (train.py:167)."""

@@ -161,43 +161,69 @@ class ClockSampler:
 
 
 # ---- CPU legs (oracle port of the reference's CPU path) ----------------------------------------
-def cpu_selfplay_worker(arrs, width, n_in_row, n_playout, n_plies, out, idx, seed, budget_s=None):
-    """n_plies of single-game self-play on the oracle port; with budget_s, stop after the first ply that
-    ends past that many seconds (at least 2 plies)."""
-    from oracle import orc
-    t_start = time.perf_counter()
-    net = orc.Net(width, width, arrs)
-    b = orc.Board(width, width, n_in_row)
-    b.init_board(0)
-    m = orc.MCTS(5, n_playout, orc.EVAL_NET, net=net)
-    rng = np.random.RandomState(seed)
-    done = 0
-    for ply in range(n_plies):
-        if budget_s is not None and ply >= 2 and time.perf_counter() - t_start >= budget_s:
-            break
-        acts, vis, _, _ = m.search(b)  # the C call releases the GIL
-        done += n_playout
+class CpuSelfplayWorker:
+    """One single-threaded self-play game on the oracle port that LIVES ACROSS STEPS: board, tree (subtree reuse,
+    mcts_alphaZero.py:183-192) and rng persist, a finished game is followed by a new one (game.py:360-416), so a
+    step of the CPU arm is what a step of the GPU arm is - one more ply of games that are already under way."""
+
+    def __init__(self, arrs, width, n_in_row, n_playout, seed):
+        from oracle import orc
+        self.orc = orc
+        self.net = orc.Net(width, width, arrs)
+        self.b = orc.Board(width, width, n_in_row)
+        self.b.init_board(0)
+        self.n_playout = n_playout
+        self.m = orc.MCTS(5, n_playout, orc.EVAL_NET, net=self.net)
+        self.rng = np.random.RandomState(seed)
+        self.playouts = 0
+        self.plies = 0
+
+    def ply(self, n_playout=None):
+        n = self.n_playout if n_playout is None else n_playout
+        acts, vis, _, _ = self.m.search(self.b, n)  # the C call releases the GIL
+        self.playouts += n
+        self.plies += 1
         p = vis / vis.sum()
-        mv = int(acts[rng.choice(len(acts), p=p)])
-        m.update_with_move(mv)
-        b.do_move(mv)
-        if b.game_end()[0]:
-            b.init_board(0)
-            m.update_with_move(-1)
-    out[idx] = done
+        mv = int(acts[self.rng.choice(len(acts), p=p)])
+        self.m.update_with_move(mv)
+        self.b.do_move(mv)
+        if self.b.game_end()[0]:
+            self.b.init_board(0)
+            self.m.update_with_move(-1)
+
+    def prefill(self, n_plies):
+        """untimed: bring the game to a mixed phase with cheap searches (the GPU arm's --prefill-plies)"""
+        for _ in range(n_plies):
+            self.ply(16)
+        self.playouts = 0
+        self.plies = 0
+
+
+def run_workers(workers, n_plies=1, budget_s=None):
+    """every worker plays n_plies on its own thread; with budget_s a worker stops after the ply that passes it"""
+    def work(w):
+        t0 = time.perf_counter()
+        for k in range(n_plies):
+            if budget_s is not None and k >= 2 and time.perf_counter() - t0 >= budget_s:
+                break
+            w.ply()
+    ts = [threading.Thread(target=work, args=(w,)) for w in workers]
+    for t in ts: t.start()
+    for t in ts: t.join()
 
 
 def cpu_baseline(arrs, width, n_in_row, n_playout, n_plies=64, budget_s=12.0):
-    """Single-thread oracle port (reference = single-threaded Python) on a bounded sample: self-play plies
-    from the empty board until budget_s seconds of CPU work are done (n_plies at most)."""
-    out = [0]
+    """Single-thread oracle port (reference = single-threaded Python) on a bounded sample: self-play plies of one
+    game that is already under way (6 cheap prefill plies), until budget_s seconds of CPU work are done."""
+    w = CpuSelfplayWorker(arrs, width, n_in_row, n_playout, 0)
+    w.prefill(6)
     t0 = time.perf_counter()
-    cpu_selfplay_worker(arrs, width, n_in_row, n_playout, n_plies, out, 0, 0, budget_s)
+    run_workers([w], n_plies, budget_s)
     dt = time.perf_counter() - t0
-    return {"value": out[0] / dt, "unit": UNIT, "cores": 1, "kind": "port",
-            "sample": "oracle/ C port of mcts_alphaZero.MCTS + Net forward, 1 thread, single-game self-play from the "
-                      "empty %dx%d board (a new game when one ends), %d plies x %d playouts, %.1f s"
-                      % (width, width, out[0] // n_playout, n_playout, dt)}
+    return {"value": w.playouts / dt, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": "oracle/ C port of mcts_alphaZero.MCTS + Net forward, 1 thread, single-game self-play on the "
+                      "%dx%d board continuing a game in progress (tree reuse, a new game when one ends), %d plies x %d "
+                      "playouts, %.1f s" % (width, width, w.plies, n_playout, dt)}
 
 
 def run_reference(args):
@@ -208,33 +234,30 @@ def run_reference(args):
     orc.build()
     arrs, wname = load_weights(args.board)
     threads = os.cpu_count() or 1
-    plies_per_step = 1
-
-    def step():
-        out = [0] * threads
-        ts = [threading.Thread(target=cpu_selfplay_worker,
-                               args=(arrs, args.board, args.n_in_row, args.playouts, plies_per_step, out, i, i))
-              for i in range(threads)]
-        for t in ts: t.start()
-        for t in ts: t.join()
-        return sum(out)
-
+    workers = [CpuSelfplayWorker(arrs, args.board, args.n_in_row, args.playouts, i) for i in range(threads)]
+    # untimed: spread the games over the phases of a game, as the GPU arm's prefill does
+    ts = [threading.Thread(target=w.prefill, args=((5 * i) % 17,)) for i, w in enumerate(workers)]
+    for t in ts: t.start()
+    for t in ts: t.join()
     for _ in range(args.warmup):
-        step()
+        run_workers(workers, 1)
+    for w in workers:
+        w.playouts = 0
     t0 = time.perf_counter()
-    total = 0
     for _ in range(args.steps):
-        total += step()
+        run_workers(workers, 1)
     dt = time.perf_counter() - t0
+    total = sum(w.playouts for w in workers)
     val = total / dt
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * dt / max(args.steps, 1),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(args, wname, games=args.games),
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
-                             "sample": "bounded sample of the same workload: each step = %d host threads (one game each) x 1 ply "
-                                       "x %d playouts (oracle/ C port of the reference's CPU path; the Python reference "
-                                       "cannot travel to this box)"
+                             "sample": "bounded sample of the same workload: %d host threads, one game each, carried from "
+                                       "step to step (board + tree with subtree reuse; games spread over 0-16 plies by an "
+                                       "untimed prefill); each step = 1 ply x %d playouts per game (oracle/ C port of the "
+                                       "reference's CPU path; the Python reference cannot travel to this box)"
                                        % (threads, args.playouts)},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -328,7 +351,12 @@ def run_ours(args):
     ctr = eng.counters(reset=True)
 
     # ---- end to end: host weights in, host results out, every step -------------------------------
+    # N > 1: the step does what a training update does around self-play (reference train.py:137-159 + :306-320 on
+    # several GPUs): rank 0's new weights go host -> device -> NCCL broadcast -> gz_set_weights on every rank, the
+    # step runs, and the step's finished samples are all-gathered over NCCL (counts, then padded packed records),
+    # so that every rank - the trainer among them - holds the union in (rank, game, ply) order.
     host_w = [torch.from_numpy(a.copy()).pin_memory() for a in arrs]
+    flat_host = torch.from_numpy(np.concatenate([a.reshape(-1) for a in arrs])).pin_memory()
     mv = torch.zeros(args.games, dtype=torch.int32).pin_memory()
     pr = torch.zeros((args.games, args.board * args.board), dtype=torch.float32).pin_memory()
     h2d = sum(a.numel() * 4 for a in host_w)
@@ -343,18 +371,71 @@ def run_ours(args):
               "game_ids": torch.zeros(cap, dtype=torch.int64).pin_memory(),
               "plies": torch.zeros(cap, dtype=torch.int32).pin_memory()}
     drain_bufs = {k: v.numpy() for k, v in pinned.items()}
+    coll = None
+    if world > 1:
+        rec_w = 4 + 5 * S_  # packed record: game id (2 floats), ply, z, pi[S], state[4S]  (train.pack_samples)
+        dev_bufs = {"states": torch.zeros((cap, 4, args.board, args.board), dtype=torch.float32, device=dev),
+                    "pis": torch.zeros((cap, S_), dtype=torch.float32, device=dev),
+                    "zs": torch.zeros(cap, dtype=torch.float32, device=dev),
+                    "game_ids": torch.zeros(cap, dtype=torch.int64, device=dev),
+                    "plies": torch.zeros(cap, dtype=torch.int32, device=dev)}
+        rec = torch.zeros((cap, rec_w), dtype=torch.float32, device=dev)
+        gathered = torch.zeros((world * cap, rec_w), dtype=torch.float32, device=dev)
+        cnt = torch.zeros(1, dtype=torch.int64, device=dev)
+        cnts = torch.zeros(world, dtype=torch.int64, device=dev)
+        ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.steps)]
+        coll = {"bytes_broadcast": int(flat.numel() * 4), "bytes_allgather": 0}
     barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        eng.set_weights([a.numpy() for a in host_w])          # H2D: the step's inputs (weights)
+    for it in range(args.steps):
+        if world == 1:
+            eng.set_weights([a.numpy() for a in host_w])          # H2D: the step's inputs (weights)
+        else:
+            with torch.cuda.stream(stream):
+                ev[it][0].record(stream)
+                if rank == 0:
+                    flat.copy_(flat_host, non_blocking=True)      # H2D on the trainer rank
+                dist.broadcast(flat, src=0)                       # NCCL over NVLink
+                ev[it][1].record(stream)
+            stream.synchronize()
+            eng.set_weights(list(torch.split(flat, sizes)))
         eng.selfplay_step(1)
         eng.selfplay_last(mv.numpy(), pr.numpy())             # D2H: (move, move_probs) of the step
-        d = eng.selfplay_drain(max_samples=cap, bufs=drain_bufs)  # D2H: samples of games that finished
-        d2h_total += mv.numel() * 4 + pr.numel() * 4 + sum(v.nbytes for v in d.values())
+        if world == 1:
+            d = eng.selfplay_drain(max_samples=cap, bufs=drain_bufs)  # D2H: samples of games that finished
+            d2h_total += mv.numel() * 4 + pr.numel() * 4 + sum(v.nbytes for v in d.values())
+        else:
+            d = eng.selfplay_drain(max_samples=cap, bufs=dev_bufs)    # stays on the device for the all-gather
+            n = int(d["zs"].shape[0])
+            with torch.cuda.stream(stream):
+                rec[:n, 0] = (d["game_ids"] >> 20).to(torch.float32)
+                rec[:n, 1] = (d["game_ids"] & ((1 << 20) - 1)).to(torch.float32)
+                rec[:n, 2] = d["plies"].to(torch.float32)
+                rec[:n, 3] = d["zs"]
+                rec[:n, 4:4 + S_] = d["pis"]
+                rec[:n, 4 + S_:] = d["states"].reshape(n, -1)
+                cnt[0] = n
+                ev[it][2].record(stream)
+                dist.all_gather_into_tensor(cnts, cnt)
+                m = int(cnts.max().item())                        # the padded length every rank sends
+                out = gathered[:world * max(m, 1)]                # rank r's rows at [r * m, (r + 1) * m)
+                dist.all_gather_into_tensor(out, rec[:max(m, 1)])
+                ev[it][3].record(stream)
+            coll["bytes_allgather"] += world * m * rec_w * 4
+            # D2H of the step's result: this rank's moves / probabilities and its own finished samples' targets
+            zs_host = d["zs"].cpu()
+            d2h_total += mv.numel() * 4 + pr.numel() * 4 + zs_host.numel() * 4
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     barrier()
+    if coll is not None:
+        coll["broadcast_ms_per_step"] = sum(e[0].elapsed_time(e[1]) for e in ev) / max(args.steps, 1)
+        coll["allgather_ms_per_step"] = sum(e[2].elapsed_time(e[3]) for e in ev) / max(args.steps, 1)
+        coll["bytes_allgather"] //= max(args.steps, 1)
+        coll["what"] = ("per step inside the e2e region: weights host -> rank 0 device -> dist.broadcast -> gz_set_weights on "
+                        "every rank; after the step the finished samples (packed records) dist.all_gather_into_tensor'ed, "
+                        "padded to the largest rank's count; times from CUDA events on the engine stream")
     stats2 = eng.selfplay_stats(reset=False)
     ctr2 = eng.counters(reset=True)
 
@@ -463,11 +544,15 @@ def run_ours(args):
                     "d2h_bytes_per_step": d2h_total // max(args.steps, 1),
                     "ms_per_step": e2e_ms_max / max(args.steps, 1),
                     "net_evals_per_playout": float(ctr2["leaf_evals"]) / max(float(ctr2["playouts"]), 1.0),
-                    "what": "per step: gz_set_weights from pinned host arrays, gz_selfplay_step(1), "
-                            "gz_selfplay_last + gz_selfplay_drain into pinned host buffers; these steps follow the "
+                    "what": ("per step: gz_set_weights from pinned host arrays, gz_selfplay_step(1), "
+                             "gz_selfplay_last + gz_selfplay_drain into pinned host buffers; " if world == 1 else
+                             "per step: weights pinned host -> rank 0 -> NCCL broadcast -> gz_set_weights, gz_selfplay_step(1), "
+                             "gz_selfplay_last into pinned host buffers, finished samples drained on the device and NCCL "
+                             "all-gathered (see collectives); ") + "these steps follow the "
                             "device-timed ones in the same games (net_evals_per_playout says how many playouts "
                             "needed the net: terminal leaves do not)"},
             "gpu_launches": int(tot_launch),
+            "collectives": coll,
             "clocks": clocks,
             "roofline": roof,
             "net": {"impl": ("tcgen05 fused trunk (fp16 hi/lo split, 3 MMA passes, fp32 accumulate in TMEM) + tcgen05 FC heads (same split)"
@@ -497,6 +582,115 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+# ---- BASELINE config C5: the train.py loop on N GPUs -------------------------------------------------
+def run_c5(args):
+    """collect self-play data -> policy update, 9x9 five-in-a-row, n_playout 600 (conf/train_config.yaml:20), batch 512,
+    <= 5 epochs, one process per GPU (reference train.py:137-159, :161-214, :306-320).
+      --c5-mode gather : every rank plays its shard, NCCL all-gather of the samples, rank 0 runs policy_update on the
+                         union, NCCL broadcast of the new weights (the reference's single trainer)
+      --c5-mode dp     : every rank keeps its samples, policy_update_dp (gradient all-reduce), no weight traffic
+    Self-play is the continuous mode (slots never idle; --c5-batch = the reference-shaped batches)."""
+    import torch
+    import torch.distributed as dist
+    from alphazero_gomoku_b200.train import TrainPipeline, broadcast_weights
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    board, playouts = (9, 600) if args.board == 8 and args.playouts == 400 else (args.board, args.playouts)
+    games = args.games if args.games != 16384 else 4096
+    conf = {"board_width": board, "board_height": board, "n_in_row": 5, "n_playout": playouts,
+            "buffer_size": 1 << 20, "batch_size": 512, "epochs": 5}
+    tp = TrainPipeline(conf, seed=args.seed, device_buffer=True, device=local, continuous=not args.c5_batch,
+                       selfplay_slots=games)
+    tp.broadcast_initial_weights()
+    t_play, t_upd, t_bc, t_ag, n_games, n_plies, ag_bytes = [], [], [], [], 0, 0, 0
+    loss = ent = float("nan")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    for it in range(args.steps + args.warmup):
+        barrier()
+        t0 = time.perf_counter()
+        if args.c5_mode == "gather":
+            tp.collect_selfplay_data_sharded(games * world)
+        else:
+            tp.collect_selfplay_data(games)
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        barrier()  # rank skew of the self-play phase is not update time
+        t1b = time.perf_counter()
+        bc = 0.0
+        if args.c5_mode == "gather":
+            if rank == 0 and len(tp.data_buffer) > tp.batch_size:
+                loss, ent = tp.policy_update()
+            w = tp.policy_value_net.get_policy_param()
+            torch.cuda.synchronize()
+            tb = time.perf_counter()
+            w = broadcast_weights(w, src=0)
+            if rank != 0:
+                tp.policy_value_net.set_policy_param(w)
+            torch.cuda.synchronize()
+            bc = time.perf_counter() - tb
+        else:
+            loss, ent = tp.policy_update_dp() if world > 1 else tp.policy_update()
+            tp.policy_value_net.get_policy_param()
+        torch.cuda.synchronize()
+        t2 = time.perf_counter()
+        if it < args.warmup:
+            continue
+        t_play.append(t1 - t0); t_upd.append(t2 - t1b); t_bc.append(bc)
+        if args.c5_mode == "gather":
+            t_ag.append(tp.last_allgather["seconds"])
+            ag_bytes += tp.last_allgather["union_samples"] * tp.last_allgather["bytes_per_sample"]
+        n_games += len(tp.last_games)
+        n_plies += sum(len(m) for _, _, m in tp.last_games)
+    stat = torch.tensor([sum(t_play), sum(t_upd), float(n_games), float(n_plies), sum(t_bc), sum(t_ag)],
+                        dtype=torch.float64, device=dev)
+    if world > 1:
+        mx = stat.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(stat, op=dist.ReduceOp.SUM)
+        t_p, t_u, t_b, t_a = float(mx[0]), float(mx[1]), float(mx[4]), float(mx[5])
+        flat = torch.from_numpy(np.concatenate([x.ravel() for x in tp.policy_value_net.get_policy_param()])).to(dev)
+        ref = flat.clone()
+        dist.broadcast(ref, 0)
+        same = torch.tensor([float(torch.equal(flat, ref))], device=dev)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        same = bool(same.item() == 1.0)
+    else:
+        t_p, t_u, t_b, t_a, same = float(stat[0]), float(stat[1]), float(stat[4]), float(stat[5]), True
+    if rank == 0:
+        g, pl = float(stat[2]), float(stat[3])
+        k = max(args.steps, 1)
+        line = {"metric": "selfplay_games_per_hour", "value": g / (t_p + t_u) * 3600.0, "unit": "games/h", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 * (t_p + t_u) / k,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32 (fp16x2-split tensor-core operands in self-play, fp32 train step)", "data": "synthetic",
+                "config": {"workload": "BASELINE config C5: train.py loop %dx%d five-in-a-row, n_playout %d, %d games per GPU "
+                                       "per iteration, batch 512, <= 5 epochs; a step = collect + update" % (board, board, playouts, games),
+                           "mode": args.c5_mode, "selfplay": "batch" if args.c5_batch else "continuous",
+                           "weights": "torch default init, seed %d" % args.seed},
+                "games_per_iteration": g / k, "mean_game_len": pl / max(g, 1),
+                "selfplay_s_per_iter": t_p / k, "update_s_per_iter": t_u / k,
+                "games_per_hour_selfplay_only": g / t_p * 3600.0,
+                "playouts_per_sec_selfplay": pl * playouts / t_p,
+                "collectives": {"allgather_s_per_iter": t_a / k, "allgather_bytes_per_iter": ag_bytes // k if ag_bytes else 0,
+                                "broadcast_s_per_iter": t_b / k,
+                                "what": "gather: samples all-gathered on the device inside selfplay_s, weights broadcast inside "
+                                        "update_s (incl. the host staging of the 16 arrays); dp: one gradient all-reduce per epoch inside update_s"},
+                "loss": loss, "entropy": ent, "weights_identical_across_ranks": same, "lr_multiplier": tp.lr_multiplier}
+        _JSON_LINE.append(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -522,6 +716,10 @@ def main():
                          "and report games/hour; 0 disables")
     ap.add_argument("--prof-stride", type=int, default=16,
                     help="CUDA-event pairs around every N-th launch of each kernel class inside the timed region")
+    ap.add_argument("--config", default="c3", choices=["c3", "c5"],
+                    help="c3 (default): the self-play step of BASELINE configs[2]; c5: the train.py loop (collect + update) at 9x9")
+    ap.add_argument("--c5-mode", default="gather", choices=["gather", "dp"])
+    ap.add_argument("--c5-batch", action="store_true", help="c5: reference-shaped self-play batches instead of the continuous mode")
     args = ap.parse_args()
     # stdout carries exactly ONE JSON line (the driver parses it): libraries that print to fd 1 (NCCL's
     # "NCCL version ..." banner, for one) are sent to stderr for the duration of the run
@@ -531,6 +729,8 @@ def main():
     try:
         if args.impl == "reference":
             run_reference(args)
+        elif args.config == "c5":
+            run_c5(args)
         else:
             run_ours(args)
     finally:

@@ -176,7 +176,11 @@ typedef struct {
 } gz_selfplay_stats;
 
 /* Start (or restart) self-play in every slot.  recycle = 1: a slot that finishes a game
- * immediately starts another (throughput mode); 0: it goes idle (collect n = G games). */
+ * immediately starts another with game id = id + G (throughput mode); 2: the same, but the next id is the next
+ * game START serial (slots that finish in one ply are numbered in slot order), so ids order the games by when
+ * they began - the continuous collect mode of train.py releases finished games in id order; 0: the slot goes idle
+ * (collect n = G games).  Game ids (which key the exploration-noise streams) never repeat on an engine: a later
+ * begin continues after the largest id handed out.                                                     */
 int gz_selfplay_begin(gz_engine *e, float temp, int32_t recycle);
 /* Play n_plies moves in every active slot (each = n_playout waves + move choice + record). */
 int gz_selfplay_step(gz_engine *e, int32_t n_plies);
@@ -194,6 +198,10 @@ int gz_selfplay_drain_games(gz_engine *e, int64_t max_games, int64_t max_moves, 
                             int64_t *offsets, int8_t *winners, int64_t *game_ids,
                             int64_t *n_games_out);
 int gz_selfplay_get_stats(gz_engine *e, gz_selfplay_stats *out, int32_t reset);
+/* Bookkeeping of the running self-play: game_ids[G] (or NULL) = id of the game in progress in every slot (the
+ * reference has no ids: they are this build's handle on "which start_self_play call of train.py:146 a sample
+ * came from"); *dropped_samples (or NULL) = samples lost because the device ring was full (must stay 0: drain). */
+int gz_selfplay_state(gz_engine *e, int64_t *game_ids, int64_t *dropped_samples);
 /* What MCTSPlayer.get_action(board, temp, return_prob=1) returned in the last ply of the last
  * gz_selfplay_step: moves int32[G] (-2 = idle slot) and move_probs float[G,S]
  * (mcts_alphaZero.py:257-260).                                                             */

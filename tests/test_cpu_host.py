@@ -132,7 +132,8 @@ import numpy as np
 import torch
 import torch.distributed as dist
 sys.path.insert(0, %(root)r)
-from alphazero_gomoku_b200.train import all_gather_samples, allreduce_mean, broadcast_weights, pack_samples, shard_games
+from alphazero_gomoku_b200.train import (all_gather_samples, all_gather_samples_device, allreduce_mean, broadcast_weights,
+                                         pack_samples, shard_games)
 rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 dist.init_process_group("gloo", rank=rank, world_size=world)
 # every rank "plays" its shard of 11 games; game g yields (g %% 4) + 1 samples tagged with g
@@ -150,6 +151,16 @@ allrec = all_gather_samples(rec)
 want = [(g, k) for g in range(11) for k in range(g %% 4 + 1)]
 got = [(int(r[1]), int(r[2])) for r in allrec]
 assert got == want, (got, want)            # union ordered (rank, game, ply) == data_buffer.extend order
+# the tensor-resident variant (NCCL on the GPU box, gloo here): same union, same order, ragged counts incl. zero
+zs = torch.tensor([100.0 * g + k for g, k in rows])
+st2, pi2, z2 = all_gather_samples_device(torch.from_numpy(states), torch.from_numpy(pis), zs)
+assert z2.tolist() == [100.0 * g + k for g, k in want]
+assert st2.shape == (len(want), 4, 3, 3) and [int(x.flatten().argmax()) for x in st2[:, 0]] == [g %% S for g, _ in want]
+assert [int(x.argmax()) for x in pi2] == [k %% S for _, k in want]
+empty = rank == 1
+e_st, e_pi, e_z = all_gather_samples_device(torch.from_numpy(states[:0] if empty else states),
+                                           torch.from_numpy(pis[:0] if empty else pis), zs[:0] if empty else zs)
+assert e_z.shape[0] == len([1 for g, k in want if g < shard_games(11, 0, world)[1]])
 ws = [np.full((3, 2), 7.0 + i, np.float32) if rank == 0 else np.zeros((3, 2), np.float32) for i in range(16)]
 out = broadcast_weights(ws, src=0)
 assert all(float(o[0, 0]) == 7.0 + i for i, o in enumerate(out))

@@ -307,3 +307,50 @@ def test_start_from_train_data_vs_reference_golden():
     tp.collect_selfplay_data(2, train_data=games)  # games = the 6x6 records
     assert tp.episode_len == 13 and len(tp.data_buffer) == 8 * 13
     assert tp.data_buffer[0][0].shape == (4, 6, 6) and abs(tp.data_buffer[0][1].sum() - (0.99999 + 35e-6)) < 1e-6
+
+
+@pytest.mark.parametrize("device_buffer", [False, True])
+def test_continuous_collect_matches_batch_mode(device_buffer):
+    """TrainPipeline(continuous=True): slots never idle, games in flight survive across collect_selfplay_data calls,
+    and a call hands out the games with the next n START serials - every game once, in start order, so short games
+    are not over-represented.  Checked against the reference-shaped batch mode on the same weights: the game-length
+    histograms agree (two-sample chi-square), serials are released consecutively, the buffer receives 8 images per
+    recorded ply, and later calls need fewer plies than the first because they find games already in progress."""
+    from helpers import chi_square_two_sample
+    from alphazero_gomoku_b200.train import TrainPipeline
+    conf = {"board_width": 6, "board_height": 6, "n_in_row": 4, "n_playout": 40, "buffer_size": 200000}
+    n, calls = 128, 4
+    model = os.path.join(GOLDEN, "weights_6_6_4.npz")
+    arrs = load_golden_weights("weights_6_6_4")
+
+    def lengths(tp):
+        out, plies_per_call = [], []
+        for k in range(calls):
+            before = tp._cont["plies"] if tp._cont else 0
+            tp.collect_selfplay_data(n)
+            assert len(tp.last_games) == n
+            out += [len(m) for _, _, m in tp.last_games]
+            assert tp.episode_len == sum(len(m) for _, _, m in tp.last_games)
+            if tp._cont:
+                plies_per_call.append(tp._cont["plies"] - before)
+                ser = [gid - tp._engine.game_id_base for gid, _, _ in tp.last_games]
+                assert ser == list(range(ser[0], ser[0] + n)) and (k == 0 or ser[0] == prev_end)
+                prev_end = ser[-1] + 1
+        assert len(tp.data_buffer) == 8 * sum(out)
+        return np.array(out), plies_per_call
+
+    tp_b = TrainPipeline(conf, seed=3, device_buffer=device_buffer)
+    tp_b.policy_value_net.set_policy_param(arrs)
+    len_b, _ = lengths(tp_b)
+    tp_c = TrainPipeline(conf, seed=4, device_buffer=device_buffer, continuous=True)
+    tp_c.policy_value_net.set_policy_param(arrs)
+    len_c, plies = lengths(tp_c)
+    hist = lambda a: np.bincount(a, minlength=37).astype(np.float64)
+    chi_square_two_sample(hist(len_b), hist(len_c), "game lengths, batch vs continuous")
+    assert abs(len_b.mean() - len_c.mean()) < 4 * np.sqrt(len_b.var() / len(len_b) + len_c.var() / len(len_c)) + 1e-9
+    assert max(plies[1:]) < plies[0], plies  # games were already in progress
+    # taking the first n games to FINISH would be biased: the continuous mode's first call is not shorter on average
+    first_call = len_c[:n]
+    assert first_call.mean() > len_b.mean() - 4 * np.sqrt(len_b.var() / n)
+    print("batch mean length %.2f, continuous %.2f (first call %.2f); plies stepped per call %s"
+          % (len_b.mean(), len_c.mean(), first_call.mean(), plies))

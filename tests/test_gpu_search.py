@@ -19,14 +19,14 @@ def _engine(w, h, n, **kw):
     return Engine(width=w, height=h, n_in_row=n, **kw)
 
 
-def _random_positions(rng, w, n, G, max_plies):
+def _random_positions(rng, w, n, G, max_plies, min_plies=0):
     from oracle import orc
     boards, lists = [], []
     while len(boards) < G:
         b = orc.Board(w, w, n)
         b.init_board(0)
         mv = []
-        for _ in range(int(rng.randint(0, max_plies + 1))):
+        for _ in range(int(rng.randint(min_plies, max_plies + 1))):
             av = b.availables
             m = av[rng.randint(len(av))]
             b.do_move(m)
@@ -256,10 +256,11 @@ def test_fused_wave_kernel_matches_split_kernels(w, n, G, P):
 
 def test_rollouts_bit_exact_vs_oracle():
     from oracle import orc
-    for (w, n) in [(6, 4), (8, 5), (15, 5)]:
+    for (w, n) in [(6, 4), (8, 5), (15, 5), (9, 5), (7, 3), (5, 4), (8, 4), (11, 5)]:
         rng = np.random.RandomState(w)
         G, R, seed, sid = 24, 16, 0x1234567890ABCDEF, 7
-        boards, lists = _random_positions(rng, w, n, G, max_plies=w * w // 3)
+        # (an empty board narrower than 6 has no candidate box, game.py:41: see test_gpu_golden2)
+        boards, lists = _random_positions(rng, w, n, G, max_plies=w * w // 3, min_plies=1 if w < 6 else 0)
         e = _engine(w, w, n, n_games=G, seed=seed, game_id_base=100)
         for g, mv in enumerate(lists):
             e.boards_set(g, mv)
@@ -289,12 +290,12 @@ def test_rollout_distribution_vs_reference_golden():
         e.close()
 
 
-@pytest.mark.parametrize("w,n,P", [(6, 4, 300), (8, 5, 200)])
+@pytest.mark.parametrize("w,n,P", [(6, 4, 300), (8, 5, 200), (9, 5, 150), (15, 5, 60), (7, 3, 120), (5, 4, 100), (11, 5, 80)])
 def test_pure_mcts_bit_exact_vs_oracle(w, n, P):
     from oracle import orc
     rng = np.random.RandomState(3)
     G, seed, sid = 16, 42, 5
-    boards, lists = _random_positions(rng, w, n, G, max_plies=10)
+    boards, lists = _random_positions(rng, w, n, G, max_plies=10, min_plies=1 if w < 6 else 0)
     e = _engine(w, w, n, n_games=G, n_playout=P, seed=seed, game_id_base=0)
     for g, mv in enumerate(lists):
         e.boards_set(g, mv)
