@@ -80,8 +80,10 @@ _PROTOS = {
     "gz_boards_cells": (C.c_int, [_P, _P]),
     "gz_net_forward": (C.c_int, [_P, _P, C.c_int64, _P, _P]),
     "gz_net_forward_noalloc": (C.c_int, [_P, _P, C.c_int64, _P, _P]),
+    "gz_debug_hash_evaluator": (C.c_int, [_P, C.c_int32, C.c_uint64]),
     "gz_debug_net_layers": (C.c_int, [_P, _P, C.c_int64, _P, _P, _P, _P, _P, _P]),
     "gz_search": (C.c_int, [_P, C.c_int32]),
+    "gz_search_vl": (C.c_int, [_P, C.c_int32, C.c_int32, C.POINTER(C.c_int32)]),
     "gz_search_select": (C.c_int, [_P, _P, _P, _P, _P]),
     "gz_search_expand_backup": (C.c_int, [_P, _P, _P]),
     "gz_search_paths": (C.c_int, [_P, _P, _P]),

@@ -219,7 +219,9 @@ extern "C" void gz_destroy(gz_engine *e)
                     e->gout_moves, e->gout_len, e->gout_winner, e->gout_gid, e->gout_count, e->counters,
                     e->roll_results, e->wts.w1, e->wts.w2, e->wts.w3, e->wts.wh, e->wts.wpfc, e->wts.wvfc,
                     e->wts.bias, e->wts.tc_img, e->wts.tc_fcimg, e->tc_head, e->tc_dbg,
-                    e->wts.tcw_img1, e->wts.tcw_img2, e->wts.tcw_img3, e->tcw_a0, e->tcw_act1, e->tcw_act2, e->tcw_dbg};
+                    e->wts.tcw_img1, e->wts.tcw_img2, e->wts.tcw_img3, e->tcw_a0, e->tcw_act1, e->tcw_act2, e->tcw_dbg,
+                    e->vl_path, e->vl_path_len, e->vl_leaf_state, e->vl_leaf_value, e->vl_leaf_slot, e->vl_leaf_board,
+                    e->vl_keff, e->vl_remaining, e->vl_planes, e->vl_probs, e->vl_values, e->vl_count};
     for (void *p : ptrs) if (p) cudaFree(p);
     gz_train_free(e);
     for (int i = 0; i < 16; ++i) if (e->wts.raw[i]) cudaFree(e->wts.raw[i]);
@@ -391,9 +393,80 @@ extern "C" int gz_get_weights(gz_engine *e, float *const ptrs[16])
     return GZ_OK;
 }
 
+// ---- diagnostic evaluator (parity tests of the tree kernels) -------------------------------------------------------
+// The integer-hash evaluator of oracle/orc_mcts.c:orc_hash_eval computed on the device from the leaf planes (own /
+// opponent stones, colour plane; start_player 0 assumed: an even stone count means player 1 is to move), so that the
+// FUSED search paths (gz_search, gz_search_vl) can be compared with the oracle bit for bit - the real net differs
+// from the oracle's by ~1e-6, which flips near-ties.  Off unless gz_debug_hash_evaluator switches it on.
+__device__ __forceinline__ uint64_t gz_splitmix64(uint64_t x)
+{
+    x += 0x9E3779B97F4A7C15ull;
+    uint64_t z = x;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+__global__ void __launch_bounds__(128) hash_eval_kernel(const float *planes, const int32_t *count, long long maxB, int W,
+                                                        int S, uint64_t salt, float *probs, float *values)
+{
+    const int lane = threadIdx.x & 31;
+    const long long b = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
+    const long long n = count ? min((long long)*count, maxB) : maxB;
+    if (b >= n) return;
+    const float *pl = planes + b * 4 * S;
+    const int cur = pl[3 * S] > 0.5f ? 1 : 2; // plane 3 is all ones iff the stone count is even
+    uint64_t key = 0ull;
+    for (int mv = lane; mv < S; mv += 32) {
+        const int idx = (W - 1 - mv / W) * W + mv % W; // current_state is stored row-reversed (game.py:116)
+        const int st = pl[idx] > 0.5f ? cur : (pl[S + idx] > 0.5f ? 3 - cur : 0);
+        if (st) key ^= gz_splitmix64(salt + (uint64_t)(mv * 2 + (st - 1)) + 1ull);
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) key ^= __shfl_xor_sync(0xffffffffu, key, off);
+    key ^= gz_splitmix64(salt + 1000ull + (uint64_t)cur);
+    uint32_t wsum = 0u;
+    for (int mv = lane; mv < S; mv += 32) {
+        const int idx = (W - 1 - mv / W) * W + mv % W;
+        if (pl[idx] > 0.5f || pl[S + idx] > 0.5f) continue;
+        const uint32_t t = (uint32_t)(gz_splitmix64(key + (uint64_t)mv + 1ull) >> 56) + 1u;
+        wsum += t * t * t;
+    }
+    wsum = __reduce_add_sync(0xffffffffu, wsum);
+    for (int mv = lane; mv < S; mv += 32) {
+        const int idx = (W - 1 - mv / W) * W + mv % W;
+        float pr = 0.f;
+        if (!(pl[idx] > 0.5f || pl[S + idx] > 0.5f)) {
+            const uint32_t t = (uint32_t)(gz_splitmix64(key + (uint64_t)mv + 1ull) >> 56) + 1u;
+            pr = __fdiv_rn((float)(t * t * t), (float)wsum);
+        }
+        probs[b * S + mv] = pr;
+    }
+    if (lane == 0) {
+        const int vi = (int)(gz_splitmix64(key ^ 0x5555555555555555ull) % 2001ull) - 1000;
+        values[b] = __fdiv_rn((float)vi, 1000.0f);
+    }
+}
+
+extern "C" int gz_debug_hash_evaluator(gz_engine *e, int32_t on, uint64_t salt)
+{
+    if (!e) return GZ_E_INVALID;
+    e->dbg_hash_on = on != 0;
+    e->dbg_hash_salt = salt;
+    return GZ_OK;
+}
+
 int gzk_net_forward(gz_engine *e, const float *d_planes, const int32_t *d_count, int64_t maxB,
                     float *d_probs, float *d_values)
 {
+    if (e->dbg_hash_on) {
+        if (maxB <= 0) return GZ_OK;
+        hash_eval_kernel<<<(unsigned)((maxB + 3) / 4), 128, 0, e->stream>>>(d_planes, d_count, (long long)maxB, e->W, e->S,
+                                                                            e->dbg_hash_salt, d_probs, d_values);
+        e->launches++;
+        GZ_CUDA(e, cudaGetLastError());
+        return GZ_OK;
+    }
     if (!e->wts.loaded) { e->err = "gz_set_weights has not been called"; return GZ_E_NOWEIGHTS; }
     GZ_TRY(gz_train_flush(e)); // weights trained on the device since the last forward
     // net_impl: 0 = tcgen05 path (fused kernel for the reference trunk 32/64/128, layer-wise kernels of
@@ -651,7 +724,7 @@ static int gz_waves(gz_engine *e, int n)
 extern "C" int gz_search(gz_engine *e, int32_t n_playout)
 {
     if (!e || n_playout < 0) return GZ_E_INVALID;
-    if (!e->wts.loaded) { e->err = "gz_set_weights has not been called"; return GZ_E_NOWEIGHTS; }
+    if (!e->wts.loaded && !e->dbg_hash_on) { e->err = "gz_set_weights has not been called"; return GZ_E_NOWEIGHTS; }
     if (e->W != e->H) { e->err = "the net needs a square board"; return GZ_E_INVALID; }
     GZ_CUDA(e, cudaSetDevice(e->cfg.device));
     GZ_TRY(gz_waves(e, n_playout));
@@ -1130,3 +1203,4 @@ extern "C" int gz_profile_read(gz_engine *e, double *ms, int64_t *launches, int3
 #include "gz_augment.cu"
 #include "gz_train.cu"
 #include "gz_noalloc.cu"
+#include "gz_vl.cu"

@@ -141,6 +141,16 @@ struct gz_engine {
     int64_t *gout_gid;   // [gout_cap]
     unsigned long long *gout_count; // [1]
     int64_t gout_drained;
+    bool dbg_hash_on;       // diagnostic: the oracle's integer-hash evaluator instead of the net (gz_debug_hash_evaluator)
+    uint64_t dbg_hash_salt;
+    // several leaves in flight per game (gz_vl.cu), allocated on first use for K = vl_K
+    int vl_K;
+    uint32_t *vl_path;
+    int32_t *vl_path_len, *vl_leaf_slot, *vl_keff, *vl_remaining, *vl_count;
+    int8_t *vl_leaf_state;
+    double *vl_leaf_value;
+    GameBoard *vl_leaf_board;
+    float *vl_planes, *vl_probs, *vl_values;
     DevCounters *counters;
     TrainState *tr;      // device train step state (master weights, Adam moments), created on first use
     // rollouts

@@ -202,6 +202,10 @@ class Engine:
                 raise TypeError("net_forward_noalloc takes torch CUDA tensors (device pointers)")
         self._ck(self.L.gz_net_forward_noalloc(self._h, _ptr(planes), int(planes.shape[0]), _ptr(probs), _ptr(values)))
 
+    def debug_hash_evaluator(self, on=True, salt=0):
+        """diagnostic: the oracle's integer-hash evaluator replaces the net inside the fused searches"""
+        self._ck(self.L.gz_debug_hash_evaluator(self._h, int(bool(on)), int(salt)))
+
     def debug_net_layers(self, planes):
         """tensor-core path with per-layer activations: dict(act1 [B,S,c1], act2 [B,S,c2],
         act3 [B,S,c3], head [B,6,S], probs [B,S], values [B])."""
@@ -217,8 +221,17 @@ class Engine:
         return out
 
     # ---- search ----------------------------------------------------------------------------
-    def search(self, n_playout=None):
-        self._ck(self.L.gz_search(self._h, int(self.n_playout if n_playout is None else n_playout)))
+    def search(self, n_playout=None, leaves_in_flight=1):
+        """n_playout playouts in every active game.  leaves_in_flight = K > 1: up to K leaves of a game per wave
+        (virtual loss, gz_search_vl) - faster for few games, not the reference's sequential search; returns the
+        number of kernel chains launched."""
+        n = int(self.n_playout if n_playout is None else n_playout)
+        if int(leaves_in_flight) <= 1:
+            self._ck(self.L.gz_search(self._h, n))
+            return n
+        waves = C.c_int32()
+        self._ck(self.L.gz_search_vl(self._h, n, int(leaves_in_flight), C.byref(waves)))
+        return int(waves.value)
 
     def search_select(self, want_cells=True):
         G, S = self.G, self.S

@@ -57,7 +57,11 @@ def check_pool(owner, engine):
 class MCTS(object):
     """mcts_alphaZero.py:95-192 over a one-slot device tree."""
 
-    def __init__(self, policy_value_fn, c_puct=5, n_playout=10000):
+    def __init__(self, policy_value_fn, c_puct=5, n_playout=10000, leaves_in_flight=1):
+        """leaves_in_flight = K > 1 (not in the reference): up to K leaves per kernel chain with virtual loss
+        (gz_search_vl) - about 3x lower latency for a single game at K = 8, but no longer the reference's sequential
+        search (visit distributions ~0.04 total variation away at 400 playouts).  Default 1 = the reference."""
+        self.leaves_in_flight = int(leaves_in_flight)
         self._policy = policy_value_fn
         self._c_puct = c_puct
         self._n_playout = int(n_playout)
@@ -92,7 +96,7 @@ class MCTS(object):
         e = self._ensure_engine(state)
         self._sync_board(e, state)
         if self._net is not None:
-            e.search(self._n_playout)
+            e.search(self._n_playout, leaves_in_flight=self.leaves_in_flight)
         else:
             for _ in range(self._n_playout):
                 self._playout_external(e, state)
@@ -154,8 +158,8 @@ def _board_from_cells(template, cells, player, planes=None):
 class MCTSPlayer(object):
     """AI player based on MCTS (mcts_alphaZero.py:198-265)"""
 
-    def __init__(self, policy_value_function, c_puct=5, n_playout=2000, is_selfplay=0):
-        self.mcts = MCTS(policy_value_function, c_puct, n_playout)
+    def __init__(self, policy_value_function, c_puct=5, n_playout=2000, is_selfplay=0, leaves_in_flight=1):
+        self.mcts = MCTS(policy_value_function, c_puct, n_playout, leaves_in_flight=leaves_in_flight)
         self._is_selfplay = is_selfplay
 
     def set_player_ind(self, p):

@@ -375,6 +375,8 @@ class TrainPipeline():
         import time
         import torch
         torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier(group)  # ranks finish their shards at different times: that wait is self-play, not all-gather
         t0 = time.perf_counter()
         local_rows = int(z.shape[0])
         st, pi, z = all_gather_samples_device(st, pi, z, group)
@@ -617,7 +619,7 @@ class TrainPipeline():
         self.policy_value_net.save_model('./current_policy.model')
 
 
-def arena_play(engine, n_playout, pure_playouts, start_players, temp=1e-3, search_salt=0):
+def arena_play(engine, n_playout, pure_playouts, start_players, temp=1e-3, search_salt=0, leaves_in_flight=1):
     """Batched Game.start_play (game.py:211-290) of MCTSPlayer (player 1, net-guided, is_selfplay=0)
     against mcts_pure.MCTSPlayer (player 2, rollouts) in every slot of `engine` at once.
 
@@ -646,7 +648,7 @@ def arena_play(engine, n_playout, pure_playouts, start_players, temp=1e-3, searc
             engine.set_active(mask)
             engine.update_with_move(np.where(mask, -1, -2).astype(np.int32))  # fresh trees for the movers
             if who == 1:
-                engine.search(n_playout)
+                engine.search(n_playout, leaves_in_flight=leaves_in_flight)
                 mv, _ = engine.root_select_move(temp=temp, selfplay=False)
                 if engine.width == 15 and engine.height == 15:  # mcts_alphaZero.py:251-253
                     first = mask & (st["n_stones"] == 0)

@@ -123,6 +123,10 @@ int gz_net_forward(gz_engine *e, const float *planes, int64_t B, float *probs, f
  * (the part a call uses is cleared first; it keeps the last call's contents): calls that overlap on the GPU
  * (several engines or streams) race and must be serialised by the caller.                                  */
 int gz_net_forward_noalloc(gz_engine *e, const float *planes, int64_t B, float *probs, float *values);
+/* Diagnostic for parity tests: on != 0 replaces the net inside gz_search / gz_search_vl / gz_selfplay_step by the
+ * integer-hash evaluator of oracle/orc_mcts.c:orc_hash_eval computed on the device from the leaf planes (positions
+ * with start_player 0), so the fused search paths can be compared with the oracle bit for bit.  Off by default. */
+int gz_debug_hash_evaluator(gz_engine *e, int32_t on, uint64_t salt);
 /* Diagnostic for parity tests: runs the tensor-core path and also returns the activations after
  * each ReLU: act1 [B,S,32], act2 [B,S,64], act3 [B,S,128] (cell-major, channel-minor) and
  * head [B,6,S] (the two 1x1 head convs, policy_value_net_pytorch.py:49,53).  Any output may be NULL. */
@@ -133,6 +137,13 @@ int gz_debug_net_layers(gz_engine *e, const float *planes, int64_t B, float *act
  * gz_search runs n_playout waves; each wave = one playout in every active game
  * (select -> net on the gathered leaves -> expand + backup).                             */
 int gz_search(gz_engine *e, int32_t n_playout);
+/* gz_search with up to K (1..16) leaves of a game in flight per wave (virtual loss): a single game or a small arena
+ * fills a leaf batch K times larger per kernel chain.  The reference's loop (mcts_alphaZero.py:161-163) is strictly
+ * sequential; K = 1 reproduces it (and gz_search) exactly, K > 1 picks descents 2..K of a wave without the results of
+ * the earlier ones (each counted as a virtual loss while in flight) - deterministic, specified in
+ * oracle/orc_mcts.c:orc_mcts_search_vl, but outside the TV <= 0.02 tier (0.057 mean at K = 8, 400 playouts).
+ * Every game still gets exactly n_playout playouts; *waves_out (or NULL) = kernel chains launched.          */
+int gz_search_vl(gz_engine *e, int32_t n_playout, int32_t K, int32_t *waves_out);
 /* Same wave split in two so that a caller-supplied evaluator (the reference's
  * policy_value_fn protocol, mcts_alphaZero.py:98-107) can sit in the middle:
  * select fills leaf_* (each [G]; leaf_state 0 = needs evaluation, 1 = terminal, 2 = game

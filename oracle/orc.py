@@ -64,6 +64,7 @@ def lib():
                                       C.c_void_p, C.c_void_p]
         L.orc_mcts_replay.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orc_replay_stats_init.argtypes = [C.c_void_p]
+        L.orc_mcts_search_vl.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.orc_mcts_root_visits.argtypes = [C.c_void_p]
         L.orc_mcts_root_q.argtypes = [C.c_void_p]
         L.orc_mcts_root_q.restype = C.c_double
@@ -227,6 +228,14 @@ class MCTS:
         probs = np.exp(x - np.max(x))
         probs /= np.sum(probs)
         return tuple(int(a) for a in acts), probs
+
+    def search_vl(self, board, n_playout, k):
+        """n_playout playouts with up to k leaves in flight per wave (orc_mcts_search_vl: the build's own virtual-loss
+        specification, not a reference behaviour).  Returns (acts, visits, Q, P, waves)."""
+        waves = C.c_int()
+        rc = lib().orc_mcts_search_vl(self.h, C.addressof(board.c), int(n_playout), int(k), C.byref(waves))
+        assert rc == 0
+        return self.root_children() + (waves.value,)
 
     def replay(self, board, tlen, trace):
         """Decision-level replay of a recorded search (orc_mcts_replay): tlen uint8 [n_playout] = depth of

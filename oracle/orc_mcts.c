@@ -30,6 +30,7 @@ typedef struct orc_node {
     int n_visits;
     double Q, u, P;
     int p_f32;               /* prior is np.float32 (AlphaZero) vs float64 (pure) */
+    int vl, taken;           /* virtual-loss mode only (orc_mcts_search_vl): in-flight paths through / ending at this node */
 } orc_node;
 
 typedef struct {
@@ -361,6 +362,76 @@ int orc_mcts_search(orc_mcts *m, const orc_board *b, int n_playout, int *acts, i
         if (prior) prior[i] = r->kids[i]->P;
     }
     return r->n_children;
+}
+
+/* ---- several leaves in flight per search (virtual loss) ----------------------------------------------------------
+ * NOT in the reference (its loop mcts_alphaZero.py:161-163 is strictly sequential); this is the build's own
+ * specification of the K-leaves-per-wave mode of the CUDA engine (gz_search_vl), restated on the pointer tree so that
+ * the kernels can be checked bit for bit.  A wave: up to K descents from the root, one after another; descent j scores a
+ * child as if every earlier descent of this wave that passed through it had already come back as a LOSS for the player
+ * choosing there: n_eff = n + c, q_eff = c running-mean updates of Q with -1 (the reference's own update rule :64-65),
+ * N_parent = the parent's visits + the paths through the parent; only the first ORC_VL_DEPTH levels of a path carry
+ * virtual losses.  A descent that ends at a non-terminal leaf an earlier descent of the wave already holds ends the
+ * wave early (that leaf is about to be expanded).  Then the leaves are evaluated, expanded and backed up IN ORDER with
+ * the reference's arithmetic - the statistics never contain a virtual loss.  K = 1 is the reference's loop. */
+#define ORC_VL_DEPTH 32
+#define ORC_VL_MAXK 16
+
+static double vl_score(const orc_node *c, double c_puct, double np_eff)
+{
+    double cp = c->p_f32 ? (double)((float)c_puct * (float)c->P) : c_puct * c->P;
+    double q = c->Q;
+    for (int t = 0; t < c->vl; ++t) q += 1.0 * (-1.0 - q) / (double)(c->n_visits + t + 1);
+    return q + cp * sqrt(np_eff) / (double)(1 + c->n_visits + c->vl);
+}
+
+int orc_mcts_search_vl(orc_mcts *m, const orc_board *b, int n_playout, int K, int *waves_out)
+{
+    if (K < 1 || K > ORC_VL_MAXK) return -1;
+    int done = 0, waves = 0;
+    orc_node *path[ORC_VL_MAXK][ORC_MAXS + 1];
+    int plen[ORC_VL_MAXK];
+    orc_board leafb[ORC_VL_MAXK];
+    while (done < n_playout) {
+        int kmax = n_playout - done < K ? n_playout - done : K, keff = 0;
+        for (int j = 0; j < kmax; ++j) {
+            orc_board st = *b;
+            orc_node *node = m->root;
+            int d = 0;
+            path[j][0] = node;
+            while (node->n_children != 0) {
+                double np_eff = (double)(node->n_visits + node->vl);
+                int best = 0;
+                double bv = vl_score(node->kids[0], m->c_puct, np_eff);
+                for (int i = 1; i < node->n_children; ++i) {
+                    double v = vl_score(node->kids[i], m->c_puct, np_eff);
+                    if (v > bv) { bv = v; best = i; }
+                }
+                orc_board_do_move(&st, node->acts[best]);
+                node = node->kids[best];
+                path[j][++d] = node;
+            }
+            int winner, end = orc_board_game_end(&st, &winner);
+            if (!end && node->taken) break;              /* an earlier descent of this wave holds this leaf */
+            for (int i = 0; i <= d && i <= ORC_VL_DEPTH; ++i) path[j][i]->vl++;   /* node at depth i = edge i - 1 */
+            if (!end) node->taken = 1;
+            plen[j] = d;
+            leafb[j] = st;
+            keff = j + 1;
+        }
+        for (int j = 0; j < keff; ++j) {
+            for (int i = 0; i <= plen[j] && i <= ORC_VL_DEPTH; ++i) path[j][i]->vl--;
+            path[j][plen[j]]->taken = 0;
+        }
+        for (int j = 0; j < keff; ++j) {
+            m->playout_idx = (uint32_t)(done + j);
+            playout_leaf(m, &leafb[j], path[j][plen[j]]);
+        }
+        done += keff;
+        ++waves;
+    }
+    if (waves_out) *waves_out = waves;
+    return 0;
 }
 
 int orc_mcts_root_visits(const orc_mcts *m) { return m->root->n_visits; }

@@ -1,0 +1,146 @@
+"""Several leaves in flight per game (virtual loss, gz_search_vl; north_star subsystem 1, opt-in).
+
+The reference's search is sequential (mcts_alphaZero.py:161-163), so there is no reference behaviour for K > 1; what
+is pinned is (1) K = 1 is today's search bit for bit, (2) for every K the kernels implement the build's own
+specification - restated on the oracle's pointer tree, oracle/orc_mcts.c:orc_mcts_search_vl - bit for bit under the
+shared integer-hash evaluator (visit counts AND float64 Q of every root child, over two searches with tree reuse),
+(3) every game gets exactly n_playout playouts, deterministically, and (4) how far the K > 1 search is from the
+reference's visit counts is MEASURED and bounded loosely: it is outside the TV <= 0.02 tier and documented as such."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from helpers import Mcts2, golden_net_arrays, tv_distance
+
+pytestmark = pytest.mark.gpu
+
+
+def _engine(w, n, **kw):
+    from alphazero_gomoku_b200 import Engine
+    return Engine(width=w, height=w, n_in_row=n, **kw)
+
+
+def _positions(rng, w, n, G, max_plies):
+    from oracle import orc
+    boards, lists = [], []
+    while len(boards) < G:
+        b = orc.Board(w, w, n)
+        b.init_board(0)
+        mv = []
+        for _ in range(int(rng.randint(0, max_plies + 1))):
+            av = b.availables
+            m = av[rng.randint(len(av))]
+            b.do_move(m)
+            mv.append(m)
+            if b.game_end()[0]:
+                break
+        if not b.game_end()[0]:
+            boards.append(b)
+            lists.append(mv)
+    return boards, lists
+
+
+def _search_vl(e, n, k):
+    waves = C.c_int32()
+    e._ck(e.L.gz_search_vl(e._h, int(n), int(k), C.byref(waves)))
+    return waves.value
+
+
+@pytest.mark.parametrize("w,n,G,P", [(8, 5, 40, 200), (6, 4, 24, 150), (9, 5, 12, 90), (15, 5, 6, 60)])
+def test_k1_is_the_sequential_search(w, n, G, P):
+    """gz_search_vl(K = 1) == gz_search: same trees (visits and float64 Q), fused hash evaluator on both."""
+    rng = np.random.RandomState(w)
+    _, lists = _positions(rng, w, n, G, w * w // 3)
+    res = []
+    for mode in (0, 1):
+        e = _engine(w, n, n_games=G, n_playout=P)
+        e.debug_hash_evaluator(True, salt=77)
+        for g, mv in enumerate(lists):
+            e.boards_set(g, mv)
+        for rounds in (P, P // 2):
+            if mode == 0:
+                e.search(rounds)
+            else:
+                _search_vl(e, rounds, 1)
+        res.append(e.root_visits(want_q=True))
+        e.close()
+    for a, b in zip(res[0], res[1]):
+        assert np.array_equal(a, b)
+    assert (res[0][2] == P + P // 2).all()
+
+
+@pytest.mark.parametrize("K", [2, 4, 8, 16])
+@pytest.mark.parametrize("w,n,G,P", [(8, 5, 32, 200), (6, 4, 24, 130), (9, 5, 10, 100), (15, 5, 5, 70)])
+def test_vl_kernels_match_the_oracle_specification(w, n, G, P, K):
+    """Device K-leaf search vs orc_mcts_search_vl under the shared hash evaluator: identical visit counts and
+    bit-identical float64 Q for every root child, identical root N, over two searches with subtree reuse."""
+    from oracle import orc
+    rng = np.random.RandomState(100 + w + K)
+    boards, lists = _positions(rng, w, n, G, w * w // 3)
+    salt = 900 + K
+    e = _engine(w, n, n_games=G, n_playout=P)
+    e.debug_hash_evaluator(True, salt=salt)
+    for g, mv in enumerate(lists):
+        e.boards_set(g, mv)
+    _search_vl(e, P, K)
+    vis, q, rn = e.root_visits(want_q=True)
+    trees = []
+    for g, b in enumerate(boards):
+        m = orc.MCTS(5, P, orc.EVAL_HASH, salt=salt)
+        acts, ovis, oq, _, _ = m.search_vl(b, P, K)
+        trees.append(m)
+        assert np.nonzero(vis[g] >= 0)[0].tolist() == acts.tolist()
+        assert np.array_equal(vis[g][acts], ovis), (g, K)
+        assert np.array_equal(q[g][acts], oq)
+        assert int(rn[g]) == m.root_visits() == P
+        assert ovis.sum() == P - 1  # a fresh root: the first playout only expands it
+    best = np.array([int(np.argmax(vis[g])) for g in range(G)], np.int32)
+    e.update_with_move(best)
+    e.boards_do_move(best)
+    _search_vl(e, P // 2, K)
+    vis2, q2, rn2 = e.root_visits(want_q=True)
+    for g, b in enumerate(boards):
+        trees[g].update_with_move(int(best[g]))
+        b.do_move(int(best[g]))
+        acts, ovis, oq, _, _ = trees[g].search_vl(b, P // 2, K)
+        if b.game_end()[0]:
+            assert (vis2[g] < 0).all()
+        else:
+            assert np.array_equal(vis2[g][acts], ovis) and np.array_equal(q2[g][acts], oq)
+        assert int(rn2[g]) == trees[g].root_visits()
+    assert e.selfplay_stats()["pool_overflows"] == 0
+    e.close()
+
+
+def test_vl_search_with_the_net_distance_to_the_reference_is_reported():
+    """With the real net: every game gets exactly n_playout playouts, two runs agree bit for bit, and the distance of
+    the visit distribution to the REFERENCE's sequential search (golden fixture, 400 playouts, 8x8) grows with K.
+    Measured on the oracle's specification: TV mean 0.008 / 0.031 / 0.057 at K = 2 / 4 / 8 - bounds below are loose."""
+    fx = Mcts2("8_8_5")
+    G, P = 32, fx.n_playout
+    arrs = golden_net_arrays("8_8_5")
+    out = {}
+    for K in (1, 2, 4, 8):
+        runs = []
+        for _ in range(2 if K == 8 else 1):
+            e = _engine(8, 5, n_games=G, n_playout=P, net_impl=2)
+            e.set_weights(arrs)
+            for g in range(G):
+                e.boards_set(g, fx.moves(g))
+            waves = e.search(P, leaves_in_flight=K)
+            vis, rn = e.root_visits()
+            runs.append(vis.copy())
+            assert (rn == P).all() and (np.maximum(vis, 0).sum(axis=1) == P - 1).all()
+            assert e.selfplay_stats()["pool_overflows"] == 0
+            e.close()
+        if len(runs) == 2:
+            assert np.array_equal(runs[0], runs[1])  # deterministic
+        tvs = np.array([tv_distance(runs[0][g], fx.visits(1, g)) for g in range(G)])
+        same_best = sum(int(np.argmax(runs[0][g]) == np.argmax(fx.visits(1, g))) for g in range(G))
+        out[K] = (waves, tvs.mean(), tvs.max(), same_best)
+        print("K = %d: %d kernel chains, TV to the reference mean %.4f max %.4f, same most-visited move %d / %d"
+              % (K, waves, tvs.mean(), tvs.max(), same_best, G))
+    assert out[1][2] <= 0.02
+    assert out[2][1] <= 0.03 and out[4][1] <= 0.06 and out[8][1] <= 0.10
+    assert out[8][0] <= P // 8 + 12 and out[8][3] >= G * 3 // 4
