@@ -53,13 +53,106 @@ __device__ __forceinline__ void gz_vl_game(const TreeParams &p, const VlParams &
     // ---- expand + backup of the wave in flight, leaf by leaf in descent order (mcts_alphaZero.py:131-148)
     if (do_expand) {
         const int keff = vp.keff[g];
-        // one trip for the per-leaf scalars of all leaves, one for their values
+        // trip 1: the per-leaf scalars of all leaves (lane j holds leaf j)
         int my_st = 2, my_d = 0, my_slot = 0;
         double my_val = 0.0;
         if (lane < keff) {
             const size_t v = (size_t)g * K + lane;
             my_st = vp.leaf_state[v]; my_d = vp.path_len[v]; my_slot = vp.leaf_slot[v];
         }
+        const bool deep = __any_sync(0xffffffffu, my_d > 32);
+        if (!deep) {
+            // trip 2, everything at once: values, every leaf's path (lane = level), the free nodes in pop order, the
+            // leaf positions; trip 3: the statistics of every path edge.  After that the leaves are processed in order
+            // FROM REGISTERS: an edge shared by two paths of the wave sits at the same level, i.e. in the same lane,
+            // so the later path finds the earlier one's update by comparing edge ids - no reload, no wait.
+            if (lane < keff) my_val = my_st == 0 ? (double)values[my_slot] : vp.leaf_value[(size_t)g * K + lane];
+            uint32_t e_all[GZ_VL_MAXK], n_all[GZ_VL_MAXK];
+            double q_all[GZ_VL_MAXK];
+#pragma unroll
+            for (int j = 0; j < GZ_VL_MAXK; ++j) {
+                const int d = __shfl_sync(0xffffffffu, my_d, j);
+                e_all[j] = (j < keff && lane < d) ? vp.path[((size_t)g * K + j) * S + lane] : 0xffffffffu;
+            }
+            int fs_mine = -1;
+            if (lane < keff && lane < top) fs_mine = p.free_stack[nbase + top - 1 - lane];
+            BB occ_mine = bb_zero();
+            if (lane < keff) {
+                const size_t v = (size_t)g * K + lane;
+                occ_mine = bb_or(load_bb(vp.leaf_board[v].stones[0]), load_bb(vp.leaf_board[v].stones[1]));
+            }
+#pragma unroll
+            for (int j = 0; j < GZ_VL_MAXK; ++j) {
+                n_all[j] = 0u; q_all[j] = 0.0;
+                if (e_all[j] != 0xffffffffu) {
+                    NodeView nv = gz_node_view(p.pool, nbase + e_all[j] / SP, SP);
+                    n_all[j] = nv.N[e_all[j] % SP];
+                    q_all[j] = nv.Q[e_all[j] % SP];
+                }
+            }
+            int n_exp = 0;
+#pragma unroll
+            for (int j = 0; j < GZ_VL_MAXK; ++j) {
+                if (j < keff) {
+                    const int st = __shfl_sync(0xffffffffu, my_st, j), d = __shfl_sync(0xffffffffu, my_d, j);
+                    const int slot = __shfl_sync(0xffffffffu, my_slot, j);
+                    const double val = __shfl_sync(0xffffffffu, my_val, j);
+                    if (st == 0) {
+                        const int newn = __shfl_sync(0xffffffffu, fs_mine, n_exp & 31);
+                        if (n_exp < top && newn >= 0) {
+                            BB occ;
+#pragma unroll
+                            for (int wq = 0; wq < 4; ++wq) occ.w[wq] = __shfl_sync(0xffffffffu, occ_mine.w[wq], j);
+                            NodeView nv = gz_node_view(p.pool, nbase + newn, SP);
+                            unsigned cnt = 0;
+#pragma unroll
+                            for (int q = 0; q < NSL; ++q) {
+                                const int i = lane + 32 * q;
+                                const bool leg = (i < S) && !bb_test(occ, bb_bit(i, p.W));
+                                nv.P[i] = leg ? priors[(size_t)slot * S + i] : -1.f;
+                                nv.N[i] = 0u; nv.Q[i] = 0.0; nv.child[i] = -1;
+                                cnt += leg;
+                            }
+                            if (d == 0) root = newn;
+                            else {
+                                const uint32_t e = __shfl_sync(0xffffffffu, e_all[j], (d - 1) & 31);
+                                if (lane == 0) gz_node_view(p.pool, nbase + e / SP, SP).child[e % SP] = newn;
+                            }
+                            ++n_exp;
+                            cnt = __reduce_add_sync(0xffffffffu, cnt);
+                            if (lane == 0) {
+                                atomicAdd(&p.ctr->expanded_children, (unsigned long long)cnt);
+                                atomicAdd(&p.ctr->leaf_evals, 1ull);
+                            }
+                        } else if (lane == 0) {
+                            atomicAdd(&p.ctr->pool_overflows, 1ull);
+                        }
+                    }
+                    if (lane < d) { // backup of this lane's level (:57-73): latest statistics of the edge, updated, stored
+                        uint32_t n = n_all[j];
+                        double q = q_all[j];
+#pragma unroll
+                        for (int i = 0; i < j; ++i)
+                            if (e_all[i] == e_all[j]) { n = n_all[i]; q = q_all[i]; }
+                        const double x = ((d - (lane + 1)) & 1) ? val : -val;
+                        n += 1u;
+                        q = q + 1.0 * (x - q) / (double)n;
+                        n_all[j] = n; q_all[j] = q;
+                        NodeView nv = gz_node_view(p.pool, nbase + e_all[j] / SP, SP);
+                        nv.N[e_all[j] % SP] = n;
+                        nv.Q[e_all[j] % SP] = q;
+                    }
+                    {
+                        const double x = (d & 1) ? val : -val;
+                        rootN += 1u;
+                        rootQ = rootQ + 1.0 * (x - rootQ) / (double)rootN;
+                    }
+                }
+            }
+            top -= n_exp;
+            __syncwarp(); // the descents below read what other lanes have just written
+        } else {
+        // paths deeper than a warp (rare): leaf by leaf with reloads
         if (lane < keff) my_val = my_st == 0 ? (double)values[my_slot] : vp.leaf_value[(size_t)g * K + lane];
         for (int j = 0; j < keff; ++j) {
             const size_t v = (size_t)g * K + j;
@@ -98,7 +191,6 @@ __device__ __forceinline__ void gz_vl_game(const TreeParams &p, const VlParams &
                     atomicAdd(&p.ctr->pool_overflows, 1ull);
                 }
             }
-            // backup: lanes = levels, then the root (:57-73)
             for (int k = lane; k < d; k += 32) {
                 const uint32_t e = k < 32 ? e_mine : vp.path[v * S + k];
                 NodeView nv = gz_node_view(p.pool, nbase + e / SP, SP);
@@ -115,6 +207,7 @@ __device__ __forceinline__ void gz_vl_game(const TreeParams &p, const VlParams &
                 rootQ = rootQ + 1.0 * (x - rootQ) / (double)rootN;
             }
             __syncwarp(); // the next leaf's backup (and the descents below) read what other lanes have just written
+        }
         }
         if (lane == 0) {
             p.root_node[g] = root; p.root_N[g] = rootN; p.root_Q[g] = rootQ; p.free_top[g] = top;

@@ -271,6 +271,10 @@ class TrainPipeline():
         self.last_games = []
         self.continuous = bool(continuous)
         self.selfplay_slots = selfplay_slots
+        # continuous mode on several ranks: agree after every ply whether ALL ranks hold their quota and leave the
+        # collect loop together, so that no GPU idles at the next collective waiting for a slower rank (the extra
+        # games a fast rank plays meanwhile are carried to its next call, not wasted)
+        self.sync_plies = False
         self._cont = None  # continuous mode: {"next": first unreleased game serial, "games": {...}, "chunks": [...]}
 
     def get_equi_data(self, play_data):
@@ -457,7 +461,20 @@ class TrainPipeline():
 
         def have():
             return sum(1 for g in range(lo, hi) if g in c["done"])
-        while have() < n_games:
+
+        def all_ready():
+            ready = have() >= n_games
+            if not self.sync_plies:
+                return ready
+            import torch
+            import torch.distributed as dist
+            if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+                return ready
+            flag = torch.tensor([1 if ready else 0], dtype=torch.int32,
+                                device=torch.device("cuda", e.device) if dist.get_backend() == "nccl" else "cpu")
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            return bool(flag.item())
+        while not all_ready():
             e.selfplay_step(1)
             c["plies"] += 1
             n = int(e.selfplay_pending()[0])

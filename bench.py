@@ -374,36 +374,39 @@ def run_ours(args):
     coll = None
     if world > 1:
         rec_w = 4 + 5 * S_  # packed record: game id (2 floats), ply, z, pi[S], state[4S]  (train.pack_samples)
-        dev_bufs = {"states": torch.zeros((cap, 4, args.board, args.board), dtype=torch.float32, device=dev),
-                    "pis": torch.zeros((cap, S_), dtype=torch.float32, device=dev),
-                    "zs": torch.zeros(cap, dtype=torch.float32, device=dev),
-                    "game_ids": torch.zeros(cap, dtype=torch.int64, device=dev),
-                    "plies": torch.zeros(cap, dtype=torch.int32, device=dev)}
-        rec = torch.zeros((cap, rec_w), dtype=torch.float32, device=dev)
-        gathered = torch.zeros((world * cap, rec_w), dtype=torch.float32, device=dev)
-        cnt = torch.zeros(1, dtype=torch.int64, device=dev)
-        cnts = torch.zeros(world, dtype=torch.int64, device=dev)
-        ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(args.steps)]
-        coll = {"bytes_broadcast": int(flat.numel() * 4), "bytes_allgather": 0}
-        with torch.cuda.stream(stream):  # untimed: NCCL sets its channels up on the first collective of each kind and size
+        # two sets of device buffers: the all-gather of step i runs on a side stream underneath step i + 1
+        # (SURVEY 8e), fixed-size (cap rows per rank, the count in row 0 of a header) so that no rank reads a
+        # count on the host - a host read would make every step wait for the slowest rank twice
+        dev_bufs = [{"states": torch.zeros((cap, 4, args.board, args.board), dtype=torch.float32, device=dev),
+                     "pis": torch.zeros((cap, S_), dtype=torch.float32, device=dev),
+                     "zs": torch.zeros(cap, dtype=torch.float32, device=dev),
+                     "game_ids": torch.zeros(cap, dtype=torch.int64, device=dev),
+                     "plies": torch.zeros(cap, dtype=torch.int32, device=dev)} for _ in range(2)]
+        rec = [torch.zeros((cap + 1, rec_w), dtype=torch.float32, device=dev) for _ in range(2)]
+        gathered = [torch.zeros((world * (cap + 1), rec_w), dtype=torch.float32, device=dev) for _ in range(2)]
+        coll_stream = torch.cuda.Stream(device=dev)
+        ev_b = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(args.steps + 1)]
+        ev_g = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(args.steps + 1)]
+        ev_drained = [torch.cuda.Event() for _ in range(2)]
+        ev_gathered = [torch.cuda.Event() for _ in range(2)]
+        coll = {"bytes_broadcast": int(flat.numel() * 4), "bytes_allgather": int(world * (cap + 1) * rec_w * 4)}
+        with torch.cuda.stream(coll_stream):  # untimed: NCCL sets its channels up on the first collective of each kind and size
             for _ in range(2):
                 dist.broadcast(flat, src=0)
-                dist.all_gather_into_tensor(cnts, cnt)
-                dist.all_gather_into_tensor(gathered, rec)
-        stream.synchronize()
-    barrier()
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for it in range(args.steps):
+                dist.all_gather_into_tensor(gathered[0], rec[0])
+        coll_stream.synchronize()
+
+    def e2e_step(it):
+        nonlocal d2h_total
         if world == 1:
             eng.set_weights([a.numpy() for a in host_w])          # H2D: the step's inputs (weights)
         else:
             with torch.cuda.stream(stream):
-                ev[it][0].record(stream)
+                ev_b[it][0].record(stream)
                 if rank == 0:
                     flat.copy_(flat_host, non_blocking=True)      # H2D on the trainer rank
                 dist.broadcast(flat, src=0)                       # NCCL over NVLink
-                ev[it][1].record(stream)
+                ev_b[it][1].record(stream)
             stream.synchronize()
             eng.set_weights(list(torch.split(flat, sizes)))
         eng.selfplay_step(1)
@@ -412,36 +415,53 @@ def run_ours(args):
             d = eng.selfplay_drain(max_samples=cap, bufs=drain_bufs)  # D2H: samples of games that finished
             d2h_total += mv.numel() * 4 + pr.numel() * 4 + sum(v.nbytes for v in d.values())
         else:
-            d = eng.selfplay_drain(max_samples=cap, bufs=dev_bufs)    # stays on the device for the all-gather
+            k = it & 1
+            ev_gathered[k].synchronize()                          # the all-gather that last used this buffer set is over
+            d = eng.selfplay_drain(max_samples=cap, bufs=dev_bufs[k])  # stays on the device for the all-gather
             n = int(d["zs"].shape[0])
-            with torch.cuda.stream(stream):
-                rec[:n, 0] = (d["game_ids"] >> 20).to(torch.float32)
-                rec[:n, 1] = (d["game_ids"] & ((1 << 20) - 1)).to(torch.float32)
-                rec[:n, 2] = d["plies"].to(torch.float32)
-                rec[:n, 3] = d["zs"]
-                rec[:n, 4:4 + S_] = d["pis"]
-                rec[:n, 4 + S_:] = d["states"].reshape(n, -1)
-                cnt[0] = n
-                ev[it][2].record(stream)
-                dist.all_gather_into_tensor(cnts, cnt)
-                m = int(cnts.max().item())                        # the padded length every rank sends
-                out = gathered[:world * max(m, 1)]                # rank r's rows at [r * m, (r + 1) * m)
-                dist.all_gather_into_tensor(out, rec[:max(m, 1)])
-                ev[it][3].record(stream)
-            coll["bytes_allgather"] += world * m * rec_w * 4
-            # D2H of the step's result: this rank's moves / probabilities and its own finished samples' targets
-            zs_host = d["zs"].cpu()
-            d2h_total += mv.numel() * 4 + pr.numel() * 4 + zs_host.numel() * 4
+            ev_drained[k].record(stream)
+            with torch.cuda.stream(coll_stream):
+                coll_stream.wait_event(ev_drained[k])
+                ev_g[it][0].record(coll_stream)
+                r = rec[k]
+                r[0, 0] = float(n)                                # header row: this rank's sample count
+                torch.bitwise_right_shift(d["game_ids"], 20, out=tmp_i64[:n])
+                r[1:n + 1, 0] = tmp_i64[:n]
+                torch.bitwise_and(d["game_ids"], (1 << 20) - 1, out=tmp_i64[:n])
+                r[1:n + 1, 1] = tmp_i64[:n]
+                r[1:n + 1, 2] = d["plies"]
+                r[1:n + 1, 3] = d["zs"]
+                r[1:n + 1, 4:4 + S_] = d["pis"]
+                r[1:n + 1, 4 + S_:] = d["states"].reshape(n, -1)
+                dist.all_gather_into_tensor(gathered[k], r)       # rank q's rows at [q * (cap + 1), ...)
+                ev_g[it][1].record(coll_stream)
+                ev_gathered[k].record(coll_stream)
+            # D2H of the step's result besides the moves: this rank's own finished samples' targets
+            d2h_total += mv.numel() * 4 + pr.numel() * 4 + n * 4
+            zs_pinned[:n].copy_(d["zs"], non_blocking=True)
+
+    if world > 1:
+        tmp_i64 = torch.zeros(cap, dtype=torch.int64, device=dev)
+        zs_pinned = torch.zeros(cap, dtype=torch.float32).pin_memory()
+        e2e_step(args.steps)  # one untimed e2e step: allocator pools and NCCL buffers of this code path are warm afterwards
+        torch.cuda.synchronize()
+        d2h_total = 0
+    barrier()
+    torch.cuda.synchronize()
+    eng.counters(reset=True)
+    t0 = time.perf_counter()
+    for it in range(args.steps):
+        e2e_step(it)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     barrier()
     if coll is not None:
-        coll["broadcast_ms_per_step"] = sum(e[0].elapsed_time(e[1]) for e in ev) / max(args.steps, 1)
-        coll["allgather_ms_per_step"] = sum(e[2].elapsed_time(e[3]) for e in ev) / max(args.steps, 1)
-        coll["bytes_allgather"] //= max(args.steps, 1)
-        coll["what"] = ("per step inside the e2e region: weights host -> rank 0 device -> dist.broadcast -> gz_set_weights on "
-                        "every rank; after the step the finished samples (packed records) dist.all_gather_into_tensor'ed, "
-                        "padded to the largest rank's count; times from CUDA events on the engine stream")
+        coll["broadcast_ms_per_step"] = sum(ev_b[i][0].elapsed_time(ev_b[i][1]) for i in range(args.steps)) / max(args.steps, 1)
+        coll["allgather_ms_per_step"] = sum(ev_g[i][0].elapsed_time(ev_g[i][1]) for i in range(args.steps)) / max(args.steps, 1)
+        coll["what"] = ("per step inside the e2e region: weights host -> rank 0 device -> dist.broadcast (engine stream; includes the wait "
+                        "for the slowest rank of the previous step) -> gz_set_weights on every rank; after the step the finished samples "
+                        "are packed and dist.all_gather_into_tensor'ed on a side stream underneath the next step (fixed-size: %d rows "
+                        "per rank, count in a header row); times from CUDA events on those streams" % (cap + 1))
     stats2 = eng.selfplay_stats(reset=False)
     ctr2 = eng.counters(reset=True)
 
@@ -612,6 +632,7 @@ def run_c5(args):
             "buffer_size": 1 << 20, "batch_size": 512, "epochs": 5}
     tp = TrainPipeline(conf, seed=args.seed, device_buffer=True, device=local, continuous=not args.c5_batch,
                        selfplay_slots=games)
+    tp.sync_plies = world > 1
     tp.broadcast_initial_weights()
     t_play, t_upd, t_bc, t_ag, n_games, n_plies, ag_bytes = [], [], [], [], 0, 0, 0
     loss = ent = float("nan")

@@ -144,3 +144,40 @@ def test_vl_search_with_the_net_distance_to_the_reference_is_reported():
     assert out[1][2] <= 0.02
     assert out[2][1] <= 0.03 and out[4][1] <= 0.06 and out[8][1] <= 0.10
     assert out[8][0] <= P // 8 + 12 and out[8][3] >= G * 3 // 4
+
+
+@pytest.mark.parametrize("w,n,G,P", [(8, 5, 64, 300), (6, 4, 32, 200), (9, 5, 16, 150), (15, 5, 6, 80), (11, 5, 8, 60)])
+def test_fused_search_is_bit_exact_against_the_oracle_with_the_device_hash_evaluator(w, n, G, P):
+    """gz_search as the bench runs it (fused expand_select kernels, dependent-launch chain, compacted leaf batch) with
+    the device-side hash evaluator in the net's place: visit counts, float64 Q and root N identical to the oracle's
+    pointer tree, two searches with subtree reuse.  (The split API proves the same through host round trips; this
+    is the fused path itself.)"""
+    from oracle import orc
+    rng = np.random.RandomState(31 + w)
+    boards, lists = _positions(rng, w, n, G, w * w // 3)
+    salt = 4321 + w
+    e = _engine(w, n, n_games=G, n_playout=P)
+    e.debug_hash_evaluator(True, salt=salt)
+    for g, mv in enumerate(lists):
+        e.boards_set(g, mv)
+    e.search(P)
+    vis, q, rn = e.root_visits(want_q=True)
+    trees = []
+    for g, b in enumerate(boards):
+        m = orc.MCTS(5, P, orc.EVAL_HASH, salt=salt)
+        acts, ovis, oq, _ = m.search(b)
+        trees.append(m)
+        assert np.array_equal(vis[g][acts], ovis) and np.array_equal(q[g][acts], oq) and int(rn[g]) == P
+    best = np.array([int(np.argmax(vis[g])) for g in range(G)], np.int32)
+    e.update_with_move(best)
+    e.boards_do_move(best)
+    e.search(P // 2)
+    vis2, q2, rn2 = e.root_visits(want_q=True)
+    for g, b in enumerate(boards):
+        trees[g].update_with_move(int(best[g]))
+        b.do_move(int(best[g]))
+        acts, ovis, oq, _ = trees[g].search(b, P // 2)
+        if not b.game_end()[0]:
+            assert np.array_equal(vis2[g][acts], ovis) and np.array_equal(q2[g][acts], oq)
+        assert int(rn2[g]) == trees[g].root_visits()
+    e.close()
