@@ -534,12 +534,20 @@ def run_ours(args):
         roof = {"bound": "tensor", "kernel": dom, "unit": "TFLOP/s", "peak": pk["bf16_tflops_sustained"],
                 "peak_source": pk_src + ", sustained bf16 (kernel timed inside a long step)",
                 "traffic": None}
-        # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
-        # (profiles/r1_ncu_v11_summary.txt: dram__bytes_read.sum + dram__bytes_write.sum, one launch,
-        # 16384 leaves at 8x8); only quoted for the configuration it was captured on
-        if dom == "trunk_tc" and args.board == 8 and args.games == 16384:
-            roof["traffic"] = 17241856 + 512
-            roof["traffic_source"] = "profiles/r1_ncu_v11_summary.txt (ncu --set full, 1 launch; algorithmic input planes 16.8 MB)"
+        # DRAM bytes per launch of the dominant kernel: read from the committed ncu --set full capture
+        # (profiles/r2_ncu_traffic.json, written by tools/ncu_traffic.py from a launch over a KNOWN number of leaves)
+        # and scaled to the mean number of leaves a launch of this run evaluated
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r2_ncu_traffic.json")))
+            cap = [v[0] for k, v in tj["kernels"].items() if k.startswith(dom)]
+            if cap and args.board == 8 and tuple(args.trunk) == (32, 64, 128) and dom_n > 0:
+                per_unit = (cap[0]["dram_read_bytes"] + cap[0]["dram_write_bytes"]) / tj["units_per_launch"]
+                roof["traffic"] = per_unit * ctr["leaf_evals"] / dom_n
+                roof["traffic_source"] = ("profiles/r2_ncu_traffic.json: %.0f B per leaf measured by ncu (dram__bytes_read + write, one launch "
+                                          "over %d leaves) x the mean leaves per launch of this run; algorithmic input planes 1024 B per leaf"
+                                          % (per_unit, tj["units_per_launch"]))
+        except Exception as ex:
+            roof["traffic_source"] = "profiles/r2_ncu_traffic.json unreadable: %r" % (ex,)
         if dom in fl and dom_ms > 0:
             ach = ctr["leaf_evals"] * fl[dom] / (dom_ms * 1e-3) / 1e12
             roof.update({"achieved": ach, "frac": ach / pk["bf16_tflops_sustained"],
