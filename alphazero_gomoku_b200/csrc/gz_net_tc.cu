@@ -165,6 +165,21 @@ __device__ __forceinline__ void tc_tmem_ld16_nowait(uint32_t taddr, uint32_t (&v
                  : "r"(taddr)
                  : "memory");
 }
+// 8 columns, no wait
+__device__ __forceinline__ void tc_tmem_ld8_nowait(uint32_t taddr, uint32_t (&v)[8])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                 : "r"(taddr)
+                 : "memory");
+}
+// timeline marks: a volatile read with a memory clobber (clock64() may be scheduled ahead of a preceding bar.sync)
+__device__ __forceinline__ long long tc_clock()
+{
+    long long t;
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(t)::"memory");
+    return t;
+}
 __device__ __forceinline__ void tc_tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tc_bar_sync_all() { asm volatile("bar.sync 3, 544;" ::: "memory"); } // front + MMA + back warps
 // K-major, no-swizzle shared-memory matrix descriptor: rows 16 B apart inside an 8-row core
@@ -194,39 +209,38 @@ __device__ __forceinline__ void tc_split8(const float *f, uint4 &hi, uint4 &lo)
     lo = make_uint4(l[0], l[1], l[2], l[3]);
 }
 
-// conv2 epilogue for 16 output channels (half h, quarter sub) of one row: accumulator columns
-// (hi*hi + lo*hi at 0-63, hi*lo at 64-127) -> scale, bias, ReLU, hi/lo split -> act2 planes.
-// Front warps take sub 0, back-end warps sub 1 of the same rows.
+// conv2 epilogue for 8 output channels of one row - input-channel quarter `quarter` of conv3 (16 channels), of which
+// the front warps take the first 8 (sub 0) and the back-end warps the second 8 (sub 1): accumulator columns
+// (hi*hi + lo*hi at 0-63, hi*lo at 64-127) -> scale, bias, ReLU, hi/lo split -> one act2 chunk plane each.
+// conv3 consumes act2 quarter by quarter (its K = 16 MMA step is one quarter), so its first MMAs wait for this
+// much of the epilogue only.
 template <bool DENSE>
 __device__ __forceinline__ void tc_ep2_part(uint8_t *smem, uint32_t tmem_tile, uint32_t row_off, const TcConsts &cst,
-                                            float inv_s2, int half, int sub, bool valid, float *dbg_row)
+                                            float inv_s2, int quarter, int sub, bool valid, float *dbg_row)
 {
     using namespace tc;
     constexpr int CH = Lay<DENSE>::CH, OFF_ACT2 = Lay<DENSE>::OFF_ACT2;
-    uint32_t v[16], v2[16];
-    tc_tmem_ld16_nowait(tmem_tile + half * 32 + sub * 16, v);
-    tc_tmem_ld16_nowait(tmem_tile + 64 + half * 32 + sub * 16, v2);
+    uint32_t v[8], v2[8];
+    tc_tmem_ld8_nowait(tmem_tile + quarter * 16 + sub * 8, v);
+    tc_tmem_ld8_nowait(tmem_tile + 64 + quarter * 16 + sub * 8, v2);
     tc_tmem_wait_ld();
-    float f[16];
+    float f[8];
 #pragma unroll
-    for (int c = 0; c < 16; c += 2) {
-        const int ch = half * 32 + sub * 16 + c;
+    for (int c = 0; c < 8; c += 2) {
+        const int ch = quarter * 16 + sub * 8 + c;
         float2 a = __fadd2_rn(make_float2(__uint_as_float(v[c]), __uint_as_float(v[c + 1])),
                               make_float2(__uint_as_float(v2[c]), __uint_as_float(v2[c + 1])));
         a = __ffma2_rn(a, make_float2(inv_s2, inv_s2), make_float2(cst.b2[ch], cst.b2[ch + 1]));
         f[c] = valid ? fmaxf(a.x, 0.f) : 0.f;
         f[c + 1] = valid ? fmaxf(a.y, 0.f) : 0.f;
     }
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
-        uint4 hi, lo;
-        tc_split8(f + 8 * c, hi, lo);
-        *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (half * 4 + sub * 2 + c) * CH + row_off) = hi;
-        *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (8 + half * 4 + sub * 2 + c) * CH + row_off) = lo;
-    }
+    uint4 hi, lo;
+    tc_split8(f, hi, lo);
+    *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (quarter * 2 + sub) * CH + row_off) = hi;
+    *reinterpret_cast<uint4 *>(smem + OFF_ACT2 + (8 + quarter * 2 + sub) * CH + row_off) = lo;
     if (dbg_row && valid) {
 #pragma unroll
-        for (int c = 0; c < 16; ++c) dbg_row[half * 32 + sub * 16 + c] = f[c];
+        for (int c = 0; c < 8; ++c) dbg_row[quarter * 16 + sub * 8 + c] = f[c];
     }
     tc_fence_async_smem();
     tc_fence_before();
@@ -333,23 +347,47 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         __half *s_hst = reinterpret_cast<__half *>(smem + OFF_HST);
         uint32_t ph3 = 0;
         int tl_b = 0, tl_w = 0; // tl_w: per-warp release times of the conv3 accumulators (first 24 groups)
-#define TC_MARK_BACK() /* back-end marks (3 per group): conv3 done, accumulators released, copy-out done */ \
+#define TC_MARK_BACK() /* back-end marks (3 per group): previous group copied out, conv3 done, accumulators released */ \
     do {                                                                           \
-        if (timeline && blockIdx.x == 0 && tid == 320 && tl_b < 256) timeline[1024 + tl_b++] = clock64(); \
+        if (timeline && blockIdx.x == 0 && tid == 320 && tl_b < 256) timeline[1024 + tl_b++] = tc_clock(); \
     } while (0)
+        // copy a drained group's head activations out as 16-byte chunks of heads_tc_kernel's A operand:
+        // step j = [pass 2][chunk 2][board 128][8]
+        auto copy_out = [&](long long cgrp) {
+            const int per_board = 4 * g.J; // 2 passes x 2 J chunks
+            for (int idx = tid - 320; idx < g.NB * per_board; idx += 256) {
+                const int b = idx / per_board, rem = idx - b * per_board;
+                const int p = rem / (2 * g.J), c = rem - p * 2 * g.J;
+                const long long brd = cgrp * g.NB + b;
+                if (brd < B)
+                    *reinterpret_cast<uint4 *>(head_act + (size_t)(brd >> 7) * g.J * 4096 +
+                                               (size_t)((c >> 1) * 4 + p * 2 + (c & 1)) * 1024 + (size_t)(brd & 127) * 8) =
+                        *reinterpret_cast<const uint4 *>(s_hst + (size_t)idx * 8);
+            }
+        };
+        long long prev_grp = -1;
         for (long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
             const long long board = grp * g.NB + bq;
             const bool valid = geo_ok && board < B;
-            {   // second 16 channels of each conv2 epilogue half (the front warps take the first 16).
+            {   // second 8 channels of each quarter of the conv2 epilogue (the front warps take the first 8).  This comes
+                // BEFORE the previous group's copy-out: the first quarter is what the tensor pipe is waiting for.
                 float *drow = dbg ? dbg + (size_t)maxB * g.S * C1 + ((size_t)board * g.S + cell) * C2 : nullptr;
                 const uint32_t row_off = (uint32_t)(LEAD + (DENSE ? (r >> 3) * 9 + (r & 7) : r)) * 16u;
                 tc_mbar_wait(bar_c2back, ph3);
                 tc_fence_after();
                 tc_ep2_part<DENSE>(smem, tmem + t_lane + TM_C2 + tile * 128, row_off, cst, inv_s2, 0, 1, valid, drow);
-                tc_bar_sync_all(); // A
+                tc_bar_sync_all(); // A0 (also orders the staged head activations of the previous group)
                 tc_ep2_part<DENSE>(smem, tmem + t_lane + TM_C2 + tile * 128, row_off, cst, inv_s2, 1, 1, valid, drow);
+                tc_bar_sync_all(); // A1
+                tc_ep2_part<DENSE>(smem, tmem + t_lane + TM_C2 + tile * 128, row_off, cst, inv_s2, 2, 1, valid, drow);
+                tc_ep2_part<DENSE>(smem, tmem + t_lane + TM_C2 + tile * 128, row_off, cst, inv_s2, 3, 1, valid, drow);
                 tc_bar_sync_all(); // B
             }
+            if (prev_grp >= 0) {
+                copy_out(prev_grp);
+                asm volatile("bar.sync 2, 256;" ::: "memory"); // the drain below overwrites the staging buffer
+            }
+            TC_MARK_BACK();
             tc_mbar_wait(bar_mma3, ph3);
             ph3 ^= 1u;
             tc_fence_after();
@@ -406,24 +444,13 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             tc_fence_before();
             __syncwarp();
             if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_c3free) : "memory");
-            if (timeline && blockIdx.x == 0 && lane == 0 && tl_w < 24) timeline[1400 + (warp - 10) * 24 + tl_w++] = clock64();
+            if (timeline && blockIdx.x == 0 && lane == 0 && tl_w < 24) timeline[1400 + (warp - 10) * 24 + tl_w++] = tc_clock();
             TC_MARK_BACK();
-            // copy out as 16-byte chunks of heads_tc_kernel's A operand: step j = [pass 2][chunk 2][board 128][8]
-            asm volatile("bar.sync 2, 256;" ::: "memory");
-            {
-                const int per_board = 4 * g.J; // 2 passes x 2 J chunks
-                for (int idx = tid - 320; idx < g.NB * per_board; idx += 256) {
-                    const int b = idx / per_board, rem = idx - b * per_board;
-                    const int p = rem / (2 * g.J), c = rem - p * 2 * g.J;
-                    const long long brd = grp * g.NB + b;
-                    if (brd < B)
-                        *reinterpret_cast<uint4 *>(head_act + (size_t)(brd >> 7) * g.J * 4096 +
-                                                   (size_t)((c >> 1) * 4 + p * 2 + (c & 1)) * 1024 + (size_t)(brd & 127) * 8) =
-                            *reinterpret_cast<const uint4 *>(s_hst + (size_t)idx * 8);
-                }
-            }
-            asm volatile("bar.sync 2, 256;" ::: "memory");
-            TC_MARK_BACK();
+            prev_grp = grp;
+        }
+        if (prev_grp >= 0) {
+            asm volatile("bar.sync 2, 256;" ::: "memory"); // every back-end warp has staged its rows
+            copy_out(prev_grp);
         }
 #undef TC_MARK_BACK
     } else {
@@ -452,11 +479,11 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         int tl_i = 0;
 #define TC_MARK()                                                                  \
     do {                                                                           \
-        if (timeline && blockIdx.x == 0 && tid == 0 && tl_i < 256) timeline[tl_i++] = clock64(); \
+        if (timeline && blockIdx.x == 0 && tid == 0 && tl_i < 256) timeline[tl_i++] = tc_clock(); \
     } while (0)
 #define TC_MARK_MMA() /* MMA warp's own marks, second half of the buffer (7 per group) */ \
     do {                                                                           \
-        if (timeline && blockIdx.x == 0 && tid == 256 && tl_i < 256) timeline[256 + tl_i++] = clock64(); \
+        if (timeline && blockIdx.x == 0 && tid == 256 && tl_i < 256) timeline[256 + tl_i++] = tc_clock(); \
     } while (0)
 
         // input planes -> A0 chunk 0 (fp16 hi in channels 0-3, lo in 4-7); front warps
@@ -553,31 +580,35 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             tc_umma_commit(leader, bar_mma);
             tc_umma_commit(leader, bar_c2back);
         };
-        // front warps: conv2 accumulators (hi*hi + lo*hi in columns 0-63, hi*lo in 64-127) -> act2,
-        // one 32-channel half at a time so conv3 can start on channels 0-31
-        auto ep2 = [&](long long board, bool valid, int half) {
-            tc_ep2_part<DENSE>(smem, tmem + t_lane + TM_C2 + tile * 128, row_off, cst, inv_s2, half, 0, valid,
+        // front warps: conv2 accumulators (hi*hi + lo*hi in columns 0-63, hi*lo in 64-127) -> act2, one 16-channel
+        // quarter at a time (8 channels here, 8 in the back-end warps): conv3 starts on channels 0-15
+        auto ep2 = [&](long long board, bool valid, int quarter) {
+            tc_ep2_part<DENSE>(smem, tmem + t_lane + TM_C2 + tile * 128, row_off, cst, inv_s2, quarter, 0, valid,
                         dbg ? dbg + (size_t)maxB * g.S * C1 + ((size_t)board * g.S + cell) * C2 : nullptr);
+        };
+        // MMA warp: one K = 16 step (input-channel quarter 2 * h + ks) of conv3 ring stage s on both M tiles:
+        // x_hi * w_hi, x_lo * w_hi, x_hi * w_lo
+        auto conv3_step = [&](int s, uint32_t slot, int ks) {
+            const int t = s % 9, h = s / 9;
+            const uint64_t da = dAct2 + (int64_t)(shift[t] + h * ((4 * CH) / 16));
+            const uint64_t db = dRing3 + slot * (STAGE_BYTES / 16);
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+                for (int p = 0; p < 3; ++p) {
+                    const int ap = (p == 1), bp = (p == 2);
+                    tc_umma_f16(leader, tmem + TM_C3 + j * C3, da + (uint32_t)(((ap * 8 + 2 * ks) * CH) / 16 + j * TILE),
+                                db + (uint32_t)(bp * 512 + ks * 256), tc_idesc(C3), (s | ks | p) != 0);
+                }
         };
         // MMA warp: conv3 ring stages [s0, s1), h-major: 9 taps of input channels 0-31, then of 32-63
         auto issue_conv3 = [&](int s0, int s1) {
             for (int s = s0; s < s1; ++s, ++it) {
-                const int t = s % 9, h = s / 9;
                 const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
                 tc_mbar_wait(bar_full + 8 * slot, ph);
                 tc_fence_after();
-                const uint64_t da = dAct2 + (int64_t)(shift[t] + h * ((4 * CH) / 16));
-                const uint64_t db = dRing3 + slot * (STAGE_BYTES / 16);
-#pragma unroll
-                for (int j = 0; j < 2; ++j)
-#pragma unroll
-                    for (int ks = 0; ks < 2; ++ks)
-#pragma unroll
-                        for (int p = 0; p < 3; ++p) {
-                            const int ap = (p == 1), bp = (p == 2);
-                            tc_umma_f16(leader, tmem + TM_C3 + j * C3, da + (uint32_t)(((ap * 8 + 2 * ks) * CH) / 16 + j * TILE),
-                                        db + (uint32_t)(bp * 512 + ks * 256), tc_idesc(C3), (s | ks | p) != 0);
-                        }
+                conv3_step(s, slot, 0);
+                conv3_step(s, slot, 1);
                 tc_umma_commit(leader, bar_empty + 8 * slot);
             }
         };
@@ -605,16 +636,28 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                 TC_MARK_MMA(); // m0
                 issue_conv2();
                 TC_MARK_MMA(); // m1: conv2 issued
-                tc_bar_sync_all(); // A: act2 channels 0-31 written
-                TC_MARK_MMA(); // m2: barrier A passed
-                if (!first_group) { // the back end must have drained the previous conv3 accumulators
-                    tc_mbar_wait(bar_c3free, c3_phase);
+                if (!first_group) { // the back end must have drained the previous conv3 accumulators (it does
+                    tc_mbar_wait(bar_c3free, c3_phase); // so while conv2 runs)
                     c3_phase ^= 1u;
                 }
                 first_group = false;
-                TC_MARK_MMA(); // m3: conv3 accumulators free
+                TC_MARK_MMA(); // m2: conv3 accumulators free
+                tc_bar_sync_all(); // A0: act2 channels 0-15 written
+                TC_MARK_MMA(); // m3: barrier A0 passed
                 tc_fence_after();
-                issue_conv3(0, 4);
+                {   // the first stage is split at its K = 16 steps: tap 0 of channels 0-15 runs under the epilogue
+                    // of channels 16-31 (same accumulation order as issue_conv3)
+                    const uint32_t slot = it % NSTAGE, ph = (it / NSTAGE) & 1u;
+                    tc_mbar_wait(bar_full + 8 * slot, ph);
+                    tc_fence_after();
+                    conv3_step(0, slot, 0);
+                    tc_bar_sync_all(); // A1: act2 channels 16-31 written
+                    tc_fence_after();
+                    conv3_step(0, slot, 1);
+                    tc_umma_commit(leader, bar_empty + 8 * slot);
+                    ++it;
+                }
+                issue_conv3(1, 4);
                 tc_bar_sync_all(); // B: act2 channels 32-63 written, next group's planes staged
                 TC_MARK_MMA(); // m4: barrier B passed
                 tc_fence_after();
@@ -630,8 +673,11 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                 tc_fence_after();
                 TC_MARK(); // 1: conv2 MMAs done
                 ep2(board, valid, 0);
-                tc_bar_sync_all(); // A
+                tc_bar_sync_all(); // A0
                 ep2(board, valid, 1);
+                tc_bar_sync_all(); // A1
+                ep2(board, valid, 2);
+                ep2(board, valid, 3);
                 if (has_next) stage_in(nboard, nvalid);
                 tc_bar_sync_all(); // B
                 TC_MARK(); // 2: conv2 epilogue done, next group staged

@@ -16,8 +16,8 @@ print('group period (cycles)', med([F[i + 1][0] - F[i][0] for i in range(5, len(
 print('front: wait conv2 %d | ep2 + stage next %d | ep1 next %d | idle %d' % (
     med([f[1] - f[0] for f in F[5:-2]]), med([f[2] - f[1] for f in F[5:-2]]), med([f[3] - f[2] for f in F[5:-2]]),
     med([F[i + 1][0] - F[i][3] for i in range(5, len(F) - 2)])))
-names = ['issue conv2', 'barrier A (ep2 half 0)', 'wait conv3 accum free', 'conv3 st 0-3 + barrier B', 'conv1 next + conv3 st 4-17',
-         'barrier C (ep1 next)']
+names = ['issue conv2', 'wait conv3 accum free', 'barrier A0 (ep2 quarter 0)', 'conv3 st 0-3 + barriers A1, B',
+         'conv1 next + conv3 st 4-17', 'barrier C (ep1 next)']
 for k in range(6):
     print('mma  %-28s %6d' % (names[k], med([m[k + 1] - m[k] for m in M[5:-2]])))
 vals = [(int(a), int(b)) for a, b in re.findall(r'(-?\d+):(-?\d+)', cta.split('duration)')[1])]
