@@ -218,7 +218,7 @@ extern "C" void gz_destroy(gz_engine *e)
                     e->sel_probs, e->out_states, e->out_pi, e->out_z, e->out_gid, e->out_ply, e->out_count,
                     e->gout_moves, e->gout_len, e->gout_winner, e->gout_gid, e->gout_count, e->counters,
                     e->roll_results, e->wts.w1, e->wts.w2, e->wts.w3, e->wts.wh, e->wts.wpfc, e->wts.wvfc,
-                    e->wts.bias, e->wts.tc_img, e->wts.tc_fcimg, e->tc_head, e->tc_dbg,
+                    e->wts.bias, e->wts.tc_img, e->wts.tc_imgp, e->wts.tc_fcimg, e->tc_head, e->tc_dbg,
                     e->wts.tcw_img1, e->wts.tcw_img2, e->wts.tcw_img3, e->tcw_a0, e->tcw_act1, e->tcw_act2, e->tcw_dbg,
                     e->vl_path, e->vl_path_len, e->vl_leaf_state, e->vl_leaf_value, e->vl_leaf_slot, e->vl_leaf_board,
                     e->vl_keff, e->vl_remaining, e->vl_planes, e->vl_probs, e->vl_values, e->vl_count};

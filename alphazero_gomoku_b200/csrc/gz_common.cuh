@@ -407,3 +407,21 @@ static cudaError_t gz_launch_chain(void (*kern)(KArgs...), dim3 grid, dim3 block
     return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 
+// the same, as thread-block clusters of `cluster` CTAs along x (grid.x must be a multiple of it)
+template <typename... KArgs, typename... Args>
+static cudaError_t gz_launch_chain_cluster(void (*kern)(KArgs...), unsigned cluster, dim3 grid, dim3 block, size_t smem,
+                                           cudaStream_t stream, Args &&...args)
+{
+    static const bool no_pdl = getenv("GZ_NO_PDL") != nullptr;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = no_pdl ? 1 : 2;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+

@@ -50,6 +50,7 @@ struct NetWeights {
     int off_b1 = 0, off_b2 = 0, off_b3 = 0, off_bh = 0, off_bp = 0, off_bv = 0, off_wv2 = 0, off_bv2 = 0;
     std::vector<float> tc_consts; // host copy of the tcgen05 trunk's epilogue constants (kernel parameter)
     uint8_t *tc_img = nullptr; // tcgen05 path: fp16 hi/lo conv weight image (gz_net_tc.cu layout)
+    uint8_t *tc_imgp = nullptr; // the same weights as two per-rank half images for the CTA-pair (cta_group::2) trunk
     float tc_inv[5] = {1.f, 1.f, 1.f, 1.f, 1.f}; // 1 / power-of-two weight scale of conv1..3, policy FC, value FC1
     uint8_t *tcw_img1 = nullptr, *tcw_img2 = nullptr, *tcw_img3 = nullptr; // wide-trunk tcgen05 path: conv weight images (gz_net_tcw.cu)
     float tcw_inv[3] = {1.f, 1.f, 1.f}; // 1 / weight scale of conv2, conv3, conv1

@@ -121,6 +121,50 @@ def test_tc_large_batch_matches_small_batches():
     e.close()
 
 
+_PAIR_SCRIPT = r"""
+import sys, numpy as np
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[1] + "/tests")
+from alphazero_gomoku_b200 import Engine
+from helpers import load_golden_weights
+out = {}
+for tag, w, n, B in (("8", 8, 5, 4099), ("6", 6, 4, 1), ("9", 9, 5, 777), ("15", 15, 5, 130)):
+    rng = np.random.RandomState(11 + w)
+    if w in (6, 8):
+        arrs = load_golden_weights("weights_%d_%d_%d" % (w, w, n))
+    else:
+        from test_gpu_net_tc import _random_weights
+        arrs = _random_weights(rng, w)
+    planes = (rng.rand(B, 4, w, w) < 0.3).astype(np.float32)
+    e = Engine(width=w, height=w, n_in_row=n, net_impl=2)
+    e.set_weights(arrs)
+    p, v = e.net_forward(planes)
+    out["p" + tag], out["v" + tag] = p, v
+    e.close()
+np.savez(sys.argv[2], **out)
+"""
+
+
+def test_tc_cta_pair_variant_matches_single_cta(tmp_path):
+    """GZ_TC_PAIR=1 runs the trunk as clusters of two CTAs issuing cta_group::2 MMAs (M = 256 over the pair, each CTA
+    holding half of every B operand; DESIGN 4.5: built, measured slower, kept as an A/B switch).  Same products in the
+    same order, so it must reproduce the shipped kernel bit for bit - dense 8x8 and padded layouts, odd group counts
+    (a peer CTA without a group), a single board."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for pair in (False, True):
+        env = dict(os.environ)
+        env.pop("GZ_TC_PAIR", None)
+        if pair:
+            env["GZ_TC_PAIR"] = "1"
+        f = str(tmp_path / ("pair%d.npz" % pair))
+        subprocess.run([sys.executable, "-c", _PAIR_SCRIPT, root, f], check=True, env=env, timeout=240)
+        outs.append(np.load(f))
+    for k in outs[0].files:
+        assert np.array_equal(outs[0][k], outs[1][k]), k
+
+
 @pytest.mark.parametrize("w,B,trunk", [(15, 5, (64, 128, 256)), (8, 700, (64, 128, 256)), (6, 41, (96, 64, 64)),
                                        (9, 333, (64, 128, 128)), (15, 160, (32, 64, 256)), (3, 1, (128, 128, 192))])
 def test_tc_wide_trunk_layers_vs_torch(w, B, trunk):
