@@ -135,6 +135,7 @@ static int gz_alloc_all(gz_engine *e)
     e->leaf_count = e->leaf_count_pair;
     GZ_TRY(gz_dalloc(e, &e->leaf_planes, G * 4 * S));
     GZ_TRY(gz_dalloc(e, &e->leaf_board, G));
+    GZ_TRY(gz_dalloc(e, &e->slot_game, G));
     GZ_TRY(gz_dalloc(e, &e->leaf_meta, G));
     GZ_TRY(gz_dalloc(e, &e->net_probs, G * S));
     GZ_TRY(gz_dalloc(e, &e->net_values, G));
@@ -213,7 +214,7 @@ extern "C" void gz_destroy(gz_engine *e)
     cudaStreamSynchronize(e->stream);
     void *ptrs[] = {e->boards, e->meta, e->active, e->pool, e->free_stack, e->free_top, e->root_node,
                     e->root_N, e->root_Q, e->path, e->path_len, e->leaf_state, e->leaf_value, e->leaf_slot,
-                    e->leaf_count_pair, e->leaf_planes, e->leaf_board, e->leaf_meta, e->net_probs, e->net_values,
+                    e->leaf_count_pair, e->leaf_planes, e->leaf_board, e->slot_game, e->leaf_meta, e->net_probs, e->net_values,
                     e->act1, e->act2, e->act3, e->stage, e->sp_moves, e->sp_pi, e->sp_game_id, e->sp_fin_flag, e->sp_serial, e->sel_moves,
                     e->sel_probs, e->out_states, e->out_pi, e->out_z, e->out_gid, e->out_ply, e->out_count,
                     e->gout_moves, e->gout_len, e->gout_winner, e->gout_gid, e->gout_count, e->counters,
@@ -476,7 +477,8 @@ int gzk_net_forward(gz_engine *e, const float *d_planes, const int32_t *d_count,
     if (impl != 1 && !gz_tc_supported(e) && gz_tcw_supported(e))
         return gz_net_forward_tcw(e, d_planes, d_count, maxB, d_probs, d_values, false);
     if (impl == 2 || (impl == 0 && gz_tc_supported(e)))
-        return gz_net_forward_tc(e, d_planes, d_count, maxB, d_probs, d_values, false);
+        return gz_net_forward_tc(e, d_planes, d_count, maxB, d_probs, d_values, false,
+                                 e->leaf_packed && d_planes == e->leaf_planes);
     return gz_net_forward_ffma(e, d_planes, d_count, maxB, d_probs, d_values);
 }
 
@@ -712,6 +714,15 @@ extern "C" int gz_debug_net_layers(gz_engine *e, const float *planes, int64_t B,
 static int gz_waves(gz_engine *e, int n)
 {
     if (n <= 0) return GZ_OK;
+    // When the leaves go to the fused tcgen05 trunk, the tree kernels do not write fp32 planes (1 KB per 8x8 leaf): they
+    // record which game owns a batch slot and the trunk's staging warps build the four planes from that game's leaf
+    // bitboards (64 B + 16 B, which the tree kernels store anyway).  GZ_LEAF_FLOAT=1 keeps the planes (A/B switch).
+    static const bool leaf_float = getenv("GZ_LEAF_FLOAT") != nullptr;
+    struct PackedScope {
+        gz_engine *e;
+        ~PackedScope() { e->leaf_packed = false; }
+    } scope{e};
+    e->leaf_packed = !leaf_float && !e->dbg_hash_on && e->wts.loaded && e->cfg.net_impl != 1 && gz_tc_supported(e);
     GZ_TRY(gzk_select(e, false));
     for (int i = 0; i < n; ++i) {
         GZ_TRY(gzk_net_forward(e, e->leaf_planes, e->leaf_count, e->G, e->net_probs, e->net_values));

@@ -94,6 +94,9 @@ struct gz_engine {
     int32_t *leaf_count_pair;
     float *leaf_planes;  // [G][4][S] compacted rows
     GameBoard *leaf_board; // [G] leaf position (by game)
+    int32_t *slot_game = nullptr; // [G] game of a leaf-batch slot: the fused tcgen05 trunk stages a leaf straight from
+                                  // leaf_board / leaf_meta of that game instead of from fp32 planes (leaf_packed)
+    bool leaf_packed = false;     // set for the duration of gz_waves when that path is taken
     GameMeta *leaf_meta;   // [G]
     float *net_probs;    // [G][S] compacted rows
     float *net_values;   // [G]

@@ -338,7 +338,8 @@ __global__ void __launch_bounds__(tc::THREADS, 1)
 trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wimg,
                 const __grid_constant__ TcConsts cst, float inv_s1, float inv_s2, float inv_s3,
                 __half *__restrict__ head_act, const int32_t *__restrict__ count, long long maxB, TcGeom g,
-                float *__restrict__ dbg, long long *__restrict__ timeline)
+                float *__restrict__ dbg, long long *__restrict__ timeline, const int32_t *__restrict__ slot_game,
+                const GameBoard *__restrict__ lboard, const GameMeta *__restrict__ lmeta)
 {
     using namespace tc;
     using L = Lay<DENSE>;
@@ -610,7 +611,18 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         // input planes -> A0 chunk 0 (fp16 hi in channels 0-3, lo in 4-7); front warps
         auto stage_in = [&](long long board, bool valid) {
             uint4 v = make_uint4(0, 0, 0, 0);
-            if (valid) {
+            if (valid && slot_game) {
+                // search leaves: slot -> game -> leaf bitboards (16-stride, bit = row * 16 + column) + meta; the four
+                // planes of game.py:92-116 in the returned (row-reversed) orientation, as gz_write_planes forms them
+                const int gme = slot_game[board];
+                const int4 mt = *reinterpret_cast<const int4 *>(lmeta + gme); // n_stones, last_move, start_player, flags
+                const int pl = (mt.z + mt.x) & 1;
+                const int rr0 = g.W - 1 - ci, bit = rr0 * 16 + cj;
+                const uint64_t own = lboard[gme].stones[pl][bit >> 6], opp = lboard[gme].stones[pl ^ 1][bit >> 6];
+                const bool is_last = mt.x > 0 && mt.y >= 0 && rr0 == mt.y / g.W && cj == mt.y % g.W;
+                v.x = (((own >> (bit & 63)) & 1ull) ? 0x3C00u : 0u) | (((opp >> (bit & 63)) & 1ull) ? 0x3C000000u : 0u);
+                v.y = (is_last ? 0x3C00u : 0u) | ((mt.x & 1) == 0 ? 0x3C000000u : 0u); // fp16 1.0 = 0x3C00; lo halves are 0
+            } else if (valid) {
                 // exact for {0,1} boards, fp32-grade for the arbitrary float states
                 // policy_value(state_batch) may be given
                 const float *pp = planes + board * 4 * g.S + cell;
@@ -1180,7 +1192,7 @@ int gz_tc_prepare_weights(gz_engine *e, std::vector<float> h[16])
                 put2(base + o, base + 8192 + o, v);
             }
     GZ_TRY(gz_upload(e, &e->wts.tc_img, img));
-    {   // CTA-pair images: rank r keeps rows [N/2 * r, N/2 * (r + 1)) of every B operand (see tc::WIMGP_BYTES)
+    if (getenv("GZ_TC_PAIR")) { // CTA-pair images: rank r keeps rows [N/2 * r, N/2 * (r + 1)) of every B operand (see tc::WIMGP_BYTES)
         std::vector<uint8_t> imgp(2 * WIMGP_BYTES, 0);
         for (int r = 0; r < 2; ++r) {
             uint8_t *dst = imgp.data() + (size_t)r * WIMGP_BYTES;
@@ -1280,8 +1292,11 @@ static int gz_tc_launch_heads(gz_engine *e, const TcGeom &g, float *d_probs, flo
                               int64_t maxB);
 
 static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t *d_count, int64_t maxB,
-                             float *d_probs, float *d_values, bool want_dbg)
+                             float *d_probs, float *d_values, bool want_dbg, bool from_leaf_boards = false)
 {
+    // from_leaf_boards: batch slot i is the leaf of game e->slot_game[i]; the planes are formed from e->leaf_board /
+    // e->leaf_meta in the kernel's staging warps and d_planes is not read
+    const int32_t *sg = from_leaf_boards ? e->slot_game : nullptr;
     using namespace tc;
     if (maxB <= 0) return GZ_OK;
     if (!gz_tc_supported(e)) { e->err = "tcgen05 net path needs a square board and the 32/64/128 trunk"; return GZ_E_INVALID; }
@@ -1304,7 +1319,7 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
     unsigned grid = (unsigned)(groups < e->n_sm ? groups : e->n_sm);
     // GZ_TC_PAIR=1: the CTA-pair (cta_group::2) trunk, clusters of two CTAs (A/B switch while it is being measured)
     static const bool pair_env = getenv("GZ_TC_PAIR") != nullptr;
-    const bool pair = pair_env && e->n_sm >= 2;
+    const bool pair = pair_env && e->n_sm >= 2 && w.tc_imgp;
     if (pair) {
         if (!(e->attr_done & 16u)) {
             GZ_CUDA(e, (cudaFuncSetAttribute(trunk_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, Lay<false>::SMEM_BYTES)));
@@ -1331,12 +1346,14 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
             GZ_CUDA(e, gz_launch_chain_cluster(kern, 2u, dim3(grid), dim3(THREADS), (size_t)smem_bytes, e->stream, d_planes,
                                                w.tc_imgp, cst, w.tc_inv[0], w.tc_inv[1], w.tc_inv[2],
                                                reinterpret_cast<__half *>(e->tc_head), d_count, (long long)maxB, g,
-                                               want_dbg ? e->tc_dbg : nullptr, d_tl));
+                                               want_dbg ? e->tc_dbg : nullptr, d_tl, sg, (const GameBoard *)e->leaf_board,
+                                               (const GameMeta *)e->leaf_meta));
         } else {
             auto kern = dense ? trunk_tc_kernel<true> : trunk_tc_kernel<false>;
             GZ_CUDA(e, gz_launch_chain(kern, dim3(grid), dim3(THREADS), (size_t)smem_bytes, e->stream, d_planes, w.tc_img, cst,
                                        w.tc_inv[0], w.tc_inv[1], w.tc_inv[2], reinterpret_cast<__half *>(e->tc_head), d_count,
-                                       (long long)maxB, g, want_dbg ? e->tc_dbg : nullptr, d_tl));
+                                       (long long)maxB, g, want_dbg ? e->tc_dbg : nullptr, d_tl, sg,
+                                       (const GameBoard *)e->leaf_board, (const GameMeta *)e->leaf_meta));
         }
     }
     if (d_tl) {

@@ -98,7 +98,8 @@ extern "C" int gz_net_forward_noalloc(gz_engine *e, const float *planes, int64_t
     auto kern = dense ? trunk_tc_kernel<true> : trunk_tc_kernel<false>;
     GZ_CUDA(e, gz_launch_chain(kern, dim3(grid), dim3(THREADS), (size_t)smem_bytes, e->stream, planes, w.tc_img, cst,
                                w.tc_inv[0], w.tc_inv[1], w.tc_inv[2], reinterpret_cast<__half *>(scratch),
-                               (const int32_t *)nullptr, (long long)B, g, (float *)nullptr, (long long *)nullptr));
+                               (const int32_t *)nullptr, (long long)B, g, (float *)nullptr, (long long *)nullptr,
+                               (const int32_t *)nullptr, (const GameBoard *)nullptr, (const GameMeta *)nullptr));
     FcTc fw;
     fw.wimg = w.tc_fcimg; fw.bp = w.bias + w.off_bp; fw.bv = w.bias + w.off_bv;
     fw.wv2 = w.bias + w.off_wv2; fw.bv2 = w.bias + w.off_bv2;

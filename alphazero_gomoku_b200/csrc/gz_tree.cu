@@ -28,7 +28,8 @@ struct TreeParams {
     double *leaf_value;
     int32_t *leaf_slot, *leaf_count;
     int32_t *leaf_zero; // fused wave kernels: the counter of the wave whose leaves were just evaluated, reset for re-use (or null)
-    float *leaf_planes;
+    float *leaf_planes;   // null: the evaluator reads leaf_board / leaf_meta through slot_game instead
+    int32_t *slot_game;   // [G] game of a leaf-batch slot
     GameBoard *leaf_board;
     GameMeta *leaf_meta;
     DevCounters *ctr;
@@ -187,9 +188,13 @@ __device__ __forceinline__ void gz_select_game(const TreeParams &p, int g, int l
             p.leaf_slot[g] = slot;
         }
         slot = __shfl_sync(0xffffffffu, slot, 0);
-        if (!PURE)
-            gz_write_planes(bb_pick(s0, s1, player == 0), bb_pick(s1, s0, player == 0), last, ns, p.W, p.H,
-                            p.leaf_planes + (size_t)slot * 4 * p.S, lane);
+        if (!PURE) {
+            if (p.leaf_planes)
+                gz_write_planes(bb_pick(s0, s1, player == 0), bb_pick(s1, s0, player == 0), last, ns, p.W, p.H,
+                                p.leaf_planes + (size_t)slot * 4 * p.S, lane);
+            else if (lane == 0)
+                p.slot_game[slot] = g;
+        }
     }
     levels_out = (unsigned)depth;
     children_out = __reduce_add_sync(0xffffffffu, nchild);
@@ -536,9 +541,10 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
         } else {
             p.leaf_state[g] = 0;
             p.leaf_slot[g] = nslot;
+            if (!p.leaf_planes) p.slot_game[nslot] = g;
         }
     }
-    if (!end) {
+    if (!end && p.leaf_planes) {
         nslot = __shfl_sync(0xffffffffu, nslot, 0);
         gz_write_planes(bb_pick(s0, s1, player == 0), bb_pick(s1, s0, player == 0), last, ns, BW, BH,
                         p.leaf_planes + (size_t)nslot * 4 * BS, lane);
@@ -694,7 +700,8 @@ static TreeParams gz_tree_params(gz_engine *e)
     p.free_stack = e->free_stack; p.free_top = e->free_top; p.root_node = e->root_node;
     p.root_N = e->root_N; p.root_Q = e->root_Q; p.path = e->path; p.path_len = e->path_len;
     p.leaf_state = e->leaf_state; p.leaf_value = e->leaf_value; p.leaf_slot = e->leaf_slot;
-    p.leaf_count = e->leaf_count; p.leaf_zero = nullptr; p.leaf_planes = e->leaf_planes; p.leaf_board = e->leaf_board;
+    p.leaf_count = e->leaf_count; p.leaf_zero = nullptr; p.leaf_planes = e->leaf_packed ? nullptr : e->leaf_planes; p.slot_game = e->slot_game;
+    p.leaf_board = e->leaf_board;
     p.leaf_meta = e->leaf_meta; p.ctr = e->counters;
     p.G = e->G; p.W = e->W; p.H = e->H; p.S = e->S; p.Sp = e->Sp; p.n_in_row = e->n_in_row;
     p.cap = e->cap; p.c_puct = e->cfg.c_puct; p.g0 = 0;

@@ -544,7 +544,9 @@ def run_ours(args):
                 per_unit = (cap[0]["dram_read_bytes"] + cap[0]["dram_write_bytes"]) / tj["units_per_launch"]
                 roof["traffic"] = per_unit * ctr["leaf_evals"] / dom_n
                 roof["traffic_source"] = ("profiles/r2_ncu_traffic.json: %.0f B per leaf measured by ncu (dram__bytes_read + write, one launch "
-                                          "over %d leaves) x the mean leaves per launch of this run; algorithmic input planes 1024 B per leaf"
+                                          "over %d leaves of the search path) x the mean leaves per launch of this run; algorithmic: 4*S "
+                                          "plane bits = 32 B per leaf (the kernel reads the leaf's 64 B bitboards + 16 B meta + 4 B slot map; "
+                                          "the rest is the 0.4 MB weight image per launch)"
                                           % (per_unit, tj["units_per_launch"]))
         except Exception as ex:
             roof["traffic_source"] = "profiles/r2_ncu_traffic.json unreadable: %r" % (ex,)

@@ -575,20 +575,25 @@ def test_dependent_launch_chain_matches_serial_launches(tmp_path):
     """The wave chain launched with programmatic dependent launch (kernels start before their
     predecessor has drained) must build the same trees as plain stream-ordered launches
     (GZ_NO_PDL=1): identical visit counts, small grids included - those are the ones where a
-    successor can become resident early."""
+    successor can become resident early.  Third arm, GZ_LEAF_FLOAT=1: the tree kernels write fp32
+    leaf planes for the trunk instead of the trunk forming them from the leaf bitboards of the slot's
+    game (the shipped path) - the same planes either way, so again identical trees (the wide trunk at
+    8x8 takes fp32 planes in both arms)."""
     import subprocess
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     script = tmp_path / "pdl_case.py"
     script.write_text(_PDL_SCRIPT.format(root=root, tests=os.path.join(root, "tests")))
     res = {}
-    for tag, extra in (("pdl", {}), ("serial", {"GZ_NO_PDL": "1"})):
-        env = {k: v for k, v in os.environ.items() if k != "GZ_NO_PDL"}
+    for tag, extra in (("pdl", {}), ("serial", {"GZ_NO_PDL": "1"}), ("float_planes", {"GZ_LEAF_FLOAT": "1"})):
+        env = {k: v for k, v in os.environ.items() if k not in ("GZ_NO_PDL", "GZ_LEAF_FLOAT")}
         env.update(extra)
         out = tmp_path / (tag + ".npz")
         subprocess.check_call([sys.executable, str(script), str(out)], env=env, timeout=600)
         res[tag] = np.load(out)
     assert sorted(res["pdl"].files) == sorted(res["serial"].files) and len(res["pdl"].files) == 40
+    assert sorted(res["pdl"].files) == sorted(res["float_planes"].files)
     for k in res["pdl"].files:
         assert res["pdl"][k].sum() > 0, k
         assert np.array_equal(res["pdl"][k], res["serial"][k]), k
+        assert np.array_equal(res["pdl"][k], res["float_planes"][k]), k
