@@ -370,8 +370,18 @@ def run_ours(args):
               "zs": torch.zeros(cap, dtype=torch.float32).pin_memory(),
               "game_ids": torch.zeros(cap, dtype=torch.int64).pin_memory(),
               "plies": torch.zeros(cap, dtype=torch.int32).pin_memory()}
-    drain_bufs = {k: v.numpy() for k, v in pinned.items()}
     coll = None
+    if world == 1:
+        # the finished-game samples of step i are drained into one of two DEVICE buffer sets and copied to the pinned
+        # host buffers on a side stream underneath step i + 1 (their size is known once the step is over; only the
+        # bulk copy is deferred - it is complete, and counted, before the timed region ends)
+        def _dev_set():
+            return {k: torch.zeros(v.shape, dtype=v.dtype, device=dev) for k, v in pinned.items()}
+        dev_bufs1 = [_dev_set() for _ in range(2)]
+        pinned2 = [pinned, {k: torch.zeros_like(v).pin_memory() for k, v in pinned.items()}]
+        copy_stream = torch.cuda.Stream(device=dev)
+        ev_dr1 = [torch.cuda.Event() for _ in range(2)]
+        ev_cp1 = [torch.cuda.Event() for _ in range(2)]
     if world > 1:
         rec_w = 4 + 5 * S_  # packed record: game id (2 floats), ply, z, pi[S], state[4S]  (train.pack_samples)
         # two sets of device buffers: the all-gather of step i runs on a side stream underneath step i + 1
@@ -412,8 +422,17 @@ def run_ours(args):
         eng.selfplay_step(1)
         eng.selfplay_last(mv.numpy(), pr.numpy())             # D2H: (move, move_probs) of the step
         if world == 1:
-            d = eng.selfplay_drain(max_samples=cap, bufs=drain_bufs)  # D2H: samples of games that finished
-            d2h_total += mv.numel() * 4 + pr.numel() * 4 + sum(v.nbytes for v in d.values())
+            k = it & 1
+            ev_cp1[k].synchronize()                               # the copy that last used this buffer set is over
+            d = eng.selfplay_drain(max_samples=cap, bufs=dev_bufs1[k])  # samples of games that finished, on the device
+            n = int(d["zs"].shape[0])
+            ev_dr1[k].record(stream)
+            with torch.cuda.stream(copy_stream):                  # D2H underneath the next step
+                copy_stream.wait_event(ev_dr1[k])
+                for name, t in d.items():
+                    pinned2[k][name][:n].copy_(t, non_blocking=True)
+                ev_cp1[k].record(copy_stream)
+            d2h_total += mv.numel() * 4 + pr.numel() * 4 + sum(t.numel() * t.element_size() for t in d.values())
         else:
             k = it & 1
             ev_gathered[k].synchronize()                          # the all-gather that last used this buffer set is over
@@ -581,7 +600,9 @@ def run_ours(args):
                     "ms_per_step": e2e_ms_max / max(args.steps, 1),
                     "net_evals_per_playout": float(ctr2["leaf_evals"]) / max(float(ctr2["playouts"]), 1.0),
                     "what": ("per step: gz_set_weights from pinned host arrays, gz_selfplay_step(1), "
-                             "gz_selfplay_last + gz_selfplay_drain into pinned host buffers; " if world == 1 else
+                             "gz_selfplay_last into pinned host buffers (synchronous), gz_selfplay_drain of the finished samples "
+                             "into a device buffer whose copy to pinned host memory runs on a side stream underneath the next "
+                             "step (all copies are complete before the timed region ends); " if world == 1 else
                              "per step: weights pinned host -> rank 0 -> NCCL broadcast -> gz_set_weights, gz_selfplay_step(1), "
                              "gz_selfplay_last into pinned host buffers, finished samples drained on the device and NCCL "
                              "all-gathered (see collectives); ") + "these steps follow the "
