@@ -121,6 +121,31 @@ def test_tc_large_batch_matches_small_batches():
     e.close()
 
 
+def test_tc_repeated_launches_are_identical():
+    """The fused trunk hands tiles between its warp sets through shared memory, TMEM and a dozen barriers; a missing
+    ordering shows up as an occasional different bit.  150 launches over the same 16384 boards (28 groups per CTA,
+    every pipeline phase overlapped with its neighbours) and 40 over ragged sizes must reproduce the first result."""
+    import torch
+    from alphazero_gomoku_b200 import Engine
+    rng = np.random.RandomState(17)
+    e = Engine(width=8, height=8, n_in_row=5, net_impl=2)
+    e.set_weights(load_golden_weights("weights_8_8_5"))
+    planes = torch.from_numpy((rng.rand(16384, 4, 8, 8) < 0.3).astype(np.float32)).cuda()
+    p0, v0 = e.net_forward(planes)
+    e.sync()
+    p0, v0 = p0.clone(), v0.clone()
+    for rep in range(150):
+        p, v = e.net_forward(planes)
+        e.sync()
+        assert torch.equal(p, p0) and torch.equal(v, v0), rep
+    for rep in range(40):
+        B = int(rng.randint(1, 16384))
+        p, v = e.net_forward(planes[:B])
+        e.sync()
+        assert torch.equal(p, p0[:B]) and torch.equal(v, v0[:B]), (rep, B)
+    e.close()
+
+
 _PAIR_SCRIPT = r"""
 import sys, numpy as np
 sys.path.insert(0, sys.argv[1]); sys.path.insert(0, sys.argv[1] + "/tests")
