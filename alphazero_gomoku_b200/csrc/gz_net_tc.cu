@@ -30,7 +30,7 @@
 namespace tc {
 constexpr int C1 = 32, C2 = 64, C3 = 128;
 constexpr int ROWS = 256;                 // output rows per group (2 M-tiles of 128)
-constexpr int W1_BYTES = 2 * 5 * 2 * 32 * 16; // conv1 weights, resident: [pass][tap pair 5][chunk 2][32][8]
+constexpr int W1_BYTES = 5 * 2 * 64 * 16;   // conv1 weights, resident: [tap pair 5][chunk 2][64 rows: pass 0 | pass 1][8]
 constexpr int NSTAGE = 4, STAGE_BYTES = 16384;
 constexpr int HST_BYTES = 8192;           // NB * J * 64 bytes <= 6144 for every supported board
 constexpr int W2_STAGE = 8192;            // one tap: [chunk 4][128 rows: 64 hi | 64 lo][8]
@@ -39,7 +39,7 @@ constexpr int N_STAGES_PER_GROUP = 5 + 18; // conv2: two taps per ring stage (4 
 constexpr size_t WIMG_BYTES = (size_t)W1_BYTES + 9 * W2_STAGE + 18 * W3_STAGE;
 // CTA-pair variant (cta_group::2): each CTA of a pair holds HALF of every B operand (the N columns are split
 // between the two CTAs), so its image is the row halves of the single-CTA one:
-//   conv1  [pass][tap pair 5][chunk 2][16][8]; conv2 tap [chunk 4][64: w_hi (rank 0) / w_lo (rank 1)][8] followed by
+//   conv1  [tap pair 5][chunk 2][32: pass 0 (rank 0) / pass 1 (rank 1)][8]; conv2 tap [chunk 4][64: w_hi (rank 0) / w_lo (rank 1)][8] followed by
 //   [chunk 4][32: w_hi rows 32r..32r+31][8] for the N = 64 product x_lo * w_hi; conv3 (tap, half) [pass][chunk 4][64][8]
 constexpr int W1P_BYTES = W1_BYTES / 2, W2P_MAIN = 4096, W2P_STAGE = 6144, W3P_STAGE = 8192;
 constexpr size_t WIMGP_BYTES = (size_t)W1P_BYTES + 9 * W2P_STAGE + 18 * W3P_STAGE; // per rank
@@ -579,12 +579,12 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         for (int t = 0; t < 9; ++t) shift[t] = (t / 3 - 1) * (DENSE ? L::VSTEP : g.P) + (t % 3 - 1);
         // descriptor bases; a row shift / chunk / slot offset is an add on the 16-byte address field
         // (B operands: the leading-dimension offset is the chunk stride = rows held by this CTA x 16 B)
-        const uint64_t dW1 = tc_desc(sbase + OFF_W1, PAIR ? 256 : 512);
+        const uint64_t dW1 = tc_desc(sbase + OFF_W1, PAIR ? 512 : 1024);
         const uint64_t dAct1 = tc_desc(sbase + OFF_ACT1 + LEAD * 16, CH, SBO), dAct2 = tc_desc(sbase + OFF_ACT2 + LEAD * 16, CH, SBO);
         const uint64_t dRing2 = tc_desc(sbase + OFF_RING, PAIR ? 1024 : 2048), dRing3 = dRing2;
         const uint64_t dRing2x = tc_desc(sbase + OFF_RING + W2P_MAIN, 512); // PAIR: the w_hi rows of the N = 64 product
         // 16-byte-unit strides inside the B images
-        constexpr uint32_t W1_BLK = PAIR ? 32 : 64, W2_TAP = (PAIR ? W2P_STAGE : W2_STAGE) / 16, W2_KS = PAIR ? 128 : 256,
+        constexpr uint32_t W1_BLK = PAIR ? 64 : 128, W2_TAP = (PAIR ? W2P_STAGE : W2_STAGE) / 16, W2_KS = PAIR ? 128 : 256,
                            W3_BP = PAIR ? 256 : 512, W3_KS = PAIR ? 128 : 256;
         // leader of a CTA pair: phases of the peer's relayed barriers
         uint32_t ph_pS = 0, ph_pC = 0, ph_pF = 0, ph_pA0 = 0, ph_pA1 = 0, ph_pB = 0;
@@ -641,7 +641,9 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
         // MMA warp: conv1 of the staged group, completion -> bar_mma.  One K = 16 MMA covers two
         // filter taps: the second 8-element K chunk is the same plane read `LBO` bytes further,
         // i.e. the descriptor's leading-dimension offset carries the row shift between the taps
-        // (pairs (0,1) (2,3) (4,5) (6,7); tap 8 is paired with zero weights).
+        // (pairs (0,1) (2,3) (4,5) (6,7); tap 8 is paired with zero weights).  Both weight passes ride in one N = 64
+        // MMA (columns 0-31: x * (w_hi, w_hi), 32-63: x * (w_lo, 0)): the 4 KB A tile is read once, which is what an
+        // N = 32 MMA is bound by; the epilogue adds the two column halves.
         auto issue_conv1 = [&]() {
             tc_fence_after();
 #pragma unroll
@@ -651,10 +653,8 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                     const int t0 = 2 * q;
                     const uint32_t lbo = (q == 4) ? 16u : (uint32_t)(shift[t0 + 1] - shift[t0]) * 16u;
                     const uint64_t da = tc_desc(sbase + OFF_A0 + (uint32_t)(LEAD + j * TILE + shift[t0]) * 16u, lbo, SBO);
-#pragma unroll
-                    for (int p = 0; p < 2; ++p)
-                        tc_umma_f16_t<PAIR>(leader, tmem + TM_C1 + j * C1, da, dW1 + (uint32_t)((p * 5 + q) * W1_BLK),
-                                            tc_idesc_t<PAIR>(C1), (q | p) != 0);
+                    tc_umma_f16_t<PAIR>(leader, tmem + TM_C1 + j * 2 * C1, da, dW1 + (uint32_t)(q * W1_BLK),
+                                        tc_idesc_t<PAIR>(2 * C1), q != 0);
                 }
             tc_umma_commit_t<PAIR>(leader, bar_mma);
         };
@@ -663,11 +663,13 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
             tc_mbar_wait(bar_mma, mma_phase);
             mma_phase ^= 1u;
             tc_fence_after();
-            uint32_t v[32];
-            tc_tmem_ld32(tmem + t_lane + TM_C1 + tile * C1, v);
+            uint32_t v[32], v2[32];
+            tc_tmem_ld32(tmem + t_lane + TM_C1 + tile * 2 * C1, v);
+            tc_tmem_ld32(tmem + t_lane + TM_C1 + tile * 2 * C1 + C1, v2);
             float f[32];
 #pragma unroll
-            for (int c = 0; c < 32; ++c) f[c] = valid ? fmaxf(fmaf(__uint_as_float(v[c]), inv_s1, cst.b1[c]), 0.f) : 0.f;
+            for (int c = 0; c < 32; ++c)
+                f[c] = valid ? fmaxf(fmaf(__uint_as_float(v[c]) + __uint_as_float(v2[c]), inv_s1, cst.b1[c]), 0.f) : 0.f;
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 uint4 hi, lo;
@@ -847,6 +849,10 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                 }
                 TC_MARK_MMA(); // m6: barrier C passed
             } else {
+                // the next group's planes first: the A0 chunk is free (conv1 of this group is long done), these warps
+                // would only wait for conv2 now, and the staging is a chain of dependent global loads (slot -> game ->
+                // leaf bitboards) that must not sit between the conv2 epilogue and barrier B
+                if (has_next) stage_in(nboard, nvalid);
                 tc_mbar_wait(bar_mma, mma_phase);
                 mma_phase ^= 1u;
                 tc_fence_after();
@@ -857,7 +863,6 @@ trunk_tc_kernel(const float *__restrict__ planes, const uint8_t *__restrict__ wi
                 tc_bar_sync_all(); // A1
                 ep2(board, valid, 2);
                 ep2(board, valid, 3);
-                if (has_next) stage_in(nboard, nvalid);
                 tc_bar_sync_all(); // B
                 TC_MARK(); // 2: conv2 epilogue done, next group staged
                 if (has_next) {
@@ -1161,15 +1166,15 @@ int gz_tc_prepare_weights(gz_engine *e, std::vector<float> h[16])
         memcpy(img.data() + off_hi, &hi, 2);
         memcpy(img.data() + off_lo, &lo, 2);
     };
-    // conv1: [pass][tap pair q][chunk 2][row 32][8]; chunk 0 = tap 2q, chunk 1 = tap 2q+1 (zero for
-    // q = 4).  The A operand carries hi(x) in elements 0-3 and lo(x) in 4-7 of a chunk, so pass 0 =
-    // (w_hi, w_hi) gives x_hi*w_hi + x_lo*w_hi and pass 1 = (w_lo, 0) gives x_hi*w_lo.
+    // conv1: [tap pair q][chunk 2][row 64][8]; chunk 0 = tap 2q, chunk 1 = tap 2q+1 (zero for q = 4); rows 0-31 =
+    // pass 0, rows 32-63 = pass 1 of output channel n.  The A operand carries hi(x) in elements 0-3 and lo(x) in 4-7
+    // of a chunk, so pass 0 = (w_hi, w_hi) gives x_hi*w_hi + x_lo*w_hi and pass 1 = (w_lo, 0) gives x_hi*w_lo.
     for (int t = 0; t < 9; ++t)
         for (int n = 0; n < C1; ++n)
             for (int ci = 0; ci < 4; ++ci) {
                 const float v = h[0][((size_t)n * 4 + ci) * 9 + t] * s1;
-                const size_t o = (((size_t)(t / 2) * 2 + (t % 2)) * 32 + n) * 16 + ci * 2;
-                put2(o, (size_t)5 * 1024 + o, v);
+                const size_t o = (((size_t)(t / 2) * 2 + (t % 2)) * 64 + n) * 16 + ci * 2;
+                put2(o, o + (size_t)32 * 16, v);
                 memcpy(img.data() + o + 8, img.data() + o, 2);
             }
     // conv2 stage t: [chunk 4][row 128: w_hi rows 0-63, w_lo rows 64-127][8]
@@ -1196,9 +1201,9 @@ int gz_tc_prepare_weights(gz_engine *e, std::vector<float> h[16])
         std::vector<uint8_t> imgp(2 * WIMGP_BYTES, 0);
         for (int r = 0; r < 2; ++r) {
             uint8_t *dst = imgp.data() + (size_t)r * WIMGP_BYTES;
-            // conv1: [pass 2][tap pair 5][chunk 2] blocks of 32 rows -> 16 rows
-            for (int blk = 0; blk < 20; ++blk)
-                memcpy(dst + (size_t)blk * 256, img.data() + (size_t)blk * 512 + (size_t)r * 256, 256);
+            // conv1: [tap pair 5][chunk 2] blocks of 64 rows -> 32 rows (rank 0: pass 0, rank 1: pass 1)
+            for (int blk = 0; blk < 10; ++blk)
+                memcpy(dst + (size_t)blk * 512, img.data() + (size_t)blk * 1024 + (size_t)r * 512, 512);
             for (int t = 0; t < 9; ++t) {
                 const uint8_t *src = img.data() + W1_BYTES + (size_t)t * W2_STAGE;
                 uint8_t *d2 = dst + W1P_BYTES + (size_t)t * W2P_STAGE;
