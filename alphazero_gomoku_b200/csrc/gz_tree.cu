@@ -347,7 +347,9 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
     const double rootQ = p.root_Q[g];
     const double lval = p.leaf_value[g];
     const GameMeta m = p.meta[g];
-    BB s0 = load_bb(p.boards[g].stones[0]), s1 = load_bb(p.boards[g].stones[1]);
+    // the position travels down the tree as ONE 64-bit word per lane: lane l < 8 holds word l & 3 of colour l >> 2
+    // (a stone is one OR in one lane; the eight words are put together again only for the win test at the leaf)
+    uint64_t bw = lane < 8 ? p.boards[g].stones[lane >> 2][lane & 3] : 0ull;
     const BB occ = bb_or(load_bb(p.leaf_board[g].stones[0]), load_bb(p.leaf_board[g].stones[1]));
     const uint32_t e_mine = p.path[(size_t)g * BS + (lane < BS ? lane : 0)];
     // ---- trip 2
@@ -506,8 +508,7 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
         }
         {
             const int bit = bb_bit(mv, BW);
-            bb_set_if(s0, bit, player == 0);
-            bb_set_if(s1, bit, player == 1);
+            if (lane == 4 * player + (bit >> 6)) bw |= 1ull << (bit & 63);
         }
         player ^= 1;
         last = mv;
@@ -516,10 +517,14 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
     }
     bool w0 = false, w1 = false;
     if (ns >= p.n_in_row + 2) {
+        // lanes 0-3 test colour 0, lanes 4-7 colour 1, one direction each: gather that colour's four words
         const int d4 = lane & 3;
         const int dir = (d4 == 0) ? 1 : (d4 == 1) ? 16 : (d4 == 2) ? 17 : 15;
+        BB c;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) c.w[k] = __shfl_sync(0xffffffffu, bw, (lane & 4) + k);
         bool line = false;
-        if (lane < 8) line = bb_has_line_dir(bb_pick(s0, s1, lane < 4), p.n_in_row, dir);
+        if (lane < 8) line = bb_has_line_dir(c, p.n_in_row, dir);
         const unsigned b = __ballot_sync(0xffffffffu, line);
         w0 = (b & 0x0Fu) != 0u;
         w1 = (b & 0xF0u) != 0u;
@@ -527,14 +532,13 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
     const int win = w0 ? 1 : (w1 ? 2 : -1);
     const bool end = (w0 || w1) || ns >= BW * BH;
     int nslot = 0;
+    if (lane < 8) p.leaf_board[g].stones[lane >> 2][lane & 3] = bw;
     if (lane == 0) {
         if (!end) nslot = atomicAdd(p.leaf_count, 1);
         p.path_len[g] = depth;
         GameMeta lm;
         lm.n_stones = ns; lm.last_move = last; lm.start_player = m.start_player; lm.flags = 0;
         p.leaf_meta[g] = lm;
-        store_bb(p.leaf_board[g].stones[0], s0);
-        store_bb(p.leaf_board[g].stones[1], s1);
         if (end) {
             p.leaf_state[g] = 1;
             p.leaf_value[g] = (win == -1) ? 0.0 : ((win == player + 1) ? 1.0 : -1.0);
@@ -544,10 +548,17 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
             if (!p.leaf_planes) p.slot_game[nslot] = g;
         }
     }
-    if (!end && p.leaf_planes) {
+    if (p.leaf_planes) { // evaluators that take fp32 planes (not the fused tcgen05 search path): rebuild both boards
+        BB s0, s1;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            s0.w[k] = __shfl_sync(0xffffffffu, bw, k);
+            s1.w[k] = __shfl_sync(0xffffffffu, bw, 4 + k);
+        }
         nslot = __shfl_sync(0xffffffffu, nslot, 0);
-        gz_write_planes(bb_pick(s0, s1, player == 0), bb_pick(s1, s0, player == 0), last, ns, BW, BH,
-                        p.leaf_planes + (size_t)nslot * 4 * BS, lane);
+        if (!end)
+            gz_write_planes(bb_pick(s0, s1, player == 0), bb_pick(s1, s0, player == 0), last, ns, BW, BH,
+                            p.leaf_planes + (size_t)nslot * 4 * BS, lane);
     }
     levels_out = (unsigned)depth;
     children_out = __reduce_add_sync(0xffffffffu, nchild);
