@@ -222,7 +222,8 @@ extern "C" void gz_destroy(gz_engine *e)
                     e->wts.bias, e->wts.tc_img, e->wts.tc_imgp, e->wts.tc_fcimg, e->tc_head, e->tc_dbg,
                     e->wts.tcw_img1, e->wts.tcw_img2, e->wts.tcw_img3, e->tcw_a0, e->tcw_act1, e->tcw_act2, e->tcw_dbg,
                     e->vl_path, e->vl_path_len, e->vl_leaf_state, e->vl_leaf_value, e->vl_leaf_slot, e->vl_leaf_board,
-                    e->vl_keff, e->vl_remaining, e->vl_planes, e->vl_probs, e->vl_values, e->vl_count};
+                    e->vl_keff, e->vl_remaining, e->vl_planes, e->vl_probs, e->vl_values, e->vl_count,
+                    e->vl_leaf_meta, e->vl_slot_leaf};
     for (void *p : ptrs) if (p) cudaFree(p);
     gz_train_free(e);
     for (int i = 0; i < 16; ++i) if (e->wts.raw[i]) cudaFree(e->wts.raw[i]);
@@ -477,8 +478,11 @@ int gzk_net_forward(gz_engine *e, const float *d_planes, const int32_t *d_count,
     if (impl != 1 && !gz_tc_supported(e) && gz_tcw_supported(e))
         return gz_net_forward_tcw(e, d_planes, d_count, maxB, d_probs, d_values, false);
     if (impl == 2 || (impl == 0 && gz_tc_supported(e)))
-        return gz_net_forward_tc(e, d_planes, d_count, maxB, d_probs, d_values, false,
-                                 e->leaf_packed && d_planes == e->leaf_planes);
+    {
+        const bool pk = e->leaf_packed && e->pk_slot && (d_planes == e->leaf_planes || d_planes == e->vl_planes);
+        return gz_net_forward_tc(e, d_planes, d_count, maxB, d_probs, d_values, false, pk ? e->pk_slot : nullptr,
+                                 e->pk_board, e->pk_meta);
+    }
     return gz_net_forward_ffma(e, d_planes, d_count, maxB, d_probs, d_values);
 }
 
@@ -720,9 +724,10 @@ static int gz_waves(gz_engine *e, int n)
     static const bool leaf_float = getenv("GZ_LEAF_FLOAT") != nullptr;
     struct PackedScope {
         gz_engine *e;
-        ~PackedScope() { e->leaf_packed = false; }
+        ~PackedScope() { e->leaf_packed = false; e->pk_slot = nullptr; }
     } scope{e};
     e->leaf_packed = !leaf_float && !e->dbg_hash_on && e->wts.loaded && e->cfg.net_impl != 1 && gz_tc_supported(e);
+    e->pk_slot = e->slot_game; e->pk_board = e->leaf_board; e->pk_meta = e->leaf_meta;
     GZ_TRY(gzk_select(e, false));
     for (int i = 0; i < n; ++i) {
         GZ_TRY(gzk_net_forward(e, e->leaf_planes, e->leaf_count, e->G, e->net_probs, e->net_values));

@@ -96,7 +96,10 @@ struct gz_engine {
     GameBoard *leaf_board; // [G] leaf position (by game)
     int32_t *slot_game = nullptr; // [G] game of a leaf-batch slot: the fused tcgen05 trunk stages a leaf straight from
                                   // leaf_board / leaf_meta of that game instead of from fp32 planes (leaf_packed)
-    bool leaf_packed = false;     // set for the duration of gz_waves when that path is taken
+    bool leaf_packed = false;     // set for the duration of gz_waves / gz_search_vl when that path is taken
+    const int32_t *pk_slot = nullptr;    // ... and then: slot -> leaf record, the records' boards and meta
+    const GameBoard *pk_board = nullptr; //     (gz_waves: slot_game / leaf_board / leaf_meta, by game;
+    const GameMeta *pk_meta = nullptr;   //      gz_search_vl: vl_slot_leaf / vl_leaf_board / vl_leaf_meta, by game * K + k)
     GameMeta *leaf_meta;   // [G]
     float *net_probs;    // [G][S] compacted rows
     float *net_values;   // [G]
@@ -154,6 +157,8 @@ struct gz_engine {
     int8_t *vl_leaf_state;
     double *vl_leaf_value;
     GameBoard *vl_leaf_board;
+    GameMeta *vl_leaf_meta = nullptr;  // [G*K]
+    int32_t *vl_slot_leaf = nullptr;   // [G*K] leaf record of a batch slot
     float *vl_planes, *vl_probs, *vl_values;
     DevCounters *counters;
     TrainState *tr;      // device train step state (master weights, Adam moments), created on first use

@@ -1297,11 +1297,11 @@ static int gz_tc_launch_heads(gz_engine *e, const TcGeom &g, float *d_probs, flo
                               int64_t maxB);
 
 static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t *d_count, int64_t maxB,
-                             float *d_probs, float *d_values, bool want_dbg, bool from_leaf_boards = false)
+                             float *d_probs, float *d_values, bool want_dbg, const int32_t *sg = nullptr,
+                             const GameBoard *sg_board = nullptr, const GameMeta *sg_meta = nullptr)
 {
-    // from_leaf_boards: batch slot i is the leaf of game e->slot_game[i]; the planes are formed from e->leaf_board /
-    // e->leaf_meta in the kernel's staging warps and d_planes is not read
-    const int32_t *sg = from_leaf_boards ? e->slot_game : nullptr;
+    // sg != null: batch slot i is leaf record sg[i]; the planes are formed from sg_board[sg[i]] / sg_meta[sg[i]] in the
+    // kernel's staging warps and d_planes is not read
     using namespace tc;
     if (maxB <= 0) return GZ_OK;
     if (!gz_tc_supported(e)) { e->err = "tcgen05 net path needs a square board and the 32/64/128 trunk"; return GZ_E_INVALID; }
@@ -1351,14 +1351,12 @@ static int gz_net_forward_tc(gz_engine *e, const float *d_planes, const int32_t 
             GZ_CUDA(e, gz_launch_chain_cluster(kern, 2u, dim3(grid), dim3(THREADS), (size_t)smem_bytes, e->stream, d_planes,
                                                w.tc_imgp, cst, w.tc_inv[0], w.tc_inv[1], w.tc_inv[2],
                                                reinterpret_cast<__half *>(e->tc_head), d_count, (long long)maxB, g,
-                                               want_dbg ? e->tc_dbg : nullptr, d_tl, sg, (const GameBoard *)e->leaf_board,
-                                               (const GameMeta *)e->leaf_meta));
+                                               want_dbg ? e->tc_dbg : nullptr, d_tl, sg, sg_board, sg_meta));
         } else {
             auto kern = dense ? trunk_tc_kernel<true> : trunk_tc_kernel<false>;
             GZ_CUDA(e, gz_launch_chain(kern, dim3(grid), dim3(THREADS), (size_t)smem_bytes, e->stream, d_planes, w.tc_img, cst,
                                        w.tc_inv[0], w.tc_inv[1], w.tc_inv[2], reinterpret_cast<__half *>(e->tc_head), d_count,
-                                       (long long)maxB, g, want_dbg ? e->tc_dbg : nullptr, d_tl, sg,
-                                       (const GameBoard *)e->leaf_board, (const GameMeta *)e->leaf_meta));
+                                       (long long)maxB, g, want_dbg ? e->tc_dbg : nullptr, d_tl, sg, sg_board, sg_meta));
         }
     }
     if (d_tl) {

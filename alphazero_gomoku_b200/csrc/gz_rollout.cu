@@ -323,7 +323,9 @@ __device__ __forceinline__ void gz_pure_wave_game(const TreeParams &p, int g, in
     const double rootQ = p.root_Q[g];
     const double lval = p.leaf_value[g];
     const GameMeta m = p.meta[g];
-    BB s0 = load_bb(p.boards[g].stones[0]), s1 = load_bb(p.boards[g].stones[1]);
+    // one 64-bit word of the position per lane on the way down (lane l < 8: word l & 3 of colour l >> 2), as in
+    // gz_expand_select_game; the boards are put together again at the leaf
+    uint64_t bw = lane < 8 ? p.boards[g].stones[lane >> 2][lane & 3] : 0ull;
     const uint32_t e_mine = p.path[(size_t)g * BS + (lane < BS ? lane : 0)];
     // ---- trip 2
     const bool do_bk = do_backup && st != 2;
@@ -404,9 +406,9 @@ __device__ __forceinline__ void gz_pure_wave_game(const TreeParams &p, int g, in
         double best = -1.0e300;
         int besti = 0x7fffffff, bestc = -1;
         uint32_t bestn = 0u;
-#pragma unroll
         // every child of a node carries the same prior 1 / k (mcts_pure.py:45): one division per lane and level
         float kf = -1.f;
+#pragma unroll
         for (int j = 0; j < NSL; ++j) kf = rP[j] >= 0.f ? rP[j] : kf;
         const double cp = (double)p.c_puct * (1.0 / (double)kf), cpsq = cp * sq;
 #pragma unroll
@@ -434,8 +436,7 @@ __device__ __forceinline__ void gz_pure_wave_game(const TreeParams &p, int g, in
         }
         {
             const int bit = bb_bit(mv, BW);
-            bb_set_if(s0, bit, player == 0);
-            bb_set_if(s1, bit, player == 1);
+            if (lane == 4 * player + (bit >> 6)) bw |= 1ull << (bit & 63);
         }
         player ^= 1;
         last = mv;
@@ -443,6 +444,12 @@ __device__ __forceinline__ void gz_pure_wave_game(const TreeParams &p, int g, in
         prev_node = node;
         prev_mv = mv;
         node = next;
+    }
+    BB s0, s1;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        s0.w[k] = __shfl_sync(0xffffffffu, bw, k);
+        s1.w[k] = __shfl_sync(0xffffffffu, bw, 4 + k);
     }
     bool w0 = false, w1 = false;
     if (ns >= p.n_in_row + 2) {

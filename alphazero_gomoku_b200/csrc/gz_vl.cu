@@ -30,7 +30,9 @@ struct VlParams {
     GameBoard *leaf_board; // [G*K]
     int32_t *keff;         // [G] leaves of the wave in flight
     int32_t *remaining;    // [G] playouts still to start
-    float *planes;         // [G*K][4][S] compacted rows
+    float *planes;         // [G*K][4][S] compacted rows, or null: the evaluator stages a leaf from leaf_board / leaf_meta
+    GameMeta *leaf_meta;   // [G*K]
+    int32_t *slot_leaf;    // [G*K] leaf record (g * K + k) of a batch slot
     int32_t *count, *count_zero; // leaf counter of this wave / the one the net consumed last (reset here)
     int K;
 };
@@ -50,6 +52,9 @@ __device__ __forceinline__ void gz_vl_game(const TreeParams &p, const VlParams &
     double rootQ = p.root_Q[g];
     int top = p.free_top[g];
     int remaining = vp.remaining[g];
+    int cellbit[NSL]; // bitboard bit of this lane's child slots (the board side is a run-time value here: divide once)
+#pragma unroll
+    for (int q = 0; q < NSL; ++q) cellbit[q] = (lane + 32 * q < S) ? bb_bit(lane + 32 * q, p.W) : 0;
     // ---- expand + backup of the wave in flight, leaf by leaf in descent order (mcts_alphaZero.py:131-148)
     if (do_expand) {
         const int keff = vp.keff[g];
@@ -108,7 +113,7 @@ __device__ __forceinline__ void gz_vl_game(const TreeParams &p, const VlParams &
 #pragma unroll
                             for (int q = 0; q < NSL; ++q) {
                                 const int i = lane + 32 * q;
-                                const bool leg = (i < S) && !bb_test(occ, bb_bit(i, p.W));
+                                const bool leg = (i < S) && !bb_test(occ, cellbit[q]);
                                 nv.P[i] = leg ? priors[(size_t)slot * S + i] : -1.f;
                                 nv.N[i] = 0u; nv.Q[i] = 0.0; nv.child[i] = -1;
                                 cnt += leg;
@@ -170,7 +175,7 @@ __device__ __forceinline__ void gz_vl_game(const TreeParams &p, const VlParams &
 #pragma unroll
                     for (int q = 0; q < NSL; ++q) {
                         const int i = lane + 32 * q;
-                        const bool leg = (i < S) && !bb_test(occ, bb_bit(i, p.W));
+                        const bool leg = (i < S) && !bb_test(occ, cellbit[q]);
                         nv.P[i] = leg ? priors[(size_t)slot * S + i] : -1.f;
                         nv.N[i] = 0u; nv.Q[i] = 0.0; nv.child[i] = -1;
                         cnt += leg;
@@ -226,7 +231,9 @@ __device__ __forceinline__ void gz_vl_game(const TreeParams &p, const VlParams &
         return;
     }
     const GameMeta m = p.meta[g];
-    const BB b0 = load_bb(p.boards[g].stones[0]), b1 = load_bb(p.boards[g].stones[1]);
+    // one 64-bit word of the position per lane on the way down (lane l < 8: word l & 3 of colour l >> 2), as in
+    // gz_expand_select_game
+    const uint64_t bw0 = lane < 8 ? p.boards[g].stones[lane >> 2][lane & 3] : 0ull;
     float rP0[NSL];
     uint32_t rN0[NSL];
     double rQ0[NSL];
@@ -240,14 +247,14 @@ __device__ __forceinline__ void gz_vl_game(const TreeParams &p, const VlParams &
             else { rP0[q] = -1.f; rN0[q] = 0u; rQ0[q] = 0.0; rC0[q] = -1; }
         }
     }
-    int plen[GZ_VL_MAXK];       // lane-uniform: length, last edge and kind of the descents kept so far
-    uint32_t plast[GZ_VL_MAXK];
-    unsigned term_mask = 0u;
+    int my_plen = 0;                  // lane i: length and last edge of kept descent i of this wave
+    uint32_t my_plast = 0xffffffffu;
+    unsigned term_mask = 0u;          // lane-uniform: descents that ended in a terminal leaf
     int keff = 0;
     unsigned nchild = 0, nlevels = 0;
     for (int j = 0; j < kmax; ++j) {
         const size_t v = (size_t)g * K + j;
-        BB s0 = b0, s1 = b1;
+        uint64_t bw = bw0;
         int player = (m.start_player + m.n_stones) & 1;
         int ns = m.n_stones, last = m.last_move;
         int node = root, depth = 0;
@@ -263,12 +270,15 @@ __device__ __forceinline__ void gz_vl_game(const TreeParams &p, const VlParams &
             int c[NSL];
 #pragma unroll
             for (int q = 0; q < NSL; ++q) c[q] = 0;
-            if (depth < GZ_VL_DEPTH) {
-                for (int i = 0; i < j; ++i) {
-                    if (depth >= plen[i]) continue;
-                    const uint32_t e = sh_edge[i][depth];
-                    if ((int)(e / SP) != node) continue;
-                    const int cell = (int)(e % SP);
+            if (j > 0 && depth < GZ_VL_DEPTH) {
+                // lane i < j looks at kept descent i: does it pass through this node at this depth, and by which child?
+                uint32_t e_i = 0xffffffffu;
+                if (lane < j && depth < my_plen) e_i = sh_edge[lane][depth];
+                unsigned mm = __ballot_sync(0xffffffffu, e_i != 0xffffffffu && (int)(e_i / SP) == node);
+                while (mm) { // one round per descent that does (all of them at the root, few further down)
+                    const int i = __ffs(mm) - 1;
+                    mm &= mm - 1u;
+                    const int cell = (int)(__shfl_sync(0xffffffffu, e_i, i) % SP);
 #pragma unroll
                     for (int q = 0; q < NSL; ++q) c[q] += (cell == lane + 32 * q);
                 }
@@ -309,9 +319,11 @@ __device__ __forceinline__ void gz_vl_game(const TreeParams &p, const VlParams &
                 }
             }
             {
-                const int bit = bb_bit(mv, p.W);
-                bb_set_if(s0, bit, player == 0);
-                bb_set_if(s1, bit, player == 1);
+                int cb = cellbit[0]; // the bit of cell mv sits in its owner lane
+#pragma unroll
+                for (int q = 1; q < NSL; ++q) cb = (mv >> 5) == q ? cellbit[q] : cb;
+                const int bit = __shfl_sync(0xffffffffu, cb, owner);
+                if (lane == 4 * player + (bit >> 6)) bw |= 1ull << (bit & 63);
             }
             player ^= 1;
             last = mv;
@@ -321,10 +333,14 @@ __device__ __forceinline__ void gz_vl_game(const TreeParams &p, const VlParams &
         __syncwarp(); // sh_edge[j] written by lane 0 is read by every lane in the next descent
         bool w0 = false, w1 = false;
         if (ns >= p.n_in_row + 2) {
+            // lanes 0-3 test colour 0, lanes 4-7 colour 1, one direction each: gather that colour's four words
             const int d4 = lane & 3;
             const int dir = (d4 == 0) ? 1 : (d4 == 1) ? 16 : (d4 == 2) ? 17 : 15;
+            BB cc;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) cc.w[k] = __shfl_sync(0xffffffffu, bw, (lane & 4) + k);
             bool line = false;
-            if (lane < 8) line = bb_has_line_dir(bb_pick(s0, s1, lane < 4), p.n_in_row, dir);
+            if (lane < 8) line = bb_has_line_dir(cc, p.n_in_row, dir);
             const unsigned b = __ballot_sync(0xffffffffu, line);
             w0 = (b & 0x0Fu) != 0u;
             w1 = (b & 0xF0u) != 0u;
@@ -332,27 +348,35 @@ __device__ __forceinline__ void gz_vl_game(const TreeParams &p, const VlParams &
         const int win = w0 ? 1 : (w1 ? 2 : -1);
         const bool end = (w0 || w1) || ns >= p.W * p.H;
         if (!end) { // a non-terminal leaf an earlier descent holds is about to be expanded: the wave ends here
-            bool taken = false;
-            for (int i = 0; i < j; ++i)
-                taken = taken || (!((term_mask >> i) & 1u) && plen[i] == depth && plast[i] == edge);
-            if (taken) break;
+            const bool mine = lane < j && !((term_mask >> lane) & 1u) && my_plen == depth && my_plast == edge;
+            if (__any_sync(0xffffffffu, mine)) break;
         }
-        plen[j] = depth;
-        plast[j] = edge;
+        if (lane == j) { my_plen = depth; my_plast = edge; }
         term_mask |= end ? (1u << j) : 0u;
         keff = j + 1;
         nlevels += (unsigned)depth;
         int slot = 0;
+        if (lane < 8) vp.leaf_board[v].stones[lane >> 2][lane & 3] = bw;
         if (lane == 0) {
             if (!end) slot = atomicAdd(vp.count, 1);
             vp.path_len[v] = depth;
-            store_bb(vp.leaf_board[v].stones[0], s0);
-            store_bb(vp.leaf_board[v].stones[1], s1);
             vp.leaf_state[v] = end ? 1 : 0;
             vp.leaf_slot[v] = slot;
             if (end) vp.leaf_value[v] = (win == -1) ? 0.0 : ((win == player + 1) ? 1.0 : -1.0);
+            else if (!vp.planes) {
+                GameMeta lm;
+                lm.n_stones = ns; lm.last_move = last; lm.start_player = m.start_player; lm.flags = 0;
+                vp.leaf_meta[v] = lm;
+                vp.slot_leaf[slot] = (int32_t)v;
+            }
         }
-        if (!end) {
+        if (!end && vp.planes) {
+            BB s0, s1;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                s0.w[k] = __shfl_sync(0xffffffffu, bw, k);
+                s1.w[k] = __shfl_sync(0xffffffffu, bw, 4 + k);
+            }
             slot = __shfl_sync(0xffffffffu, slot, 0);
             gz_write_planes(bb_pick(s0, s1, player == 0), bb_pick(s1, s0, player == 0), last, ns, p.W, p.H,
                             vp.planes + (size_t)slot * 4 * S, lane);
@@ -375,6 +399,10 @@ vl_wave_kernel(TreeParams p, VlParams vp, const float *__restrict__ priors, cons
     __shared__ uint32_t sh_edge[4][GZ_VL_MAXK][GZ_VL_DEPTH];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int g = blockIdx.x * 4 + wid;
+    // link of the dependent-launch chain heads -> this kernel -> trunk (gz_common.cuh): scheduled while the heads
+    // kernel drains, and the trunk after it may set itself up while this one runs
+    gz_pdl_wait();
+    gz_pdl_trigger();
     unsigned lv = 0, ch = 0, pl = 0;
     if (g < p.G) gz_vl_game<NSL>(p, vp, g, lane, priors, values, do_expand, do_select, sh_edge[wid], lv, ch, pl);
     if (lane == 0 && (lv | ch)) {
@@ -401,7 +429,8 @@ static int gz_vl_ensure(gz_engine *e, int K)
 {
     if (e->vl_K >= K) return GZ_OK;
     void *old[] = {e->vl_path, e->vl_path_len, e->vl_leaf_state, e->vl_leaf_value, e->vl_leaf_slot, e->vl_leaf_board,
-                   e->vl_keff, e->vl_remaining, e->vl_planes, e->vl_probs, e->vl_values, e->vl_count};
+                   e->vl_keff, e->vl_remaining, e->vl_planes, e->vl_probs, e->vl_values, e->vl_count, e->vl_leaf_meta,
+                   e->vl_slot_leaf};
     GZ_CUDA(e, cudaStreamSynchronize(e->stream));
     for (void *q : old) if (q) cudaFree(q);
     const size_t GK = (size_t)e->G * K, S = e->S;
@@ -412,6 +441,8 @@ static int gz_vl_ensure(gz_engine *e, int K)
     GZ_CUDA(e, cudaMalloc((void **)&e->vl_leaf_value, GK * sizeof(double)));
     GZ_CUDA(e, cudaMalloc((void **)&e->vl_leaf_slot, GK * sizeof(int32_t)));
     GZ_CUDA(e, cudaMalloc((void **)&e->vl_leaf_board, GK * sizeof(GameBoard)));
+    GZ_CUDA(e, cudaMalloc((void **)&e->vl_leaf_meta, GK * sizeof(GameMeta)));
+    GZ_CUDA(e, cudaMalloc((void **)&e->vl_slot_leaf, GK * sizeof(int32_t)));
     GZ_CUDA(e, cudaMalloc((void **)&e->vl_keff, (size_t)e->G * sizeof(int32_t)));
     GZ_CUDA(e, cudaMalloc((void **)&e->vl_remaining, (size_t)e->G * sizeof(int32_t)));
     GZ_CUDA(e, cudaMalloc((void **)&e->vl_planes, GK * 4 * S * sizeof(float)));
@@ -426,7 +457,7 @@ static int gz_vl_launch(gz_engine *e, const TreeParams &p, const VlParams &vp, i
 {
     const unsigned grid = gz_warp_blocks(e->G, 4);
     ProfScope ps(e, PC_SELECT);
-#define GZ_VLK(NSL) vl_wave_kernel<NSL><<<grid, 128, 0, e->stream>>>(p, vp, e->vl_probs, e->vl_values, do_expand, do_select)
+#define GZ_VLK(NSL) GZ_CUDA(e, gz_launch_chain(vl_wave_kernel<NSL>, dim3(grid), dim3(128), 0, e->stream, p, vp, (const float *)e->vl_probs, (const float *)e->vl_values, do_expand, do_select))
     switch (e->Sp / 32) {
     case 1: GZ_VLK(1); break;
     case 2: GZ_VLK(2); break;
@@ -456,7 +487,16 @@ extern "C" int gz_search_vl(gz_engine *e, int32_t n_playout, int32_t K, int32_t 
     VlParams vp;
     vp.path = e->vl_path; vp.path_len = e->vl_path_len; vp.leaf_state = e->vl_leaf_state; vp.leaf_value = e->vl_leaf_value;
     vp.leaf_slot = e->vl_leaf_slot; vp.leaf_board = e->vl_leaf_board; vp.keff = e->vl_keff; vp.remaining = e->vl_remaining;
-    vp.planes = e->vl_planes; vp.K = K;
+    vp.leaf_meta = e->vl_leaf_meta; vp.slot_leaf = e->vl_slot_leaf; vp.K = K;
+    // leaves for the fused tcgen05 trunk are staged from their bitboards, as in gz_waves (GZ_LEAF_FLOAT=1: fp32 planes)
+    static const bool leaf_float = getenv("GZ_LEAF_FLOAT") != nullptr;
+    struct PackedScope {
+        gz_engine *e;
+        ~PackedScope() { e->leaf_packed = false; e->pk_slot = nullptr; }
+    } scope{e};
+    e->leaf_packed = !leaf_float && !e->dbg_hash_on && e->wts.loaded && e->cfg.net_impl != 1 && gz_tc_supported(e);
+    e->pk_slot = e->vl_slot_leaf; e->pk_board = e->vl_leaf_board; e->pk_meta = e->vl_leaf_meta;
+    vp.planes = e->leaf_packed ? nullptr : e->vl_planes;
     GZ_CUDA(e, cudaMemsetAsync(e->vl_count, 0, 4 * sizeof(int32_t), e->stream));
     vl_init_kernel<<<(e->G + 255) / 256, 256, 0, e->stream>>>(e->active, e->vl_remaining, e->vl_keff, e->G, n_playout);
     e->launches++;
