@@ -188,6 +188,11 @@ extern "C" int gz_create(const gz_config *cfg, gz_engine **out)
         return GZ_E_CUDA;
     }
     if (cudaDeviceGetAttribute(&e->n_sm, cudaDevAttrMultiProcessorCount, cfg->device) != cudaSuccess) e->n_sm = 0;
+    if (gz_sqrt_tab_init(cfg->device) != 0) {
+        g_create_error = std::string("cudaMemcpyToSymbol(gz_sqrt_tab): ") + cudaGetErrorString(cudaGetLastError());
+        delete e;
+        return GZ_E_CUDA;
+    }
     if (cfg->stream) { e->stream = (cudaStream_t)cfg->stream; e->own_stream = false; }
     else {
         if (cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess) {

@@ -111,6 +111,28 @@ __host__ __device__ __forceinline__ bool bb_has_line_dir(const BB &b, int n, int
     for (int k = 1; k < n; ++k) t = bb_and(b, bb_shr(t, s));
     return bb_any(t);
 }
+// The same test for boards of at most 8 x 8 cells, on ONE 64-bit word: w0 / w1 are words 0 and 1 of the colour's
+// 16-stride bitboard (rows 0-3 / 4-7, 16 bits apart); the rows are squeezed to one byte each (pitch 8), a direction is
+// a shift by 1 / 8 / 9 / 7, and a run may only START where it stays on the board (columns <= W - n for E and NE,
+// >= n - 1 for NW: the range guards of game.py:144-158) - with pitch 8 there is no guard column when W = 8.
+// d4 = 0 E, 1 N, 2 NE, 3 NW, as the 16-stride shifts 1 / 16 / 17 / 15 of the callers above.
+__host__ __device__ __forceinline__ uint64_t bb8_squeeze(uint64_t x) // bytes 0, 2, 4, 6 -> 0, 1, 2, 3
+{
+    x &= 0x00FF00FF00FF00FFull;
+    x = (x | (x >> 8)) & 0x0000FFFF0000FFFFull;
+    return (x | (x >> 16)) & 0xFFFFFFFFull;
+}
+__host__ __device__ __forceinline__ bool bb8_has_line_dir(uint64_t w0, uint64_t w1, int W, int n, int d4)
+{
+    const uint64_t b = bb8_squeeze(w0) | (bb8_squeeze(w1) << 32);
+    const int s = d4 == 0 ? 1 : (d4 == 1 ? 8 : (d4 == 2 ? 9 : 7));
+    uint64_t t = b;
+    for (int k = 1; k < n; ++k) t = b & (t >> s);
+    const uint32_t ce = (W - n >= 0) ? ((2u << (W - n)) - 1u) : 0u;                       // columns 0 .. W - n
+    const uint32_t cw = (n - 1 < W) ? (((1u << W) - 1u) & ~((1u << (n - 1)) - 1u)) : 0u;  // columns n - 1 .. W - 1
+    const uint64_t col = d4 == 1 ? 0xFFull : (d4 == 3 ? (uint64_t)cw : (uint64_t)ce);
+    return (t & (col * 0x0101010101010101ull)) != 0ull;
+}
 // full-board mask for a W x H board
 __host__ __device__ __forceinline__ BB bb_board_mask(int W, int H)
 {

@@ -402,7 +402,7 @@ __device__ __forceinline__ void gz_pure_wave_game(const TreeParams &p, int g, in
     int depth = 0;
     unsigned int nchild = 0;
     while (node >= 0) {
-        const double sq = sqrt((double)Np);
+        const double sq = gz_sqrt_visits(Np);
         double best = -1.0e300;
         int besti = 0x7fffffff, bestc = -1;
         uint32_t bestn = 0u;
@@ -456,7 +456,9 @@ __device__ __forceinline__ void gz_pure_wave_game(const TreeParams &p, int g, in
         const int d4 = lane & 3;
         const int dir = (d4 == 0) ? 1 : (d4 == 1) ? 16 : (d4 == 2) ? 17 : 15;
         bool line = false;
-        if (lane < 8) line = bb_has_line_dir(bb_pick(s0, s1, lane < 4), p.n_in_row, dir);
+        if (WT > 0 && WT <= 8) { // one squeezed 64-bit word per colour (gz_common.cuh: bb8_has_line_dir)
+            if (lane < 8) line = bb8_has_line_dir(lane < 4 ? s0.w[0] : s1.w[0], lane < 4 ? s0.w[1] : s1.w[1], BW, p.n_in_row, d4);
+        } else if (lane < 8) line = bb_has_line_dir(bb_pick(s0, s1, lane < 4), p.n_in_row, dir);
         const unsigned b = __ballot_sync(0xffffffffu, line);
         w0 = (b & 0x0Fu) != 0u;
         w1 = (b & 0xF0u) != 0u;

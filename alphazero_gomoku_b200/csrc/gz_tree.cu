@@ -38,6 +38,23 @@ struct TreeParams {
     int g0; // first game of the launch (kernels that work on a slice of the games: [g0, G))
 };
 
+// sqrt(N_parent) of the PUCT score (mcts_alphaZero.py:81) for the visit counts a search actually meets: the correctly
+// rounded double, filled by the host at gz_create (IEEE sqrt on both sides, so the values ARE the device's); a
+// warp-uniform constant-bank read instead of the 13-instruction double-precision sequence, once per level.
+#define GZ_SQRT_TAB 4096
+__constant__ double gz_sqrt_tab[GZ_SQRT_TAB];
+__device__ __forceinline__ double gz_sqrt_visits(uint32_t n) { return n < GZ_SQRT_TAB ? gz_sqrt_tab[n] : sqrt((double)n); }
+static int gz_sqrt_tab_init(int device)
+{
+    static bool done[64] = {};
+    if (device >= 0 && device < 64 && done[device]) return 0;
+    static double h[GZ_SQRT_TAB];
+    for (int i = 0; i < GZ_SQRT_TAB; ++i) h[i] = std::sqrt((double)i);
+    if (cudaMemcpyToSymbol(gz_sqrt_tab, h, sizeof(h)) != cudaSuccess) return -1;
+    if (device >= 0 && device < 64) done[device] = true;
+    return 0;
+}
+
 __device__ __forceinline__ void warp_argmax(double &s, int &i)
 {
 #pragma unroll
@@ -111,7 +128,7 @@ __device__ __forceinline__ void gz_select_game(const TreeParams &p, int g, int l
     const size_t nbase = (size_t)g * p.cap;
     while (node >= 0) {
         NodeView v = gz_node_view(p.pool, nbase + node, p.Sp);
-        const double sq = sqrt((double)Np);
+        const double sq = gz_sqrt_visits(Np);
         double best = -1.0e300;
         int besti = 0x7fffffff, bestc = -1;
         uint32_t bestn = 0u;
@@ -478,7 +495,7 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
     int depth = 0;
     unsigned int nchild = 0;
     while (node >= 0) {
-        const double sq = sqrt((double)Np);
+        const double sq = gz_sqrt_visits(Np);
         double best = -1.0e300;
         int besti = 0x7fffffff, bestc = -1;
         uint32_t bestn = 0u;
@@ -517,14 +534,19 @@ __device__ __forceinline__ void gz_expand_select_game(const TreeParams &p, int g
     }
     bool w0 = false, w1 = false;
     if (ns >= p.n_in_row + 2) {
-        // lanes 0-3 test colour 0, lanes 4-7 colour 1, one direction each: gather that colour's four words
+        // lanes 0-3 test colour 0, lanes 4-7 colour 1, one direction each: gather that colour's words
         const int d4 = lane & 3;
-        const int dir = (d4 == 0) ? 1 : (d4 == 1) ? 16 : (d4 == 2) ? 17 : 15;
-        BB c;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) c.w[k] = __shfl_sync(0xffffffffu, bw, (lane & 4) + k);
         bool line = false;
-        if (lane < 8) line = bb_has_line_dir(c, p.n_in_row, dir);
+        if (WT > 0 && WT <= 8) { // rows 0-7 are words 0 and 1: the test runs on one squeezed 64-bit word
+            const uint64_t c0 = __shfl_sync(0xffffffffu, bw, lane & 4), c1 = __shfl_sync(0xffffffffu, bw, (lane & 4) + 1);
+            if (lane < 8) line = bb8_has_line_dir(c0, c1, BW, p.n_in_row, d4);
+        } else {
+            const int dir = (d4 == 0) ? 1 : (d4 == 1) ? 16 : (d4 == 2) ? 17 : 15;
+            BB c;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) c.w[k] = __shfl_sync(0xffffffffu, bw, (lane & 4) + k);
+            if (lane < 8) line = bb_has_line_dir(c, p.n_in_row, dir);
+        }
         const unsigned b = __ballot_sync(0xffffffffu, line);
         w0 = (b & 0x0Fu) != 0u;
         w1 = (b & 0xF0u) != 0u;

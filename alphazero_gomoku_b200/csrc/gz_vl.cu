@@ -283,7 +283,7 @@ __device__ __forceinline__ void gz_vl_game(const TreeParams &p, const VlParams &
                     for (int q = 0; q < NSL; ++q) c[q] += (cell == lane + 32 * q);
                 }
             }
-            const double sq = sqrt((double)Np);
+            const double sq = gz_sqrt_visits(Np);
             double best = -1.0e300;
             int besti = 0x7fffffff, bestc = -1;
             uint32_t bestn = 0u;
