@@ -922,11 +922,7 @@ heads_tc_kernel(const uint8_t *__restrict__ head_act, FcTc w, float *__restrict_
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
-    gz_pdl_wait(); // the leaf count and the head activations come from the trunk kernel before this one
-    gz_pdl_trigger();
-    const long long B = __shfl_sync(0xffffffffu, count ? (long long)*count : maxB, 0);
     const long long T = blockIdx.x;
-    if (T * 128 >= B) return;
     const uint32_t sbase = tc_smem_u32(smem);
     const uint32_t bar_full = sbase + OFF_BAR, bar_empty = sbase + OFF_BAR + 64, bar_done = sbase + OFF_BAR + 128;
     volatile uint32_t *tmem_slot = reinterpret_cast<volatile uint32_t *>(smem + OFF_BAR + 136);
@@ -959,6 +955,15 @@ heads_tc_kernel(const uint8_t *__restrict__ head_act, FcTc w, float *__restrict_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+    // everything above is private set-up (biases are weights): it runs while the trunk's last CTAs are still at
+    // work elsewhere; the leaf count and the head activations come from the trunk kernel before this one
+    gz_pdl_wait();
+    gz_pdl_trigger();
+    const long long B = __shfl_sync(0xffffffffu, count ? (long long)*count : maxB, 0);
+    if (T * 128 >= B) { // no tile for this CTA
+        if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+        return;
+    }
 
     if (warp == 5) {
         if (lane == 0) {
