@@ -252,3 +252,21 @@ def test_games_from_steps_log(tmp_path):
                     "{'steps': [112, 97, 125], 'winner': 1, 'start_player': 1}\n"
                     "\n{'steps': [9], 'winner': 1}\n")
     assert games_from_steps_log(str(path)) == [[2, [1, 2, 3, 4]], [1, [112, 97, 125]]]
+
+
+def test_one_word_win_test_matches_the_wide_detector(tmp_path):
+    """bb8_has_line_dir (gz_common.cuh), the win test of the fused tree kernels on boards up to 8 x 8, is host-callable:
+    tests/csrc/bb8_check.cu compares it on the CPU, direction by direction, with the 256-bit detector it replaces and
+    with a plain scan written from game.py:131-160 - 288 000 (position, direction) pairs over board sides 3..8 and
+    run lengths 3..6."""
+    import shutil
+    nvcc = os.environ.get("NVCC") or shutil.which("nvcc")
+    if not nvcc:
+        pytest.skip("nvcc not found")
+    exe = str(tmp_path / "bb8_check")
+    src = os.path.join(ROOT, "tests", "csrc", "bb8_check.cu")
+    subprocess.check_call([nvcc, "-O2", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-o", exe, src],
+                          stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=300)
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0 and out.stdout.startswith("ok "), out.stdout + out.stderr
+    assert int(out.stdout.split()[1]) >= 200000
